@@ -1,0 +1,168 @@
+/*
+ * wtprune.h -- C ABI of libwtprune.so, the B200 (sm_100a) implementation of the reference's
+ * DWT-prune hot path and its two sibling maskers.
+ *
+ * Every entry point replaces one interface of iAmGiG/WaveletTransforms (paths relative to the
+ * reference checkout) or of the third-party code that interface calls (PyWavelets / NumPy / ATen,
+ * which are not part of the reference tree).  Plain pointers and sizes only: no torch types.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative WT_E_* code on failure; wt_last_error()
+ *     returns a thread-local message for the last failure on the calling thread;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream);
+ *   - device pointers unless a parameter is documented as HOST;
+ *   - all tensors are contiguous row-major fp32; a "plane" is the last two axes (H x W) and
+ *     `batch` is the product of all leading axes (conv weight [O,I,kH,kW] -> batch O*I, H kH, W kW);
+ *   - the library never falls back to the CPU: without a usable CUDA device every compute entry
+ *     point fails with WT_E_CUDA.
+ */
+#ifndef WTPRUNE_H
+#define WTPRUNE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WT_OK 0
+#define WT_E_INVALID (-1)   /* bad argument (unknown wavelet / mode, level < 0, null pointer ...) */
+#define WT_E_CUDA (-2)      /* CUDA runtime failure (message in wt_last_error) */
+#define WT_E_WORKSPACE (-3) /* caller workspace too small */
+#define WT_E_UNSUPPORTED (-4)
+
+/* pywt boundary modes on the reference's path: dwt_pruning.py:35 (default 'periodization');
+ * 'symmetric' is pywt's own default and the second mode carried. */
+#define WT_MODE_PERIODIZATION 0
+#define WT_MODE_SYMMETRIC 1
+
+/* np.percentile arithmetic: the reference pins numpy 1.22.4 (requirements.txt:2),
+ * the GPU box runs numpy 2.x. */
+#define WT_NUMPY_LEGACY_1_22 0
+#define WT_NUMPY_NEP50_2X 1
+
+/* threshold kinds */
+#define WT_THRESHOLD_PERCENTILE 0 /* dwt_pruning.py:25-32 */
+#define WT_THRESHOLD_ABSOLUTE 1   /* dwt_pruning_NoEntropy.py:45 */
+
+typedef struct WtLayerDesc {
+    const float* in; /* weight tensor [batch][H][W] (device; HOST for host-I/O plans) */
+    float* out;      /* pruned tensor, same shape; may alias `in` */
+    int64_t batch;   /* product of leading axes; a <2-D tensor is batch=1,H=1,W=numel with level 0 */
+    int32_t H, W;
+    int32_t level;   /* decomposition level actually applied to this tensor (>= 0); 0 = the
+                        select-and-zero path wavedec2(level=0) degenerates to */
+    int32_t reserved;
+} WtLayerDesc;
+
+typedef struct WtPlan WtPlan;
+
+/* ---- metadata ------------------------------------------------------------------------------ */
+
+/* library / ABI version (bumped on any signature change) */
+int wt_version(void);
+const char* wt_last_error(void);
+
+/* pywt.Wavelet(name): id for the other calls and dec_len.  Names = the --wavelet enum of
+ * ResNet/main_pruning.py:89-96.  Unknown name -> WT_E_INVALID (pywt raises ValueError). */
+int wt_wavelet_lookup(const char* name, int* id, int* dec_len);
+/* copies the four float64 filters (dec_lo, dec_hi, rec_lo, rec_hi), each `dec_len` long (HOST) */
+int wt_wavelet_filters(int wavelet_id, double* dec_lo, double* dec_hi, double* rec_lo, double* rec_hi);
+
+/* pywt.dwt_max_level(data_len, filter_len) as used by calculate_max_level, dwt_pruning.py:12-13 */
+int wt_dwt_max_level(int data_len, int filter_len);
+/* pywt.dwt_coeff_len(data_len, filter_len, mode) */
+int wt_dwt_coeff_len(int data_len, int filter_len, int mode);
+/* per-plane shape of pywt.coeffs_to_array(wavedec2(...))[0] (dwt_pruning.py:69-70) and the number
+ * of real coefficients inside it (the rest is padding zeros that np.percentile counts) */
+int wt_packed_shape(int H, int W, int wavelet_id, int level, int mode, int* side_h, int* side_w,
+                    int64_t* coeffs_per_plane);
+
+/* np.percentile's index arithmetic (method='linear') for a population of n values:
+ * order-statistic ranks k0 <= k1 and interpolation weight gamma, under either NumPy semantic. */
+int wt_percentile_plan(int64_t n, double percentile, int numpy_semantics, int64_t* k0, int64_t* k1,
+                       double* gamma);
+
+/* ---- the hot path: plans ------------------------------------------------------------------- */
+
+/*
+ * Build a plan that prunes `n_layers` tensors the way
+ *   multi_resolution_analysis  (ResNet/dwt_pruning.py:35-95, threshold_kind PERCENTILE) or
+ *   multi_resolution_analysis  (ResNet/dwt_pruning_NoEntropy.py:12-62, threshold_kind ABSOLUTE)
+ * does for each of them: wavedec2(level=layers[i].level, mode, axes=(-2,-1)) -> coeffs_to_array ->
+ * threshold -> array_to_coeffs -> waverec2 -> crop to the input shape -> zero count.
+ * `threshold_value` is the percentile (0..100) or the absolute threshold.
+ * host_io = 0: layers[i].in/out are device pointers (may alias).  host_io = 1: they are HOST
+ * pointers; wt_plan_run then copies in, prunes and copies out (staging owned by the plan).
+ * `layers` is copied; the caller may free it after the call.
+ */
+int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavelet_id, int mode,
+                   int threshold_kind, double threshold_value, int numpy_semantics, int host_io,
+                   WtPlan** plan_out);
+int wt_plan_destroy(WtPlan* plan);
+/* bytes of device memory the plan owns (coefficient workspace, histograms, tables, staging) */
+size_t wt_plan_device_bytes(const WtPlan* plan);
+/* number of kernel launches one wt_plan_run enqueues */
+int wt_plan_num_launches(const WtPlan* plan);
+/* re-point the plan at other tensors of identical shapes (same n_layers, batch, H, W, level) */
+int wt_plan_set_io(WtPlan* plan, const WtLayerDesc* layers, int n_layers);
+/* enqueue the whole pruning pass on `stream`; no host synchronisation for device-I/O plans */
+int wt_plan_run(WtPlan* plan, void* stream);
+/*
+ * Results of the last run (HOST arrays; synchronises `stream`):
+ *   counts[i*3+0] = numel               ("Original Parameter Count")
+ *   counts[i*3+1] = nonzeros after      (dwt_pruning.py:119-120)
+ *   counts[i*3+2] = zeros after         (dwt_pruning.py:88, torch.sum(pruned == 0))
+ *   nonzero_before[i] = nonzeros of the input (dwt_pruning_NoEntropy.py:58,81); may be NULL
+ *   thresholds[i] = the float32 value the strict `<` compared against; may be NULL
+ */
+int wt_plan_results(WtPlan* plan, void* stream, int64_t* counts, int64_t* nonzero_before,
+                    float* thresholds);
+/* device address of the int64 [n_layers][4] result block {numel, nonzero, zeros, nonzero_before} */
+int wt_plan_counts_device(WtPlan* plan, const int64_t** counts_dev);
+
+/* one-shot convenience: create + run + results + destroy (device I/O). */
+int wt_dwt_prune_f32(const WtLayerDesc* layers, int n_layers, int wavelet_id, int mode,
+                     int threshold_kind, double threshold_value, int numpy_semantics, void* stream,
+                     int64_t* counts, int64_t* nonzero_before, float* thresholds);
+
+/* ---- building blocks (exposed for tests and for callers that keep coefficients) ------------- */
+
+/* Exact order statistics of |x| over a population of n explicit values plus `implicit_zeros`
+ * zeros: ab_out[0] = sorted[k0], ab_out[1] = sorted[k1] (device float[2]).  Replaces the
+ * np.partition inside np.percentile (dwt_pruning.py:27). */
+int wt_select_abs_f32(const float* x, int64_t n, int64_t implicit_zeros, int64_t k0, int64_t k1,
+                      float* ab_out, void* stream);
+
+/* wavedec2 + coeffs_to_array: x [batch][H][W] -> packed [batch][side_h][side_w] (padding = 0),
+ * exactly the array dwt_pruning.py:69-70 hands to the thresholding. */
+int wt_wavedec2_packed_f32(const float* x, int64_t batch, int H, int W, int wavelet_id, int level,
+                           int mode, float* packed, void* stream);
+/* array_to_coeffs + waverec2 + crop to [batch][H][W] (dwt_pruning.py:75-82) */
+int wt_waverec2_packed_f32(const float* packed, int64_t batch, int H, int W, int wavelet_id,
+                           int level, int mode, float* out, void* stream);
+
+/* ---- sibling maskers ------------------------------------------------------------------------ */
+
+/* percentage_min_pruning (ResNet/min_weight_pruning.py:66-74), in place, for a group of tensors:
+ * zero the k[i] entries of smallest |w| of tensor i (ties: lowest flat index first), then
+ * nonzero_out[i] = count_nonzero (min_weight_pruning.py:108-109).  w[i]: device pointers given in
+ * a HOST array; n, k: HOST arrays; nonzero_out: HOST array (the call synchronises `stream`). */
+int wt_min_weight_prune_f32(float* const* w, const int64_t* n, const int64_t* k, int n_tensors,
+                            void* stream, int64_t* nonzero_out);
+
+/* flat[idx[:k]] = 0 ; count_nonzero  (ResNet/random_pruning.py:53-58), in place.  idx: device
+ * int64 indices produced by torch.randperm (kept as the RNG so masks match bit for bit).
+ * nonzero_out: device int64[1]. */
+int wt_scatter_zero_f32(float* w, int64_t n, const int64_t* idx, int64_t k, int64_t* nonzero_out,
+                        void* stream);
+
+/* count of x != 0 (torch.count_nonzero) and of |x| < eps (calculate_sparsity,
+ * testing_suite/eval_model.py:7-20); out: device int64[2] = {nonzero, below_eps} */
+int wt_count_f32(const float* x, int64_t n, float eps, int64_t* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WTPRUNE_H */

@@ -1,0 +1,133 @@
+// wt_common.cuh -- shared declarations of libwtprune (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/wtprune.h"
+
+#define WT_MAX_FILTER 18
+#define WT_MAX_LEVEL 32
+
+void wt_set_error(const char* fmt, ...);
+
+#define WT_CUDA(expr)                                                                      \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            wt_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                         __LINE__);                                                        \
+            return WT_E_CUDA;                                                              \
+        }                                                                                  \
+    } while (0)
+
+#define WT_CHECK(cond, code, ...)      \
+    do {                               \
+        if (!(cond)) {                 \
+            wt_set_error(__VA_ARGS__); \
+            return (code);             \
+        }                              \
+    } while (0)
+
+// ---- device info ------------------------------------------------------------------------------
+struct WtDeviceInfo {
+    int device;
+    int sm_count;
+    int coop;
+};
+int wt_device_info(WtDeviceInfo* info);
+
+// ---- wavelet banks (fp32 casts of the generated double tables) ---------------------------------
+struct WtBank {
+    int F;
+    float dec_lo[WT_MAX_FILTER], dec_hi[WT_MAX_FILTER], rec_lo[WT_MAX_FILTER], rec_hi[WT_MAX_FILTER];
+};
+int wt_get_bank(int wavelet_id, WtBank* bank);
+int wt_idwt_len(int n, int F, int mode);
+// sizes[0] = n, sizes[l] = coefficient length at level l
+void wt_level_sizes(int n, int F, int mode, int level, int* sizes);
+
+// ---- select (wt_select.cu) ----------------------------------------------------------------------
+// One job = one population whose order statistics are wanted: the explicit values x[0..n) plus
+// `zeros` implicit zeros (coeffs_to_array padding).  Jobs with out != nullptr also get the
+// level-0 apply phase (out = |x| < t ? 0 : x) and zero counting fused into the same launch.
+#define WT_SEL_TILE 4096
+#define WT_SEL_THREADS 512
+#define WT_SEL_BINS1 4096  // key bits 30..19
+#define WT_SEL_BINS2 1024  // key bits 18..9
+#define WT_SEL_BINS3 512   // key bits  8..0
+
+enum { WT_LERP_LEGACY = 0, WT_LERP_NEP50 = 1, WT_LERP_ABSOLUTE = 2 };
+
+struct WtSelJob {
+    const float* x;
+    float* out;  // nullable
+    long long n;
+    long long zeros;
+    long long k0, k1;
+    double gamma;
+    float abs_threshold;
+    int lerp_mode;
+    int tile_begin;  // first tile of this job in the flattened tile space
+    int n_tiles;
+    int layer;  // index into the counts / thresholds arrays
+    int pad;
+};
+
+struct WtSelState {  // per job, device
+    unsigned int prefix[2];
+    unsigned long long rem[2];
+    float a, b, t;
+    int pad;
+};
+
+struct WtSelArgs {
+    const WtSelJob* jobs;
+    int n_jobs;
+    int n_tiles;
+    WtSelState* state;
+    unsigned long long* hist1;  // [n_jobs][BINS1]
+    unsigned long long* hist2;  // [n_jobs][2][BINS2]
+    unsigned long long* hist3;  // [n_jobs][2][BINS3]
+    unsigned int* done;         // [n_jobs][4]
+    float* thresholds;          // [n_layers]
+    long long* counts;          // [n_layers][4] {numel, nonzero, zeros, nonzero_before}
+    int any_apply;              // at least one job has out != nullptr
+};
+
+size_t wt_select_scratch_bytes(int n_jobs);  // hist1+hist2+hist3+done+state, contiguous, memset to 0 before launch
+// lays out args over a zeroed scratch block
+void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
+int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
+
+// ---- level-0 apply for absolute thresholds and generic elementwise helpers (wt_select.cu) --------
+int wt_apply_threshold_launch(const float* x, float* out, long long n, const float* thr_dev, float thr_host,
+                              long long* counts4, cudaStream_t stream);
+
+// ---- small-plane regime (wt_small.cu): one thread per kH x kW plane, all levels in registers -----
+#define WT_SMALL_THREADS 128
+#define WT_SMALL_MAX_LEVEL 6
+
+struct WtSmallJob {
+    const float* in;   // [batch][H][W]
+    float* out;        // [batch][H][W]
+    float* coef;       // [ncoef][batch]  (coefficient-major so a warp's accesses coalesce)
+    long long batch;
+    int level;
+    int layer;
+    int tile_begin;
+    int n_tiles;
+    float abs_threshold;
+    int use_abs;       // 1: compare against abs_threshold, 0: against thresholds[layer]
+};
+
+// true when (H, W, F, level, mode) has a register-resident instantiation
+bool wt_small_supported(int H, int W, int F, int level, int mode);
+// number of real coefficients per plane (periodization)
+int wt_small_ncoef(int H, int W, int level);
+int wt_small_analysis_launch(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                             long long* counts, cudaStream_t stream);
+int wt_small_synthesis_launch(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                              const float* thresholds, long long* counts, cudaStream_t stream);

@@ -1,0 +1,417 @@
+// wt_small.cu -- small-plane regime of the DWT prune path (kH x kW conv-kernel planes).
+//
+// Replaces pywt.wavedec2 / pywt.waverec2 over axes (-2,-1) of a conv weight [O,I,kH,kW]
+// (/root/reference/ResNet/dwt_pruning.py:67-68,77; dwt_pruning_NoEntropy.py:41,49) for the plane
+// sizes conv layers have (1x1, 3x3, 5x5, 7x7), mode 'periodization', any of the 17 wavelets,
+// levels 0..WT_SMALL_MAX_LEVEL -- including N < F where every tap wraps several times (F6).
+//
+// One thread owns one plane; every level of the decomposition lives in registers (all loop bounds
+// are template constants, so after unrolling every array index is static and every filter tap is a
+// constant-bank operand taken from the __grid_constant__ kernel parameter).  A CTA's planes are one
+// contiguous span of global memory: it is staged through shared memory with a 1-D TMA bulk copy
+// (cp.async.bulk + mbarrier) and read back at an odd word stride (9, 25, 49 floats: conflict free).
+// Coefficients are stored coefficient-major ([ncoef][batch]) so warps read and write them coalesced.
+//
+// Arithmetic follows oracle/dwt_oracle.c exactly (fp32, multiply then add, no FMA, same order).
+#include "wt_common.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// compile-time index helpers
+// ------------------------------------------------------------------------------------------------
+__host__ __device__ constexpr int cpmod(int a, int m) { return ((a % m) + m) % m; }
+__host__ __device__ constexpr int half_up(int n) { return (n + 1) / 2; }
+// index of the periodized (odd length padded by repeating the last sample) signal
+__host__ __device__ constexpr int per_index(int idx, int n) {
+    int np = n + (n & 1);
+    int m = cpmod(idx, np);
+    return m == n ? n - 1 : m;
+}
+
+// single-level 2-D analysis of an H x W plane held in registers (dwt2: axis -2 first, then -1)
+template <int H, int W, int F>
+__device__ __forceinline__ void dwt2_regs(const float (&x)[H * W], const WtBank& bk, float (&aa)[half_up(H) * half_up(W)],
+                                          float (&da)[half_up(H) * half_up(W)], float (&ad)[half_up(H) * half_up(W)],
+                                          float (&dd)[half_up(H) * half_up(W)]) {
+    constexpr int H2 = half_up(H), W2 = half_up(W);
+    float lo[H2 * W], hi[H2 * W];
+#pragma unroll
+    for (int c = 0; c < W; ++c) {
+#pragma unroll
+        for (int o = 0; o < H2; ++o) {
+            float sl = 0.0f, sh = 0.0f;
+#pragma unroll
+            for (int j = 0; j < F; ++j) {
+                const float v = x[per_index(F / 2 + 2 * o - j, H) * W + c];
+                sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
+                sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+            }
+            lo[o * W + c] = sl;
+            hi[o * W + c] = sh;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < H2; ++r) {
+#pragma unroll
+        for (int o = 0; o < W2; ++o) {
+            float saa = 0.0f, sad = 0.0f, sda = 0.0f, sdd = 0.0f;
+#pragma unroll
+            for (int j = 0; j < F; ++j) {
+                const int m = per_index(F / 2 + 2 * o - j, W);
+                const float vl = lo[r * W + m], vh = hi[r * W + m];
+                saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
+                sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
+                sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
+                sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
+            }
+            aa[r * W2 + o] = saa;
+            ad[r * W2 + o] = sad;
+            da[r * W2 + o] = sda;
+            dd[r * W2 + o] = sdd;
+        }
+    }
+}
+
+// one output sample of the periodization synthesis of (a, d), coefficient length N, taken from
+// register arrays with element stride S starting at offset OFF (direct accumulation)
+template <int N, int F, int O, int S, int OFF, int LEN>
+__device__ __forceinline__ float idwt_per_sample(const float (&a)[LEN], const float (&d)[LEN], const WtBank& bk) {
+    constexpr int start = F / 4;
+    constexpr int shift = ((F / 2) % 2 == 0) ? 1 : 0;
+    constexpr int q = cpmod(O - shift, 2 * N);
+    constexpr int i = start + q / 2;
+    constexpr int par = q & 1;
+    float acc = 0.0f;
+#pragma unroll
+    for (int j = 0; j < F / 2; ++j) acc = __fadd_rn(acc, __fmul_rn(bk.rec_lo[2 * j + par], a[OFF + cpmod(i - j, N) * S]));
+#pragma unroll
+    for (int j = 0; j < F / 2; ++j) acc = __fadd_rn(acc, __fmul_rn(bk.rec_hi[2 * j + par], d[OFF + cpmod(i - j, N) * S]));
+    return acc;
+}
+
+template <int H, int W, int F, int R, int C>
+struct RowSynth {  // axis -1 pass: lo[r][c], hi[r][c] for r < H2, c < W (row-major, W columns kept)
+    static constexpr int H2 = half_up(H), W2 = half_up(W);
+    __device__ __forceinline__ static void run(const float (&aa)[H2 * W2], const float (&da)[H2 * W2],
+                                               const float (&ad)[H2 * W2], const float (&dd)[H2 * W2], const WtBank& bk,
+                                               float (&lo)[H2 * W], float (&hi)[H2 * W]) {
+        lo[R * W + C] = idwt_per_sample<W2, F, C, 1, R * W2, H2 * W2>(aa, ad, bk);
+        hi[R * W + C] = idwt_per_sample<W2, F, C, 1, R * W2, H2 * W2>(da, dd, bk);
+        if constexpr (C + 1 < W) RowSynth<H, W, F, R, C + 1>::run(aa, da, ad, dd, bk, lo, hi);
+        else if constexpr (R + 1 < H2) RowSynth<H, W, F, R + 1, 0>::run(aa, da, ad, dd, bk, lo, hi);
+    }
+};
+
+template <int H, int W, int F, int R, int C>
+struct ColSynth {  // axis -2 pass: x[r][c] for r < H, c < W
+    static constexpr int H2 = half_up(H);
+    __device__ __forceinline__ static void run(const float (&lo)[H2 * W], const float (&hi)[H2 * W], const WtBank& bk,
+                                               float (&x)[H * W]) {
+        x[R * W + C] = idwt_per_sample<H2, F, R, W, C, H2 * W>(lo, hi, bk);
+        if constexpr (C + 1 < W) ColSynth<H, W, F, R, C + 1>::run(lo, hi, bk, x);
+        else if constexpr (R + 1 < H) ColSynth<H, W, F, R + 1, 0>::run(lo, hi, bk, x);
+    }
+};
+
+// single-level 2-D synthesis cropped to H x W (idwt2: axis -1 first, then axis -2)
+template <int H, int W, int F>
+__device__ __forceinline__ void idwt2_regs(const float (&aa)[half_up(H) * half_up(W)], const float (&da)[half_up(H) * half_up(W)],
+                                           const float (&ad)[half_up(H) * half_up(W)], const float (&dd)[half_up(H) * half_up(W)],
+                                           const WtBank& bk, float (&x)[H * W]) {
+    constexpr int H2 = half_up(H);
+    float lo[H2 * W], hi[H2 * W];
+    RowSynth<H, W, F, 0, 0>::run(aa, da, ad, dd, bk, lo, hi);
+    ColSynth<H, W, F, 0, 0>::run(lo, hi, bk, x);
+}
+
+// ------------------------------------------------------------------------------------------------
+// multi-level recursion.  Coefficient numbering: level-1 details (da, ad, dd) first, then level 2,
+// ..., finally cA_L; all offsets are compile-time at the depth where the recursion stops.
+// ------------------------------------------------------------------------------------------------
+template <int H, int W, int F, int DEPTH, int BASE>
+struct SmallPlane {
+    static constexpr int H2 = half_up(H), W2 = half_up(W), NB = H2 * W2;
+
+    template <class Put>
+    __device__ __forceinline__ static void analyze(const float (&x)[H * W], int level, const WtBank& bk, Put& put) {
+        if (level == 0) {
+#pragma unroll
+            for (int i = 0; i < H * W; ++i) put(BASE + i, x[i]);
+            return;
+        }
+        if constexpr (DEPTH > 0) {
+            float aa[NB], da[NB], ad[NB], dd[NB];
+            dwt2_regs<H, W, F>(x, bk, aa, da, ad, dd);
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+                put(BASE + i, da[i]);
+                put(BASE + NB + i, ad[i]);
+                put(BASE + 2 * NB + i, dd[i]);
+            }
+            SmallPlane<H2, W2, F, DEPTH - 1, BASE + 3 * NB>::analyze(aa, level - 1, bk, put);
+        }
+    }
+
+    template <class Get>
+    __device__ __forceinline__ static void synthesize(float (&x)[H * W], int level, const WtBank& bk, Get& get) {
+        if (level == 0) {
+#pragma unroll
+            for (int i = 0; i < H * W; ++i) x[i] = get(BASE + i);
+            return;
+        }
+        if constexpr (DEPTH > 0) {
+            float aa[NB], da[NB], ad[NB], dd[NB];
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+                da[i] = get(BASE + i);
+                ad[i] = get(BASE + NB + i);
+                dd[i] = get(BASE + 2 * NB + i);
+            }
+            // the deeper reconstruction is already cropped to H2 x W2: that is waverec2's
+            // "drop the extra approximation sample" rule
+            SmallPlane<H2, W2, F, DEPTH - 1, BASE + 3 * NB>::synthesize(aa, level - 1, bk, get);
+            idwt2_regs<H, W, F>(aa, da, ad, dd, bk, x);
+        }
+    }
+};
+
+__device__ __forceinline__ int find_small_job(const WtSmallJob* __restrict__ jobs, int n_jobs, int tile) {
+    int lo = 0, hi = n_jobs - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (__ldg(&jobs[mid].tile_begin) <= tile) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// ---- TMA 1-D bulk copies (cp.async.bulk, SASS UBLKCP) -------------------------------------------
+__device__ __forceinline__ unsigned int smem_u32(const void* p) { return (unsigned int)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, unsigned int bytes, unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned int parity) {
+    unsigned int ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_store(void* gdst, const void* smem_src, unsigned int bytes) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+// stage `cnt` planes (contiguous) into shared memory
+template <int HW>
+__device__ __forceinline__ void stage_in(float* s, const float* __restrict__ g, int cnt, unsigned long long* bar) {
+    const unsigned int bytes = (unsigned int)cnt * HW * 4u;
+    const bool tma_ok = ((reinterpret_cast<uintptr_t>(g) & 15u) == 0) && ((bytes & 15u) == 0);
+    if (tma_ok) {
+        if (threadIdx.x == 0) {
+            mbar_init(bar, 1);
+            bulk_load(s, g, bytes, bar);
+        }
+        __syncthreads();
+        mbar_wait(bar, 0);
+    } else {
+        for (int i = threadIdx.x; i < cnt * HW; i += WT_SMALL_THREADS) s[i] = __ldg(&g[i]);
+        __syncthreads();
+    }
+}
+
+template <int HW>
+__device__ __forceinline__ void stage_out(float* g, const float* s, int cnt) {
+    const unsigned int bytes = (unsigned int)cnt * HW * 4u;
+    const bool tma_ok = ((reinterpret_cast<uintptr_t>(g) & 15u) == 0) && ((bytes & 15u) == 0);
+    __syncthreads();
+    if (tma_ok) {
+        if (threadIdx.x == 0) bulk_store(g, s, bytes);
+    } else {
+        for (int i = threadIdx.x; i < cnt * HW; i += WT_SMALL_THREADS) g[i] = s[i];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernels
+// ------------------------------------------------------------------------------------------------
+template <int H, int W, int F>
+__global__ void __launch_bounds__(WT_SMALL_THREADS)
+wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __restrict__ jobs, int n_jobs,
+                         long long* __restrict__ counts) {
+    constexpr int HW = H * W;
+    __shared__ __align__(16) float s_in[WT_SMALL_THREADS * HW];
+    __shared__ unsigned long long bar;
+    __shared__ unsigned int s_cnt[WT_SMALL_THREADS / 32];
+    const int tile = blockIdx.x;
+    const int j = find_small_job(jobs, n_jobs, tile);
+    const WtSmallJob job = jobs[j];
+    const long long p0 = (long long)(tile - job.tile_begin) * WT_SMALL_THREADS;
+    const long long left = job.batch - p0;
+    const int cnt = left < WT_SMALL_THREADS ? (int)left : WT_SMALL_THREADS;
+    stage_in<HW>(s_in, job.in + p0 * HW, cnt, &bar);
+    unsigned int nz = 0;
+    if ((int)threadIdx.x < cnt) {
+        float x[HW];
+#pragma unroll
+        for (int i = 0; i < HW; ++i) {
+            x[i] = s_in[threadIdx.x * HW + i];
+            nz += (x[i] != 0.0f);
+        }
+        float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
+        const long long stride = job.batch;
+        auto put = [&](int idx, float v) { cbase[(long long)idx * stride] = v; };
+        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0>::analyze(x, job.level, bk, put);
+    }
+    // nonzeros of the input (dwt_pruning_NoEntropy.py:58) and numel
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) nz += __shfl_down_sync(0xffffffffu, nz, d);
+    if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = nz;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int w = 0; w < WT_SMALL_THREADS / 32; ++w) t += s_cnt[w];
+        atomicAdd(reinterpret_cast<unsigned long long*>(counts + (size_t)job.layer * 4 + 3), t);
+        if (tile == job.tile_begin) counts[(size_t)job.layer * 4] = job.batch * HW;
+    }
+}
+
+template <int H, int W, int F>
+__global__ void __launch_bounds__(WT_SMALL_THREADS)
+wt_small_synthesis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __restrict__ jobs, int n_jobs,
+                          const float* __restrict__ thresholds, long long* __restrict__ counts) {
+    constexpr int HW = H * W;
+    __shared__ __align__(16) float s_out[WT_SMALL_THREADS * HW];
+    __shared__ unsigned int s_cnt[WT_SMALL_THREADS / 32];
+    const int tile = blockIdx.x;
+    const int j = find_small_job(jobs, n_jobs, tile);
+    const WtSmallJob job = jobs[j];
+    const long long p0 = (long long)(tile - job.tile_begin) * WT_SMALL_THREADS;
+    const long long left = job.batch - p0;
+    const int cnt = left < WT_SMALL_THREADS ? (int)left : WT_SMALL_THREADS;
+    const float t = job.use_abs ? job.abs_threshold : __ldg(&thresholds[job.layer]);
+    unsigned int zc = 0;
+    if ((int)threadIdx.x < cnt) {
+        float x[HW];
+        const float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
+        const long long stride = job.batch;
+        auto get = [&](int idx) {
+            const float c = __ldg(&cbase[(long long)idx * stride]);
+            return (fabsf(c) < t) ? 0.0f : c;  // np.where(|c| < t, 0, c), strict (dwt_pruning.py:31)
+        };
+        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0>::synthesize(x, job.level, bk, get);
+#pragma unroll
+        for (int i = 0; i < HW; ++i) {
+            s_out[threadIdx.x * HW + i] = x[i];
+            zc += (x[i] == 0.0f);
+        }
+    }
+    stage_out<HW>(job.out + p0 * HW, s_out, cnt);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) zc += __shfl_down_sync(0xffffffffu, zc, d);
+    if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = zc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long z = 0;
+        for (int w = 0; w < WT_SMALL_THREADS / 32; ++w) z += s_cnt[w];
+        atomicAdd(reinterpret_cast<unsigned long long*>(counts + (size_t)job.layer * 4 + 2), z);
+        atomicAdd(reinterpret_cast<unsigned long long*>(counts + (size_t)job.layer * 4 + 1),
+                  (unsigned long long)cnt * HW - z);
+    }
+}
+
+template <int H, int W>
+int launch_analysis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, int n_tiles, long long* counts,
+                       cudaStream_t stream) {
+#define WT_CASE(FL)                                                                                                  \
+    case FL:                                                                                                         \
+        wt_small_analysis_kernel<H, W, FL><<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts);    \
+        break;
+    switch (bank.F) {
+        WT_CASE(2) WT_CASE(4) WT_CASE(6) WT_CASE(8) WT_CASE(10) WT_CASE(12) WT_CASE(18)
+        default:
+            wt_set_error("small-plane path: unsupported filter length %d", bank.F);
+            return WT_E_UNSUPPORTED;
+    }
+#undef WT_CASE
+    WT_CUDA(cudaGetLastError());
+    return WT_OK;
+}
+
+template <int H, int W>
+int launch_synthesis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, int n_tiles, const float* thresholds,
+                        long long* counts, cudaStream_t stream) {
+#define WT_CASE(FL)                                                                                                  \
+    case FL:                                                                                                         \
+        wt_small_synthesis_kernel<H, W, FL>                                                                          \
+            <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, thresholds, counts);                      \
+        break;
+    switch (bank.F) {
+        WT_CASE(2) WT_CASE(4) WT_CASE(6) WT_CASE(8) WT_CASE(10) WT_CASE(12) WT_CASE(18)
+        default:
+            wt_set_error("small-plane path: unsupported filter length %d", bank.F);
+            return WT_E_UNSUPPORTED;
+    }
+#undef WT_CASE
+    WT_CUDA(cudaGetLastError());
+    return WT_OK;
+}
+
+}  // namespace
+
+bool wt_small_supported(int H, int W, int F, int level, int mode) {
+    if (mode != WT_MODE_PERIODIZATION || level < 0 || level > WT_SMALL_MAX_LEVEL) return false;
+    if (H != W || !(H == 1 || H == 3 || H == 5 || H == 7)) return false;
+    return F == 2 || F == 4 || F == 6 || F == 8 || F == 10 || F == 12 || F == 18;
+}
+
+int wt_small_ncoef(int H, int W, int level) {
+    int n = 0, h = H, w = W;
+    for (int l = 0; l < level; ++l) {
+        h = (h + 1) / 2;
+        w = (w + 1) / 2;
+        n += 3 * h * w;
+    }
+    return n + h * w;
+}
+
+int wt_small_analysis_launch(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                             long long* counts, cudaStream_t stream) {
+    if (n_tiles <= 0) return WT_OK;
+    if (H == 1 && W == 1) return launch_analysis_hw<1, 1>(bank, jobs_dev, n_jobs, n_tiles, counts, stream);
+    if (H == 3 && W == 3) return launch_analysis_hw<3, 3>(bank, jobs_dev, n_jobs, n_tiles, counts, stream);
+    if (H == 5 && W == 5) return launch_analysis_hw<5, 5>(bank, jobs_dev, n_jobs, n_tiles, counts, stream);
+    if (H == 7 && W == 7) return launch_analysis_hw<7, 7>(bank, jobs_dev, n_jobs, n_tiles, counts, stream);
+    wt_set_error("small-plane path: unsupported plane %dx%d", H, W);
+    return WT_E_UNSUPPORTED;
+}
+
+int wt_small_synthesis_launch(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                              const float* thresholds, long long* counts, cudaStream_t stream) {
+    if (n_tiles <= 0) return WT_OK;
+    if (H == 1 && W == 1) return launch_synthesis_hw<1, 1>(bank, jobs_dev, n_jobs, n_tiles, thresholds, counts, stream);
+    if (H == 3 && W == 3) return launch_synthesis_hw<3, 3>(bank, jobs_dev, n_jobs, n_tiles, thresholds, counts, stream);
+    if (H == 5 && W == 5) return launch_synthesis_hw<5, 5>(bank, jobs_dev, n_jobs, n_tiles, thresholds, counts, stream);
+    if (H == 7 && W == 7) return launch_synthesis_hw<7, 7>(bank, jobs_dev, n_jobs, n_tiles, thresholds, counts, stream);
+    wt_set_error("small-plane path: unsupported plane %dx%d", H, W);
+    return WT_E_UNSUPPORTED;
+}
