@@ -1,0 +1,541 @@
+// wt_api.cu -- C ABI of libwtprune: metadata, planning and the plan runner.
+//
+// A plan is the host-side mirror of one call of the reference's
+//   multi_resolution_analysis(weights, wavelet, level, percentile|threshold, mode)
+// (/root/reference/ResNet/dwt_pruning.py:35-95, dwt_pruning_NoEntropy.py:12-62) over a whole group
+// of tensors: it classifies every tensor (level-0 select-and-zero, small-plane register path,
+// generic tiled path), lays out one device block (job tables, histograms, coefficient workspace,
+// optional host-I/O staging) and replays a fixed launch sequence with no host synchronisation.
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+
+#include "wt_common.cuh"
+#include "wt_generic.cuh"
+#include "wt_wavelet_tables.h"
+
+// ---- errors ---------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+void wt_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* wt_last_error(void) { return g_err; }
+extern "C" int wt_version(void) { return 1; }
+
+int wt_device_info(WtDeviceInfo* info) {
+    static thread_local int cached_dev = -1;
+    static thread_local WtDeviceInfo cached;
+    int dev = 0;
+    WT_CUDA(cudaGetDevice(&dev));
+    if (dev != cached_dev) {
+        cached.device = dev;
+        WT_CUDA(cudaDeviceGetAttribute(&cached.sm_count, cudaDevAttrMultiProcessorCount, dev));
+        WT_CUDA(cudaDeviceGetAttribute(&cached.coop, cudaDevAttrCooperativeLaunch, dev));
+        cached_dev = dev;
+    }
+    *info = cached;
+    return WT_OK;
+}
+
+// ---- wavelets -----------------------------------------------------------------------------------------
+extern "C" int wt_wavelet_lookup(const char* name, int* id, int* dec_len) {
+    WT_CHECK(name != nullptr, WT_E_INVALID, "wavelet name is NULL");
+    for (int i = 0; i < WT_NUM_WAVELETS; ++i) {
+        if (strcmp(name, WT_BANKS[i].name) == 0) {
+            if (id) *id = i;
+            if (dec_len) *dec_len = WT_BANKS[i].len;
+            return WT_OK;
+        }
+    }
+    wt_set_error("Unknown wavelet name '%s', check wavelist() for the list of available builtin wavelets.", name);
+    return WT_E_INVALID;
+}
+
+extern "C" int wt_wavelet_filters(int wid, double* dec_lo, double* dec_hi, double* rec_lo, double* rec_hi) {
+    WT_CHECK(wid >= 0 && wid < WT_NUM_WAVELETS, WT_E_INVALID, "bad wavelet id %d", wid);
+    const wt_bank_t& b = WT_BANKS[wid];
+    for (int i = 0; i < b.len; ++i) {
+        if (dec_lo) dec_lo[i] = b.dec_lo[i];
+        if (dec_hi) dec_hi[i] = b.dec_hi[i];
+        if (rec_lo) rec_lo[i] = b.rec_lo[i];
+        if (rec_hi) rec_hi[i] = b.rec_hi[i];
+    }
+    return WT_OK;
+}
+
+int wt_get_bank(int wid, WtBank* bank) {
+    WT_CHECK(wid >= 0 && wid < WT_NUM_WAVELETS, WT_E_INVALID, "bad wavelet id %d", wid);
+    const wt_bank_t& b = WT_BANKS[wid];
+    memset(bank, 0, sizeof(*bank));
+    bank->F = b.len;
+    for (int i = 0; i < b.len; ++i) {
+        bank->dec_lo[i] = (float)b.dec_lo[i];
+        bank->dec_hi[i] = (float)b.dec_hi[i];
+        bank->rec_lo[i] = (float)b.rec_lo[i];
+        bank->rec_hi[i] = (float)b.rec_hi[i];
+    }
+    return WT_OK;
+}
+
+extern "C" int wt_dwt_max_level(int n, int F) {
+    if (F <= 1 || n < F - 1) return 0;
+    int q = n / (F - 1), l = 0;
+    while (q > 1) {
+        q >>= 1;
+        ++l;
+    }
+    return l;
+}
+
+extern "C" int wt_dwt_coeff_len(int n, int F, int mode) {
+    return mode == WT_MODE_PERIODIZATION ? (n + 1) / 2 : (n + F - 1) / 2;
+}
+
+int wt_idwt_len(int n, int F, int mode) { return mode == WT_MODE_PERIODIZATION ? 2 * n : 2 * n - F + 2; }
+
+void wt_level_sizes(int n, int F, int mode, int level, int* sizes) {
+    sizes[0] = n;
+    for (int l = 1; l <= level; ++l) sizes[l] = wt_dwt_coeff_len(sizes[l - 1], F, mode);
+}
+
+extern "C" int wt_packed_shape(int H, int W, int wid, int level, int mode, int* side_h, int* side_w,
+                               int64_t* coeffs_per_plane) {
+    WT_CHECK(wid >= 0 && wid < WT_NUM_WAVELETS, WT_E_INVALID, "bad wavelet id %d", wid);
+    WT_CHECK(mode == WT_MODE_PERIODIZATION || mode == WT_MODE_SYMMETRIC, WT_E_INVALID, "Unknown mode name.");
+    WT_CHECK(level >= 0, WT_E_INVALID, "Level value of %d is too low . Minimum level is 0.", level);
+    WT_CHECK(level <= WT_MAX_LEVEL, WT_E_UNSUPPORTED, "level %d above the supported maximum %d", level, WT_MAX_LEVEL);
+    WT_CHECK(H >= 1 && W >= 1, WT_E_INVALID, "empty plane");
+    const int F = WT_BANKS[wid].len;
+    int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
+    wt_level_sizes(H, F, mode, level, hs);
+    wt_level_sizes(W, F, mode, level, ws);
+    int sh = hs[level], sw = ws[level];
+    int64_t nc = (int64_t)hs[level] * ws[level];
+    for (int l = level; l >= 1; --l) {
+        sh += hs[l];
+        sw += ws[l];
+        nc += 3 * (int64_t)hs[l] * ws[l];
+    }
+    if (side_h) *side_h = sh;
+    if (side_w) *side_w = sw;
+    if (coeffs_per_plane) *coeffs_per_plane = nc;
+    return WT_OK;
+}
+
+extern "C" int wt_percentile_plan(int64_t n, double p, int sem, int64_t* k0, int64_t* k1, double* gamma) {
+    WT_CHECK(n >= 1, WT_E_INVALID, "percentile of an empty population");
+    WT_CHECK(p >= 0.0 && p <= 100.0, WT_E_INVALID, "Percentiles must be in the range [0, 100]");
+    if (sem == WT_NUMPY_LEGACY_1_22) {
+        // numpy 1.22: q = p / 100 (float64), virtual index (n-1)*q in float64
+        double q = p / 100.0;
+        double vi = (double)(n - 1) * q;
+        double f = floor(vi);
+        *gamma = vi - f;
+        if (vi >= (double)(n - 1)) {
+            *k0 = *k1 = n - 1;
+        } else {
+            *k0 = (int64_t)f;
+            *k1 = *k0 + 1;
+        }
+    } else if (sem == WT_NUMPY_NEP50_2X) {
+        // numpy 2.x on a float32 array: q = float32(p) / float32(100), index arithmetic in float32
+        volatile float q = (float)p / 100.0f;
+        volatile float nm1 = (float)(n - 1);
+        volatile float vi = nm1 * q;
+        float f = floorf(vi);
+        volatile float g = vi - f;
+        *gamma = (double)g;
+        if (vi >= nm1) {
+            *k0 = *k1 = n - 1;
+        } else {
+            *k0 = (int64_t)f;
+            *k1 = *k0 + 1;
+            if (*k1 > n - 1) *k1 = n - 1;
+        }
+    } else {
+        wt_set_error("unknown numpy_semantics %d", sem);
+        return WT_E_INVALID;
+    }
+    return WT_OK;
+}
+
+// ---- plans ------------------------------------------------------------------------------------------------
+enum { PATH_EMPTY = 0, PATH_LEVEL0 = 1, PATH_SMALL = 2, PATH_GENERIC = 3 };
+
+struct SmallClass {
+    int H, W;
+    std::vector<WtSmallJob> jobs;
+    WtSmallJob* jobs_dev = nullptr;
+    int n_tiles = 0;
+};
+
+struct WtPlan {
+    std::vector<WtLayerDesc> layers;
+    std::vector<int> path;
+    int wavelet_id = 0, mode = 0, thr_kind = 0, sem = 0, host_io = 0;
+    double thr_value = 0;
+    WtBank bank;
+    int device = 0;
+
+    char* dev = nullptr;  // one allocation
+    size_t dev_bytes = 0;
+
+    // select
+    std::vector<WtSelJob> sel_jobs;
+    WtSelJob* sel_jobs_dev = nullptr;
+    WtSelArgs sel_args;
+    // zeroed every run: [select scratch | counts]
+    char* zero_block = nullptr;
+    size_t zero_bytes = 0;
+    float* thresholds_dev = nullptr;
+    long long* counts_dev = nullptr;
+
+    std::vector<SmallClass> small;
+    std::vector<WtGenericLayer> generic;
+    std::vector<int> level0_abs;  // layers pruned by the plain threshold kernel (absolute, level 0)
+
+    // per-layer device pointers actually used by the kernels (staging for host I/O)
+    std::vector<float*> d_in, d_out, d_coef;
+    std::vector<long long> ncoef, zeros;  // per layer: explicit coefficients / implicit padding zeros
+    float *tmp0 = nullptr, *tmp1 = nullptr;
+    int n_launches = 0;
+};
+
+static size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+static long long layer_numel(const WtLayerDesc& L) { return L.batch * (long long)L.H * L.W; }
+
+// fills the host-side job tables from plan->layers and the current device pointers
+static int build_tables(WtPlan* P) {
+    const int n = (int)P->layers.size();
+    P->sel_jobs.clear();
+    for (auto& c : P->small) { c.jobs.clear(); c.n_tiles = 0; }
+    P->generic.clear();
+    P->level0_abs.clear();
+    int sel_tiles = 0;
+    bool any_apply = false;
+    for (int i = 0; i < n; ++i) {
+        const WtLayerDesc& L = P->layers[i];
+        const long long numel = layer_numel(L);
+        if (P->path[i] == PATH_EMPTY) continue;
+        const bool pct = (P->thr_kind == WT_THRESHOLD_PERCENTILE);
+        if (P->path[i] == PATH_SMALL) {
+            SmallClass* cls = nullptr;
+            for (auto& c : P->small) if (c.H == L.H && c.W == L.W) cls = &c;
+            WtSmallJob j;
+            memset(&j, 0, sizeof(j));
+            j.in = P->d_in[i]; j.out = P->d_out[i]; j.coef = P->d_coef[i];
+            j.batch = L.batch; j.level = L.level; j.layer = i;
+            j.tile_begin = cls->n_tiles;
+            j.n_tiles = (int)((L.batch + WT_SMALL_THREADS - 1) / WT_SMALL_THREADS);
+            j.abs_threshold = (float)P->thr_value;
+            j.use_abs = pct ? 0 : 1;
+            cls->n_tiles += j.n_tiles;
+            cls->jobs.push_back(j);
+        } else if (P->path[i] == PATH_GENERIC) {
+            WtGenericLayer g;
+            memset(&g, 0, sizeof(g));
+            g.in = P->d_in[i]; g.out = P->d_out[i]; g.batch = L.batch; g.H = L.H; g.W = L.W; g.level = L.level;
+            g.layer = i; g.coef = P->d_coef[i]; g.tmp0 = P->tmp0; g.tmp1 = P->tmp1;
+            g.abs_threshold = (float)P->thr_value; g.use_abs = pct ? 0 : 1;
+            P->generic.push_back(g);
+        } else if (!pct) {
+            P->level0_abs.push_back(i);
+        }
+        if (pct) {
+            WtSelJob j;
+            memset(&j, 0, sizeof(j));
+            const bool l0 = (P->path[i] == PATH_LEVEL0);
+            j.x = l0 ? P->d_in[i] : P->d_coef[i];
+            j.out = l0 ? P->d_out[i] : nullptr;
+            j.n = l0 ? numel : P->ncoef[i];
+            j.zeros = l0 ? 0 : P->zeros[i];
+            int64_t k0, k1; double gamma;
+            int rc = wt_percentile_plan(j.n + j.zeros, P->thr_value, P->sem, &k0, &k1, &gamma);
+            if (rc) return rc;
+            j.k0 = k0; j.k1 = k1; j.gamma = gamma;
+            j.lerp_mode = (P->sem == WT_NUMPY_LEGACY_1_22) ? WT_LERP_LEGACY : WT_LERP_NEP50;
+            j.tile_begin = sel_tiles;
+            const long long nt = (j.n + WT_SEL_TILE - 1) / WT_SEL_TILE;
+            WT_CHECK(sel_tiles + nt < 2147483647LL, WT_E_UNSUPPORTED, "too many select tiles");
+            j.n_tiles = (int)nt;
+            j.layer = i;
+            sel_tiles += (int)nt;
+            any_apply |= l0;
+            P->sel_jobs.push_back(j);
+        }
+    }
+    P->sel_args.n_tiles = sel_tiles;
+    P->sel_args.any_apply = any_apply ? 1 : 0;
+    return WT_OK;
+}
+
+static int upload_tables(WtPlan* P) {
+    if (!P->sel_jobs.empty())
+        WT_CUDA(cudaMemcpy(P->sel_jobs_dev, P->sel_jobs.data(), P->sel_jobs.size() * sizeof(WtSelJob), cudaMemcpyHostToDevice));
+    for (auto& c : P->small)
+        if (!c.jobs.empty())
+            WT_CUDA(cudaMemcpy(c.jobs_dev, c.jobs.data(), c.jobs.size() * sizeof(WtSmallJob), cudaMemcpyHostToDevice));
+    return WT_OK;
+}
+
+extern "C" int wt_plan_destroy(WtPlan* P) {
+    if (!P) return WT_OK;
+    if (P->dev) cudaFree(P->dev);
+    delete P;
+    return WT_OK;
+}
+
+extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavelet_id, int mode, int threshold_kind,
+                              double threshold_value, int numpy_semantics, int host_io, WtPlan** plan_out) {
+    WT_CHECK(plan_out != nullptr, WT_E_INVALID, "plan_out is NULL");
+    *plan_out = nullptr;
+    WT_CHECK(layers != nullptr || n_layers == 0, WT_E_INVALID, "layers is NULL");
+    WT_CHECK(n_layers >= 0, WT_E_INVALID, "n_layers < 0");
+    WT_CHECK(mode == WT_MODE_PERIODIZATION || mode == WT_MODE_SYMMETRIC, WT_E_INVALID, "Unknown mode name.");
+    WT_CHECK(threshold_kind == WT_THRESHOLD_PERCENTILE || threshold_kind == WT_THRESHOLD_ABSOLUTE, WT_E_INVALID,
+             "unknown threshold kind %d", threshold_kind);
+    WT_CHECK(numpy_semantics == WT_NUMPY_LEGACY_1_22 || numpy_semantics == WT_NUMPY_NEP50_2X, WT_E_INVALID,
+             "unknown numpy_semantics %d", numpy_semantics);
+    if (threshold_kind == WT_THRESHOLD_PERCENTILE)
+        WT_CHECK(threshold_value >= 0.0 && threshold_value <= 100.0, WT_E_INVALID,
+                 "Percentiles must be in the range [0, 100]");
+    WtPlan* P = new WtPlan();
+    int rc = wt_get_bank(wavelet_id, &P->bank);
+    if (rc) { delete P; return rc; }
+    if (cudaGetDevice(&P->device) != cudaSuccess) {
+        delete P;
+        wt_set_error("no usable CUDA device (libwtprune has no CPU fallback): %s", cudaGetErrorString(cudaGetLastError()));
+        return WT_E_CUDA;
+    }
+    P->wavelet_id = wavelet_id; P->mode = mode; P->thr_kind = threshold_kind; P->thr_value = threshold_value;
+    P->sem = numpy_semantics; P->host_io = host_io;
+    P->layers.assign(layers, layers + n_layers);
+    P->path.assign(n_layers, PATH_EMPTY);
+    P->d_in.assign(n_layers, nullptr); P->d_out.assign(n_layers, nullptr); P->d_coef.assign(n_layers, nullptr);
+    P->ncoef.assign(n_layers, 0); P->zeros.assign(n_layers, 0);
+    const int F = P->bank.F;
+
+    // ---- classify + size ----
+    size_t bytes = 0;
+    std::vector<size_t> off_coef(n_layers, 0), off_io(n_layers, 0);
+    long long tmp_elems = 0;
+    int n_sel = 0;
+    for (int i = 0; i < n_layers; ++i) {
+        const WtLayerDesc& L = P->layers[i];
+        if (L.batch < 0 || L.H < 0 || L.W < 0) { delete P; wt_set_error("layer %d: negative shape", i); return WT_E_INVALID; }
+        if (L.level < 0) { delete P; wt_set_error("Level value of %d is too low . Minimum level is 0.", L.level); return WT_E_INVALID; }
+        if (L.level > WT_MAX_LEVEL) { delete P; wt_set_error("layer %d: level %d above the supported maximum %d", i, L.level, WT_MAX_LEVEL); return WT_E_UNSUPPORTED; }
+        const long long numel = layer_numel(L);
+        if (numel == 0) continue;
+        if ((L.in == nullptr || L.out == nullptr)) { delete P; wt_set_error("layer %d: NULL tensor pointer", i); return WT_E_INVALID; }
+        if (L.level == 0) {
+            P->path[i] = PATH_LEVEL0;
+        } else if (wt_small_supported(L.H, L.W, F, L.level, mode)) {
+            P->path[i] = PATH_SMALL;
+            bool found = false;
+            for (auto& c : P->small) found |= (c.H == L.H && c.W == L.W);
+            if (!found) { SmallClass c; c.H = L.H; c.W = L.W; P->small.push_back(c); }
+        } else {
+            P->path[i] = PATH_GENERIC;
+            tmp_elems = std::max(tmp_elems, L.batch * wt_generic_tmp_elems(L.H, L.W, F, mode, L.level));
+        }
+        if (P->path[i] != PATH_LEVEL0) {
+            int sh, sw; int64_t nc;
+            rc = wt_packed_shape(L.H, L.W, wavelet_id, L.level, mode, &sh, &sw, &nc);
+            if (rc) { delete P; return rc; }
+            P->ncoef[i] = L.batch * nc;
+            P->zeros[i] = L.batch * ((long long)sh * sw - nc);
+        }
+        if (threshold_kind == WT_THRESHOLD_PERCENTILE) ++n_sel;
+    }
+    // ---- layout of the single device block ----
+    auto take = [&](size_t sz) { size_t o = bytes; bytes = align_up(bytes + sz); return o; };
+    const size_t off_sel_jobs = take((size_t)std::max(n_sel, 1) * sizeof(WtSelJob));
+    std::vector<size_t> off_small(P->small.size());
+    for (size_t c = 0; c < P->small.size(); ++c) off_small[c] = take((size_t)n_layers * sizeof(WtSmallJob));
+    const size_t off_thr = take((size_t)std::max(n_layers, 1) * sizeof(float));
+    const size_t sel_scratch = wt_select_scratch_bytes(std::max(n_sel, 1));
+    const size_t off_zero = take(sel_scratch + (size_t)std::max(n_layers, 1) * 4 * sizeof(long long));
+    const size_t zero_bytes = bytes - off_zero;
+    for (int i = 0; i < n_layers; ++i)
+        if (P->path[i] == PATH_SMALL || P->path[i] == PATH_GENERIC) off_coef[i] = take((size_t)P->ncoef[i] * sizeof(float));
+    const size_t off_tmp0 = take((size_t)tmp_elems * sizeof(float));
+    const size_t off_tmp1 = take((size_t)tmp_elems * sizeof(float));
+    if (host_io)
+        for (int i = 0; i < n_layers; ++i)
+            if (P->path[i] != PATH_EMPTY) off_io[i] = take((size_t)layer_numel(P->layers[i]) * sizeof(float));
+    P->dev_bytes = bytes;
+    cudaError_t e = cudaMalloc((void**)&P->dev, std::max(bytes, (size_t)256));
+    if (e != cudaSuccess) {
+        wt_set_error("cudaMalloc(%zu) failed: %s (libwtprune has no CPU fallback)", bytes, cudaGetErrorString(e));
+        delete P;
+        return WT_E_CUDA;
+    }
+    P->sel_jobs_dev = reinterpret_cast<WtSelJob*>(P->dev + off_sel_jobs);
+    for (size_t c = 0; c < P->small.size(); ++c) P->small[c].jobs_dev = reinterpret_cast<WtSmallJob*>(P->dev + off_small[c]);
+    P->thresholds_dev = reinterpret_cast<float*>(P->dev + off_thr);
+    P->zero_block = P->dev + off_zero;
+    P->zero_bytes = zero_bytes;
+    wt_select_bind(&P->sel_args, P->zero_block, std::max(n_sel, 1));
+    P->counts_dev = reinterpret_cast<long long*>(P->zero_block + align_up(sel_scratch, 16));
+    P->sel_args.jobs = P->sel_jobs_dev;
+    P->sel_args.n_jobs = n_sel;
+    P->sel_args.thresholds = P->thresholds_dev;
+    P->sel_args.counts = P->counts_dev;
+    P->tmp0 = reinterpret_cast<float*>(P->dev + off_tmp0);
+    P->tmp1 = reinterpret_cast<float*>(P->dev + off_tmp1);
+    for (int i = 0; i < n_layers; ++i) {
+        if (P->path[i] == PATH_EMPTY) continue;
+        if (P->path[i] != PATH_LEVEL0) P->d_coef[i] = reinterpret_cast<float*>(P->dev + off_coef[i]);
+        if (host_io) {
+            P->d_in[i] = P->d_out[i] = reinterpret_cast<float*>(P->dev + off_io[i]);
+        } else {
+            P->d_in[i] = const_cast<float*>(P->layers[i].in);
+            P->d_out[i] = P->layers[i].out;
+        }
+    }
+    rc = build_tables(P);
+    if (!rc) rc = upload_tables(P);
+    if (!rc) {
+        e = cudaMemset(P->thresholds_dev, 0, (size_t)std::max(n_layers, 1) * sizeof(float));
+        if (e != cudaSuccess) { wt_set_error("cudaMemset failed: %s", cudaGetErrorString(e)); rc = WT_E_CUDA; }
+    }
+    if (rc) { wt_plan_destroy(P); return rc; }
+    *plan_out = P;
+    return WT_OK;
+}
+
+extern "C" size_t wt_plan_device_bytes(const WtPlan* P) { return P ? P->dev_bytes : 0; }
+extern "C" int wt_plan_num_launches(const WtPlan* P) { return P ? P->n_launches : 0; }
+
+extern "C" int wt_plan_set_io(WtPlan* P, const WtLayerDesc* layers, int n_layers) {
+    WT_CHECK(P != nullptr && layers != nullptr, WT_E_INVALID, "NULL argument");
+    WT_CHECK(n_layers == (int)P->layers.size(), WT_E_INVALID, "wt_plan_set_io: layer count differs from the plan");
+    for (int i = 0; i < n_layers; ++i) {
+        const WtLayerDesc& a = P->layers[i];
+        const WtLayerDesc& b = layers[i];
+        WT_CHECK(a.batch == b.batch && a.H == b.H && a.W == b.W && a.level == b.level, WT_E_INVALID,
+                 "wt_plan_set_io: layer %d shape/level differs from the plan", i);
+        WT_CHECK(P->path[i] == PATH_EMPTY || (b.in && b.out), WT_E_INVALID, "layer %d: NULL tensor pointer", i);
+    }
+    for (int i = 0; i < n_layers; ++i) {
+        P->layers[i].in = layers[i].in;
+        P->layers[i].out = layers[i].out;
+        if (!P->host_io && P->path[i] != PATH_EMPTY) {
+            P->d_in[i] = const_cast<float*>(layers[i].in);
+            P->d_out[i] = layers[i].out;
+        }
+    }
+    if (P->host_io) return WT_OK;
+    int rc = build_tables(P);
+    if (rc) return rc;
+    return upload_tables(P);
+}
+
+extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int n = (int)P->layers.size();
+    int launches = 0;
+    WT_CUDA(cudaMemsetAsync(P->zero_block, 0, P->zero_bytes, stream));
+    if (P->host_io)
+        for (int i = 0; i < n; ++i)
+            if (P->path[i] != PATH_EMPTY)
+                WT_CUDA(cudaMemcpyAsync(P->d_in[i], P->layers[i].in, (size_t)layer_numel(P->layers[i]) * sizeof(float),
+                                        cudaMemcpyHostToDevice, stream));
+    int rc;
+    // 1. analysis
+    for (auto& c : P->small) {
+        rc = wt_small_analysis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev, stream);
+        if (rc) return rc;
+        if (c.n_tiles) ++launches;
+    }
+    for (auto& g : P->generic) {
+        rc = wt_generic_analysis(P->bank, P->mode, g, P->counts_dev, stream, &launches);
+        if (rc) return rc;
+    }
+    // 2. threshold: exact percentile select (+ fused level-0 apply), or plain compare
+    if (P->thr_kind == WT_THRESHOLD_PERCENTILE) {
+        if (!P->sel_jobs.empty()) {
+            rc = wt_select_launch(P->sel_args, stream);
+            if (rc) return rc;
+            ++launches;
+        }
+    } else {
+        for (int i : P->level0_abs) {
+            rc = wt_apply_threshold_launch(P->d_in[i], P->d_out[i], layer_numel(P->layers[i]), nullptr, (float)P->thr_value,
+                                           P->counts_dev + (size_t)i * 4, stream);
+            if (rc) return rc;
+            ++launches;
+        }
+    }
+    // 3. synthesis with the threshold applied on load
+    for (auto& c : P->small) {
+        rc = wt_small_synthesis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->thresholds_dev,
+                                       P->counts_dev, stream);
+        if (rc) return rc;
+        if (c.n_tiles) ++launches;
+    }
+    for (auto& g : P->generic) {
+        rc = wt_generic_synthesis(P->bank, P->mode, g, P->thresholds_dev, P->counts_dev, stream, &launches);
+        if (rc) return rc;
+    }
+    if (P->host_io)
+        for (int i = 0; i < n; ++i)
+            if (P->path[i] != PATH_EMPTY)
+                WT_CUDA(cudaMemcpyAsync(P->layers[i].out, P->d_out[i], (size_t)layer_numel(P->layers[i]) * sizeof(float),
+                                        cudaMemcpyDeviceToHost, stream));
+    P->n_launches = launches;
+    return WT_OK;
+}
+
+extern "C" int wt_plan_counts_device(WtPlan* P, const int64_t** counts_dev) {
+    WT_CHECK(P != nullptr && counts_dev != nullptr, WT_E_INVALID, "NULL argument");
+    *counts_dev = reinterpret_cast<const int64_t*>(P->counts_dev);
+    return WT_OK;
+}
+
+extern "C" int wt_plan_results(WtPlan* P, void* stream_, int64_t* counts, int64_t* nonzero_before, float* thresholds) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int n = (int)P->layers.size();
+    std::vector<long long> c4((size_t)n * 4);
+    std::vector<float> thr(n);
+    if (n) {
+        WT_CUDA(cudaMemcpyAsync(c4.data(), P->counts_dev, c4.size() * sizeof(long long), cudaMemcpyDeviceToHost, stream));
+        WT_CUDA(cudaMemcpyAsync(thr.data(), P->thresholds_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    }
+    WT_CUDA(cudaStreamSynchronize(stream));
+    for (int i = 0; i < n; ++i) {
+        if (counts) {
+            counts[i * 3 + 0] = layer_numel(P->layers[i]);
+            counts[i * 3 + 1] = c4[(size_t)i * 4 + 1];
+            counts[i * 3 + 2] = c4[(size_t)i * 4 + 2];
+        }
+        if (nonzero_before) nonzero_before[i] = c4[(size_t)i * 4 + 3];
+        if (thresholds) thresholds[i] = (P->thr_kind == WT_THRESHOLD_ABSOLUTE) ? (float)P->thr_value : thr[i];
+    }
+    return WT_OK;
+}
+
+extern "C" int wt_dwt_prune_f32(const WtLayerDesc* layers, int n_layers, int wavelet_id, int mode, int threshold_kind,
+                                double threshold_value, int numpy_semantics, void* stream, int64_t* counts,
+                                int64_t* nonzero_before, float* thresholds) {
+    WtPlan* P = nullptr;
+    int rc = wt_plan_create(layers, n_layers, wavelet_id, mode, threshold_kind, threshold_value, numpy_semantics, 0, &P);
+    if (rc) return rc;
+    rc = wt_plan_run(P, stream);
+    if (!rc) rc = wt_plan_results(P, stream, counts, nonzero_before, thresholds);
+    else cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
+    wt_plan_destroy(P);
+    return rc;
+}

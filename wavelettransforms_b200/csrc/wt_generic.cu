@@ -1,0 +1,399 @@
+// wt_generic.cu -- generic tiled single-level 2-D DWT / IDWT kernels: any plane size, modes
+// 'periodization' and 'symmetric', any of the 17 filter banks.  Replaces pywt.dwt2 / pywt.idwt2
+// as iterated by pywt.wavedec2 / waverec2 (/root/reference/ResNet/dwt_pruning.py:67-68,77;
+// dwt_pruning_NoEntropy.py:41,49) for the shapes the register-resident small-plane path does not
+// cover: large planes (the 4096 x 4096 bank), symmetric mode, odd shapes.
+//
+// One CTA produces a tile of all four sub-bands (analysis) or of the reconstructed plane
+// (synthesis) for `pb` planes: the boundary-extended input region is staged in shared memory
+// (the index map handles wrap-around and reflection for any N, including N < F), the first axis
+// pass writes its intermediate to shared memory, the second pass writes the result.  Arithmetic and
+// accumulation order are those of oracle/dwt_oracle.c (fp32, no FMA).
+#include "wt_generic.cuh"
+
+namespace {
+
+constexpr int GEN_THREADS = 256;
+constexpr int SMEM_FLOATS = 11000;  // 44 KB of dynamic shared memory per CTA
+
+__device__ __forceinline__ int pmodi(int a, int m) {
+    int r = a % m;
+    return r < 0 ? r + m : r;
+}
+
+// analysis: index of the boundary-extended signal
+__device__ __forceinline__ int ext_index(int idx, int n, int mode) {
+    if (mode == WT_MODE_PERIODIZATION) {
+        int np = n + (n & 1);
+        int m = pmodi(idx, np);
+        return m == n ? n - 1 : m;
+    }
+    int m = pmodi(idx, 2 * n);
+    return m >= n ? 2 * n - 1 - m : m;
+}
+
+struct AnaParams {
+    WtView in, aa, da, ad, dd;
+    long long batch;
+    int h, w, h2, w2, mode;
+    int t2r, t2c, tiles_r, tiles_c, pb, ir, ic;
+};
+
+__global__ void __launch_bounds__(GEN_THREADS)
+wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ AnaParams P) {
+    extern __shared__ float smem[];
+    const int F = bk.F;
+    const int tile_c = blockIdx.x % P.tiles_c;
+    const int tile_r = (blockIdx.x / P.tiles_c) % P.tiles_r;
+    const long long pg = blockIdx.x / (P.tiles_c * P.tiles_r);
+    const long long p0 = pg * P.pb;
+    const int np = (int)min((long long)P.pb, P.batch - p0);
+    const int o0 = tile_r * P.t2r, c0 = tile_c * P.t2c;
+    const int base = (P.mode == WT_MODE_PERIODIZATION) ? F / 2 : 1;
+    const int r_start = base + 2 * o0 - (F - 1), c_start = base + 2 * c0 - (F - 1);
+    const int ir = P.ir, ic = P.ic, t2r = P.t2r, t2c = P.t2c;
+    float* s_in = smem;                          // [pb][ir][ic]
+    float* s_lo = s_in + (size_t)P.pb * ir * ic;  // [pb][t2r][ic]
+    float* s_hi = s_lo + (size_t)P.pb * t2r * ic;
+
+    for (int idx = threadIdx.x; idx < np * ir * ic; idx += GEN_THREADS) {
+        const int cc = idx % ic, rr = (idx / ic) % ir, p = idx / (ic * ir);
+        const int sr = ext_index(r_start + rr, P.h, P.mode), sc = ext_index(c_start + cc, P.w, P.mode);
+        s_in[idx] = __ldg(P.in.p + (p0 + p) * P.in.pstride + (long long)sr * P.in.rstride + sc);
+    }
+    __syncthreads();
+    // axis -2
+    for (int idx = threadIdx.x; idx < np * t2r * ic; idx += GEN_THREADS) {
+        const int cc = idx % ic, ol = (idx / ic) % t2r, p = idx / (ic * t2r);
+        if (o0 + ol >= P.h2) continue;
+        const float* col = s_in + (size_t)p * ir * ic + cc;
+        float sl = 0.0f, sh = 0.0f;
+        for (int j = 0; j < F; ++j) {
+            const float v = col[(2 * ol + F - 1 - j) * ic];
+            sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
+            sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+        }
+        s_lo[idx] = sl;
+        s_hi[idx] = sh;
+    }
+    __syncthreads();
+    // axis -1
+    for (int idx = threadIdx.x; idx < np * t2r * t2c; idx += GEN_THREADS) {
+        const int cl = idx % t2c, ol = (idx / t2c) % t2r, p = idx / (t2c * t2r);
+        const int o = o0 + ol, c = c0 + cl;
+        if (o >= P.h2 || c >= P.w2) continue;
+        const float* rl = s_lo + ((size_t)p * t2r + ol) * ic;
+        const float* rh = s_hi + ((size_t)p * t2r + ol) * ic;
+        float saa = 0.0f, sad = 0.0f, sda = 0.0f, sdd = 0.0f;
+        for (int j = 0; j < F; ++j) {
+            const int m = 2 * cl + F - 1 - j;
+            const float vl = rl[m], vh = rh[m];
+            saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
+            sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
+            sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
+            sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
+        }
+        const long long pl = p0 + p;
+        P.aa.p[pl * P.aa.pstride + (long long)o * P.aa.rstride + c] = saa;
+        P.ad.p[pl * P.ad.pstride + (long long)o * P.ad.rstride + c] = sad;
+        P.da.p[pl * P.da.pstride + (long long)o * P.da.rstride + c] = sda;
+        P.dd.p[pl * P.dd.pstride + (long long)o * P.dd.rstride + c] = sdd;
+    }
+}
+
+struct SynParams {
+    WtView aa, da, ad, dd, out;
+    long long batch;
+    int h2, w2, oh, ow, mode;
+    int tr, tc, tiles_r, tiles_c, pb, cr, cc;
+    const float* thr_dev;
+    float thr_host;
+    int use_thr, thr_a;
+    long long* counts4;
+};
+
+// virtual coefficient index and tap parity that produce output sample o
+__device__ __forceinline__ void syn_index(int o, int F, int mode, int* iv, int* par) {
+    if (mode == WT_MODE_PERIODIZATION) {
+        const int shift = ((F / 2) % 2 == 0) ? 1 : 0;
+        const int q = o - shift;  // >= -1
+        *iv = F / 4 + (q >> 1);
+        *par = q & 1;
+    } else {
+        *iv = F / 2 - 1 + (o >> 1);
+        *par = o & 1;
+    }
+}
+
+__device__ __forceinline__ int syn_map(int v, int n, int mode) {
+    if (mode == WT_MODE_PERIODIZATION) return pmodi(v, n);
+    return v < 0 ? 0 : (v >= n ? n - 1 : v);
+}
+
+__device__ __forceinline__ float syn_sample(const float* a, const float* d, int stride, int top, int par, const WtBank& bk,
+                                            int mode) {
+    // a[top - j*stride] is the coefficient paired with tap 2j+par
+    const int hf = bk.F / 2;
+    if (mode == WT_MODE_PERIODIZATION) {
+        float acc = 0.0f;
+        for (int j = 0; j < hf; ++j) acc = __fadd_rn(acc, __fmul_rn(bk.rec_lo[2 * j + par], a[top - j * stride]));
+        for (int j = 0; j < hf; ++j) acc = __fadd_rn(acc, __fmul_rn(bk.rec_hi[2 * j + par], d[top - j * stride]));
+        return acc;
+    }
+    float sl = 0.0f, sh = 0.0f;
+    for (int j = 0; j < hf; ++j) sl = __fadd_rn(sl, __fmul_rn(bk.rec_lo[2 * j + par], a[top - j * stride]));
+    for (int j = 0; j < hf; ++j) sh = __fadd_rn(sh, __fmul_rn(bk.rec_hi[2 * j + par], d[top - j * stride]));
+    return __fadd_rn(__fadd_rn(0.0f, sl), sh);
+}
+
+__global__ void __launch_bounds__(GEN_THREADS)
+wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ SynParams P) {
+    extern __shared__ float smem[];
+    const int F = bk.F, hf = F / 2;
+    const int tile_c = blockIdx.x % P.tiles_c;
+    const int tile_r = (blockIdx.x / P.tiles_c) % P.tiles_r;
+    const long long pg = blockIdx.x / (P.tiles_c * P.tiles_r);
+    const long long p0 = pg * P.pb;
+    const int np = (int)min((long long)P.pb, P.batch - p0);
+    const int R0 = tile_r * P.tr, C0 = tile_c * P.tc;
+    const int cr = P.cr, cc = P.cc, tr = P.tr, tc = P.tc;
+    int iv0, par0;
+    syn_index(R0, F, P.mode, &iv0, &par0);
+    const int row_lo = iv0 - (hf - 1);
+    syn_index(C0, F, P.mode, &iv0, &par0);
+    const int col_lo = iv0 - (hf - 1);
+    const size_t band = (size_t)P.pb * cr * cc;
+    float* s_aa = smem;
+    float* s_da = s_aa + band;
+    float* s_ad = s_da + band;
+    float* s_dd = s_ad + band;
+    float* s_lo = s_dd + band;                       // [pb][cr][tc]
+    float* s_hi = s_lo + (size_t)P.pb * cr * tc;
+    const float t = P.use_thr ? (P.thr_dev ? __ldg(P.thr_dev) : P.thr_host) : 0.0f;
+
+    for (int idx = threadIdx.x; idx < np * cr * cc; idx += GEN_THREADS) {
+        const int c2 = idx % cc, r2 = (idx / cc) % cr, p = idx / (cc * cr);
+        const int sr = syn_map(row_lo + r2, P.h2, P.mode), sc = syn_map(col_lo + c2, P.w2, P.mode);
+        const long long pl = p0 + p;
+        float vaa = __ldg(P.aa.p + pl * P.aa.pstride + (long long)sr * P.aa.rstride + sc);
+        float vda = __ldg(P.da.p + pl * P.da.pstride + (long long)sr * P.da.rstride + sc);
+        float vad = __ldg(P.ad.p + pl * P.ad.pstride + (long long)sr * P.ad.rstride + sc);
+        float vdd = __ldg(P.dd.p + pl * P.dd.pstride + (long long)sr * P.dd.rstride + sc);
+        if (P.use_thr) {
+            if (P.thr_a && fabsf(vaa) < t) vaa = 0.0f;
+            if (fabsf(vda) < t) vda = 0.0f;
+            if (fabsf(vad) < t) vad = 0.0f;
+            if (fabsf(vdd) < t) vdd = 0.0f;
+        }
+        s_aa[idx] = vaa;
+        s_da[idx] = vda;
+        s_ad[idx] = vad;
+        s_dd[idx] = vdd;
+    }
+    __syncthreads();
+    // axis -1 first (idwt2)
+    for (int idx = threadIdx.x; idx < np * cr * tc; idx += GEN_THREADS) {
+        const int cl = idx % tc, r2 = (idx / tc) % cr, p = idx / (tc * cr);
+        const int c = C0 + cl;
+        if (c >= P.ow) continue;
+        int iv, par;
+        syn_index(c, F, P.mode, &iv, &par);
+        const int top = iv - col_lo;
+        const size_t rowoff = ((size_t)p * cr + r2) * cc;
+        s_lo[idx] = syn_sample(s_aa + rowoff, s_ad + rowoff, 1, top, par, bk, P.mode);
+        s_hi[idx] = syn_sample(s_da + rowoff, s_dd + rowoff, 1, top, par, bk, P.mode);
+    }
+    __syncthreads();
+    unsigned int zc = 0, wr = 0;
+    for (int idx = threadIdx.x; idx < np * tr * tc; idx += GEN_THREADS) {
+        const int cl = idx % tc, rl = (idx / tc) % tr, p = idx / (tc * tr);
+        const int r = R0 + rl, c = C0 + cl;
+        if (r >= P.oh || c >= P.ow) continue;
+        int iv, par;
+        syn_index(r, F, P.mode, &iv, &par);
+        const int top = iv - row_lo;
+        const size_t off = (size_t)p * cr * tc + cl;
+        const float v = syn_sample(s_lo + off, s_hi + off, tc, top * tc, par, bk, P.mode);
+        P.out.p[(p0 + p) * P.out.pstride + (long long)r * P.out.rstride + c] = v;
+        zc += (v == 0.0f);
+        ++wr;
+    }
+    if (P.counts4) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            zc += __shfl_down_sync(0xffffffffu, zc, d);
+            wr += __shfl_down_sync(0xffffffffu, wr, d);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(reinterpret_cast<unsigned long long*>(P.counts4 + 2), (unsigned long long)zc);
+            atomicAdd(reinterpret_cast<unsigned long long*>(P.counts4 + 1), (unsigned long long)(wr - zc));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) wt_count_nonzero_kernel(const float* __restrict__ x, long long n,
+                                                               long long* counts4) {
+    unsigned int nz = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        nz += (x[i] != 0.0f);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) nz += __shfl_down_sync(0xffffffffu, nz, d);
+    if ((threadIdx.x & 31) == 0 && nz) atomicAdd(reinterpret_cast<unsigned long long*>(counts4 + 3), (unsigned long long)nz);
+    if (blockIdx.x == 0 && threadIdx.x == 0) counts4[0] = n;
+}
+
+}  // namespace
+
+// ---- host side -----------------------------------------------------------------------------------------
+long long wt_generic_ncoef(int H, int W, int F, int mode, int level) {
+    int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
+    wt_level_sizes(H, F, mode, level, hs);
+    wt_level_sizes(W, F, mode, level, ws);
+    long long n = (long long)hs[level] * ws[level];
+    for (int l = 1; l <= level; ++l) n += 3LL * hs[l] * ws[l];
+    return n;
+}
+
+long long wt_generic_tmp_elems(int H, int W, int F, int mode, int level) {
+    int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
+    wt_level_sizes(H, F, mode, level, hs);
+    wt_level_sizes(W, F, mode, level, ws);
+    long long m = 1;
+    for (int l = 1; l <= level; ++l) {
+        m = std::max(m, (long long)hs[l] * ws[l]);                                                   // analysis cA_l
+        m = std::max(m, (long long)std::max(hs[l - 1], 1) * std::max(ws[l - 1], 1));                  // synthesis output
+    }
+    return m;
+}
+
+int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
+                              WtView da, WtView ad, WtView dd, cudaStream_t stream) {
+    AnaParams P;
+    P.in = in; P.aa = aa; P.da = da; P.ad = ad; P.dd = dd;
+    P.batch = batch; P.h = h; P.w = w; P.mode = mode;
+    P.h2 = wt_dwt_coeff_len(h, bank.F, mode);
+    P.w2 = wt_dwt_coeff_len(w, bank.F, mode);
+    P.t2r = std::min(P.h2, 16);
+    P.t2c = std::min(P.w2, 32);
+    P.tiles_r = (P.h2 + P.t2r - 1) / P.t2r;
+    P.tiles_c = (P.w2 + P.t2c - 1) / P.t2c;
+    P.ir = 2 * P.t2r + bank.F - 2;
+    P.ic = 2 * P.t2c + bank.F - 2;
+    const long long per_plane = (long long)P.ir * P.ic + 2LL * P.t2r * P.ic;
+    long long pb = SMEM_FLOATS / per_plane;
+    WT_CHECK(pb >= 1, WT_E_UNSUPPORTED, "generic analysis tile does not fit shared memory");
+    pb = std::min(pb, batch);
+    // keep the CTA busy but do not serialise too many planes behind 256 threads
+    pb = std::min(pb, std::max(1LL, 2048LL / ((long long)P.t2r * P.t2c)));
+    P.pb = (int)pb;
+    const long long groups = (batch + pb - 1) / pb;
+    const long long grid = groups * P.tiles_r * P.tiles_c;
+    WT_CHECK(grid < 2147483647LL, WT_E_UNSUPPORTED, "generic analysis grid too large");
+    const size_t smem = (size_t)pb * per_plane * sizeof(float);
+    wt_generic_analysis_kernel<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);
+    WT_CUDA(cudaGetLastError());
+    return WT_OK;
+}
+
+int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView da, WtView ad, WtView dd,
+                               long long batch, int h2, int w2, WtView out, int oh, int ow, const float* thr_dev,
+                               float thr_host, int use_thr, int thr_a, long long* counts4, cudaStream_t stream) {
+    SynParams P;
+    P.aa = aa; P.da = da; P.ad = ad; P.dd = dd; P.out = out;
+    P.batch = batch; P.h2 = h2; P.w2 = w2; P.oh = oh; P.ow = ow; P.mode = mode;
+    P.tr = std::min(oh, 32);
+    P.tc = std::min(ow, 64);
+    P.tiles_r = (oh + P.tr - 1) / P.tr;
+    P.tiles_c = (ow + P.tc - 1) / P.tc;
+    P.cr = P.tr / 2 + bank.F / 2 + 2;
+    P.cc = P.tc / 2 + bank.F / 2 + 2;
+    P.thr_dev = thr_dev; P.thr_host = thr_host; P.use_thr = use_thr; P.thr_a = thr_a; P.counts4 = counts4;
+    const long long per_plane = 4LL * P.cr * P.cc + 2LL * P.cr * P.tc;
+    long long pb = SMEM_FLOATS / per_plane;
+    WT_CHECK(pb >= 1, WT_E_UNSUPPORTED, "generic synthesis tile does not fit shared memory");
+    pb = std::min(pb, batch);
+    pb = std::min(pb, std::max(1LL, 2048LL / ((long long)P.tr * P.tc)));
+    P.pb = (int)pb;
+    const long long groups = (batch + pb - 1) / pb;
+    const long long grid = groups * P.tiles_r * P.tiles_c;
+    WT_CHECK(grid < 2147483647LL, WT_E_UNSUPPORTED, "generic synthesis grid too large");
+    const size_t smem = (size_t)pb * per_plane * sizeof(float);
+    wt_generic_synthesis_kernel<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);
+    WT_CUDA(cudaGetLastError());
+    return WT_OK;
+}
+
+int wt_count_nonzero_launch(const float* x, long long n, long long* counts4, cudaStream_t stream) {
+    if (n <= 0) return WT_OK;
+    WtDeviceInfo di;
+    int rc = wt_device_info(&di);
+    if (rc) return rc;
+    long long blocks = std::min((n + 255) / 256, (long long)di.sm_count * 8);
+    wt_count_nonzero_kernel<<<(int)blocks, 256, 0, stream>>>(x, n, counts4);
+    WT_CUDA(cudaGetLastError());
+    return WT_OK;
+}
+
+// flat coefficient layout: [cA_L | L: da, ad, dd | ... | 1: da, ad, dd]
+static void band_offsets(const WtGenericLayer& L, int F, int mode, int* hs, int* ws, long long* off /*[level+1][3]*/,
+                         long long* off_a) {
+    wt_level_sizes(L.H, F, mode, L.level, hs);
+    wt_level_sizes(L.W, F, mode, L.level, ws);
+    long long o = 0;
+    *off_a = 0;
+    o += L.batch * hs[L.level] * ws[L.level];
+    for (int l = L.level; l >= 1; --l) {
+        for (int b = 0; b < 3; ++b) {
+            off[l * 3 + b] = o;
+            o += L.batch * hs[l] * ws[l];
+        }
+    }
+}
+
+int wt_generic_analysis(const WtBank& bank, int mode, const WtGenericLayer& L, long long* counts, cudaStream_t stream,
+                        int* launches) {
+    int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
+    long long off[(WT_MAX_LEVEL + 1) * 3], off_a;
+    band_offsets(L, bank.F, mode, hs, ws, off, &off_a);
+    int rc = wt_count_nonzero_launch(L.in, L.batch * L.H * L.W, counts + (size_t)L.layer * 4, stream);
+    if (rc) return rc;
+    ++*launches;
+    WtView cur = wt_view(const_cast<float*>(L.in), L.H, L.W);
+    for (int l = 1; l <= L.level; ++l) {
+        float* dst = (l == L.level) ? L.coef + off_a : ((l & 1) ? L.tmp0 : L.tmp1);
+        WtView aa = wt_view(dst, hs[l], ws[l]);
+        WtView da = wt_view(L.coef + off[l * 3 + 0], hs[l], ws[l]);
+        WtView ad = wt_view(L.coef + off[l * 3 + 1], hs[l], ws[l]);
+        WtView dd = wt_view(L.coef + off[l * 3 + 2], hs[l], ws[l]);
+        rc = wt_generic_analysis_level(bank, mode, cur, L.batch, hs[l - 1], ws[l - 1], aa, da, ad, dd, stream);
+        if (rc) return rc;
+        ++*launches;
+        cur = aa;
+    }
+    return WT_OK;
+}
+
+int wt_generic_synthesis(const WtBank& bank, int mode, const WtGenericLayer& L, const float* thresholds,
+                         long long* counts, cudaStream_t stream, int* launches) {
+    int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
+    long long off[(WT_MAX_LEVEL + 1) * 3], off_a;
+    band_offsets(L, bank.F, mode, hs, ws, off, &off_a);
+    WtView cur = wt_view(L.coef + off_a, hs[L.level], ws[L.level]);
+    const float* thr_dev = L.use_abs ? nullptr : thresholds + L.layer;
+    for (int l = L.level; l >= 1; --l) {
+        // reconstruction is cropped to the next level's detail size, or to the input shape at l == 1
+        const int oh = hs[l - 1], ow = ws[l - 1];
+        float* dst = (l == 1) ? L.out : ((l & 1) ? L.tmp0 : L.tmp1);
+        WtView out = wt_view(dst, oh, ow);
+        WtView da = wt_view(L.coef + off[l * 3 + 0], hs[l], ws[l]);
+        WtView ad = wt_view(L.coef + off[l * 3 + 1], hs[l], ws[l]);
+        WtView dd = wt_view(L.coef + off[l * 3 + 2], hs[l], ws[l]);
+        int rc = wt_generic_synthesis_level(bank, mode, cur, da, ad, dd, L.batch, hs[l], ws[l], out, oh, ow, thr_dev,
+                                            L.abs_threshold, 1, l == L.level, l == 1 ? counts + (size_t)L.layer * 4 : nullptr,
+                                            stream);
+        if (rc) return rc;
+        ++*launches;
+        cur = out;
+    }
+    return WT_OK;
+}
