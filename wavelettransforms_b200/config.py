@@ -1,0 +1,14 @@
+"""Run-time switches that are not part of the reference's signatures.
+
+numpy_semantics: which NumPy's np.percentile arithmetic the thresholds reproduce.
+  'legacy_1_22' -- the reference's pin (requirements.txt:2, numpy==1.22.4); float64 index/lerp,
+                   float32 compare.  Default, because it is what produced the reference's logs.
+  'nep50_2x'    -- NumPy >= 2 (the NumPy installed on the GPU box); float32 index/lerp.
+Override with the environment variable WT_NUMPY_SEMANTICS or by assigning to this attribute.
+
+verbose: re-enables the reference's per-layer debug prints (dwt_pruning.py:29-30,121-122).
+"""
+import os
+
+numpy_semantics = os.environ.get('WT_NUMPY_SEMANTICS', 'legacy_1_22')
+verbose = os.environ.get('WT_VERBOSE', '0') not in ('0', '', 'false', 'False')

@@ -1,0 +1,99 @@
+"""Logging / path / model-I/O helpers the four pruning modules import, with the reference's names
+and CSV wire formats (/root/reference/ResNet/utils.py): the per-layer log (9 columns, :55-58) is read
+back by min_weight_pruning and random_pruning by column name, the experiment log has 8 columns
+(:127-128).  I/O only -- nothing here is on the GPU path."""
+import csv
+import os
+
+PER_LAYER_FIELDS = ['GUID', 'Wavelet', 'Level', 'Threshold', 'DWT Phase', 'Original Parameter Count', 'Non-zero Params',
+                    'Total Pruned Count', 'Layer Name']
+EXPERIMENT_FIELDS = ['GUID', 'Wavelet', 'Level', 'Threshold', 'Phase', 'Total Pruned Count', 'Total Non-Zero Params',
+                     'Model Path']
+
+# the reference hard-codes ../../WaveletTransforms/ResNet/SavedModels (utils.py:148-162); the
+# directory is configurable here and defaults to ./SavedModels
+OUTPUT_ROOT = os.environ.get('WT_OUTPUT_DIR', 'SavedModels')
+
+
+def load_model(model_path, config_path=None):
+    """utils.py:6-25 -- HF AutoModelForImageClassification on the CPU"""
+    from transformers import AutoModelForImageClassification
+    return AutoModelForImageClassification.from_pretrained(model_path)
+
+
+def save_model(model, output_dir):
+    """utils.py:28-38"""
+    os.makedirs(output_dir, exist_ok=True)
+    if hasattr(model, 'save_pretrained'):
+        model.save_pretrained(output_dir)
+    else:
+        import torch
+        torch.save(model.state_dict(), os.path.join(output_dir, 'pytorch_model.bin'))
+
+
+def setup_csv_writer(file_path, mode='w'):
+    """utils.py:41-65"""
+    file_exists = os.path.isfile(file_path)
+    d = os.path.dirname(file_path)
+    if d:
+        os.makedirs(d, exist_ok=True)
+    f = open(file_path, mode=mode, newline='')
+    writer = csv.DictWriter(f, fieldnames=PER_LAYER_FIELDS)
+    if mode == 'w' or (mode == 'a' and not file_exists):
+        writer.writeheader()
+    return writer, f
+
+
+def log_pruning_details(csv_writer, guid, wavelet, level, threshold, phase, original_param_count, non_zero_params,
+                        total_pruned_count, layer_name):
+    """utils.py:68-101"""
+    if not csv_writer or not layer_name:
+        return
+    csv_writer.writerow({
+        'GUID': guid, 'Wavelet': wavelet, 'Level': level, 'Threshold': threshold, 'DWT Phase': phase,
+        'Original Parameter Count': original_param_count, 'Non-zero Params': non_zero_params,
+        'Total Pruned Count': total_pruned_count, 'Layer Name': layer_name})
+
+
+def append_to_experiment_log(file_path, guid, wavelet, level, threshold, phase, total_pruned_count, total_non_zero_params,
+                             model_path):
+    """utils.py:104-145"""
+    if not file_path:
+        print('Error: Invalid file path provided.')
+        return
+    file_path = os.path.normpath(file_path)
+    file_exists = os.path.isfile(file_path)
+    d = os.path.dirname(file_path)
+    if d:
+        os.makedirs(d, exist_ok=True)
+    with open(file_path, mode='a', newline='') as f:
+        writer = csv.DictWriter(f, fieldnames=EXPERIMENT_FIELDS)
+        if not file_exists:
+            writer.writeheader()
+        writer.writerow({
+            'GUID': guid, 'Wavelet': wavelet, 'Level': level, 'Threshold': threshold, 'Phase': phase,
+            'Total Pruned Count': total_pruned_count, 'Total Non-Zero Params': total_non_zero_params,
+            'Model Path': model_path})
+
+
+def check_and_set_pruned_instance_path(pruned_instance):
+    """utils.py:148-162"""
+    path = os.path.join(OUTPUT_ROOT, pruned_instance)
+    os.makedirs(path, exist_ok=True)
+    return path
+
+
+def get_layer(model, layer_name):
+    """utils.py:209-238 -- dotted lookup; None when a component is missing"""
+    cur = model
+    for part in layer_name.split('.'):
+        if part.isdigit() and hasattr(cur, '__getitem__'):
+            try:
+                cur = cur[int(part)]
+                continue
+            except (IndexError, KeyError, TypeError):
+                return None
+        if not hasattr(cur, part):
+            return None
+        cur = getattr(cur, part)
+    return cur
