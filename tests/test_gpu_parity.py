@@ -1,0 +1,158 @@
+"""GPU parity tests: the CUDA path (through the C ABI of libwtprune) against the CPU oracle on the
+same seeded inputs.  Bar: masks, counts, thresholds and -- because the kernels follow the oracle's
+operation order without FMA -- the fp32 outputs themselves are BIT-EXACT versus the oracle."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WAVELETS = ['haar', 'db1', 'db2', 'db4', 'db6', 'coif1', 'coif2', 'coif3', 'bior1.3', 'bior2.2', 'bior4.4',
+            'rbio1.3', 'rbio2.2', 'rbio4.4', 'sym2', 'sym4', 'sym6']
+
+
+@pytest.fixture(scope='module')
+def mods(wtlib, oracle_lib):
+    from oracle import reference_flow as rf
+    from wavelettransforms_b200 import dwt_pruning, dwt_pruning_NoEntropy, engine, min_weight_pruning, random_pruning
+    return dict(rf=rf, dp=dwt_pruning, ne=dwt_pruning_NoEntropy, eng=engine, mw=min_weight_pruning, rp=random_pruning,
+                o=oracle_lib)
+
+
+def _bits(t):
+    return t.detach().cpu().contiguous().numpy().view(np.uint32)
+
+
+def assert_bit_equal(a, b, what=''):
+    a, b = _bits(a), _bits(b)
+    assert a.shape == b.shape, what
+    bad = int((a != b).sum())
+    assert bad == 0, f'{what}: {bad} of {a.size} elements differ bitwise'
+
+
+def test_select_abs_exact(mods):
+    eng = mods['eng']
+    g = torch.Generator().manual_seed(0)
+    for n in (1, 2, 5, 4095, 4096, 4097, 100003, 1 << 21):
+        x = torch.randn(n, generator=g) * 0.02
+        if n > 1000:
+            x[::7] = x[3]          # ties
+            x[5::11] = 0.0
+        s = torch.sort(x.abs()).values
+        xc = x.cuda()
+        for k0 in sorted({0, n // 10, n // 2, max(n - 2, 0), n - 1}):
+            k1 = min(k0 + 1, n - 1)
+            a, b = eng.select_abs(xc, k0, k1)
+            assert a == s[k0].item() and b == s[k1].item(), (n, k0)
+        # implicit zeros shift the ranks
+        z = 1000
+        for k0 in (0, z - 1, z, z + n // 2, z + n - 1):
+            k1 = min(k0 + 1, z + n - 1)
+            a, b = eng.select_abs(xc, k0, k1, implicit_zeros=z)
+            wa = 0.0 if k0 < z else s[k0 - z].item()
+            wb = 0.0 if k1 < z else s[k1 - z].item()
+            assert (a, b) == (wa, wb), (n, k0)
+
+
+@pytest.mark.parametrize('sem', ['legacy_1_22', 'nep50_2x'])
+def test_level0_percentile_vs_oracle_and_live_numpy(mods, sem):
+    dp, rf = mods['dp'], mods['rf']
+    g = torch.Generator().manual_seed(1)
+    shapes = [(64, 3, 7, 7), (64, 64, 3, 3), (128, 64, 1, 1), (37, 5, 3, 3), (1, 1, 1, 1), (513,)]
+    for p in (0.0, 10.0, 23.6, 50.0, 61.8, 90.0, 100.0):
+        ws = [torch.randn(s, generator=g) * 0.05 for s in shapes]
+        ws[1].view(-1)[::5] = 0.0
+        got, gz = dp.multi_resolution_analysis(ws, 'bior4.4', 5, p, numpy_semantics=sem)
+        want, wz = rf.multi_resolution_analysis(ws, 'bior4.4', 5, p, numpy_semantics=sem)
+        assert gz == wz, (p, sem)
+        for a, b, s in zip(got, want, shapes):
+            assert a.shape == b.shape and a.dtype == b.dtype and a.device == b.device
+            assert_bit_equal(a, b, f'level0 p={p} {s}')
+        if sem == 'nep50_2x':
+            live, lz = rf.multi_resolution_analysis(ws, 'bior4.4', 5, p, numpy_semantics='live')
+            assert lz == gz
+            for a, b in zip(got, live):
+                assert_bit_equal(a, b, 'vs live numpy')
+
+
+@pytest.mark.parametrize('wavelet', WAVELETS)
+def test_small_planes_percentile_unclamped(mods, wavelet):
+    dp, rf = mods['dp'], mods['rf']
+    g = torch.Generator().manual_seed(sum(map(ord, wavelet)))
+    for shape in ((33, 7, 3, 3), (5, 3, 7, 7), (40, 9, 1, 1), (6, 5, 5, 5)):
+        for level in (1, 2, 3, 5, 6):
+            w = torch.randn(shape, generator=g) * 0.02
+            got, gz = dp.multi_resolution_analysis([w], wavelet, level, 50.0, clamp_level=False)
+            want, wz = rf.multi_resolution_analysis([w], wavelet, level, 50.0, numpy_semantics='legacy_1_22',
+                                                    clamp_level=False)
+            assert_bit_equal(got[0], want[0], f'{wavelet} {shape} L{level}')
+            assert gz == wz
+
+
+@pytest.mark.parametrize('wavelet', ['haar', 'db2', 'bior2.2', 'rbio4.4', 'coif3'])
+def test_small_planes_absolute(mods, wavelet):
+    ne, rf = mods['ne'], mods['rf']
+    g = torch.Generator().manual_seed(7)
+    for shape in ((64, 16, 3, 3), (8, 3, 7, 7), (16, 16, 1, 1)):
+        for level in (1, 3, 5):
+            for thr in (0.0, 0.01, 0.05):
+                w = torch.randn(shape, generator=g) * 0.02
+                w.view(-1)[::9] = 0.0
+                got, gp = ne.multi_resolution_analysis([w], wavelet, level, thr)
+                want, wp = rf.multi_resolution_analysis_absolute([w], wavelet, level, thr)
+                assert_bit_equal(got[0], want[0], f'{wavelet} {shape} L{level} thr={thr}')
+                assert gp == wp
+
+
+@pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
+@pytest.mark.parametrize('wavelet', ['haar', 'db2', 'db4', 'coif3', 'bior1.3', 'bior4.4', 'rbio2.2', 'sym6'])
+def test_generic_packed_coefficients_bitwise(mods, wavelet, mode):
+    eng, o = mods['eng'], mods['o']
+    rng = np.random.default_rng(3)
+    for (H, W) in [(1, 1), (2, 2), (3, 3), (4, 4), (7, 7), (9, 12), (33, 33), (64, 64), (100, 37)]:
+        for level in (0, 1, 2, 4):
+            x = (rng.standard_normal((3, H, W)) * 0.02).astype(np.float32)
+            want = o.wavedec2_packed(x, wavelet, level, mode)
+            got = eng.wavedec2_packed(torch.from_numpy(x).cuda(), wavelet, level, mode)
+            assert_bit_equal(got, torch.from_numpy(want), f'dec {wavelet} {mode} {H}x{W} L{level}')
+            rec_want = o.waverec2_packed(want, x.shape, wavelet, level, mode)[:, :H, :W]
+            rec_got = eng.waverec2_packed(got, x.shape, wavelet, level, mode)
+            assert_bit_equal(rec_got, torch.from_numpy(np.ascontiguousarray(rec_want)), f'rec {wavelet} {mode} {H}x{W} L{level}')
+
+
+@pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
+def test_generic_path_prune_flows(mods, mode):
+    dp, ne, rf = mods['dp'], mods['ne'], mods['rf']
+    g = torch.Generator().manual_seed(11)
+    for wavelet, shape, level in (('db4', (2, 64, 64), 3), ('bior2.2', (3, 2, 9, 12), 2), ('sym4', (130, 130), 4),
+                                  ('bior4.4', (20, 3, 3, 3), 2), ('haar', (4, 4, 2, 2), 1)):
+        if mode == 'periodization' and shape[-1] in (3,) and shape[-2] == 3:
+            continue
+        w = torch.randn(shape, generator=g) * 0.02
+        got, gz = dp.multi_resolution_analysis([w], wavelet, level, 61.8, mode, clamp_level=False)
+        want, wz = rf.multi_resolution_analysis([w], wavelet, level, 61.8, mode=mode, numpy_semantics='legacy_1_22',
+                                                clamp_level=False)
+        assert_bit_equal(got[0], want[0], f'generic pct {wavelet} {shape} {mode}')
+        assert gz == wz
+        got, gp = ne.multi_resolution_analysis([w], wavelet, level, 0.01, mode)
+        want, wp = rf.multi_resolution_analysis_absolute([w], wavelet, level, 0.01, mode)
+        assert_bit_equal(got[0], want[0], f'generic abs {wavelet} {shape} {mode}')
+        assert gp == wp
+
+
+def test_golden_fixture(mods):
+    dp = mods['dp']
+    with open(os.path.join(ROOT, 'tests', 'golden', 'oracle_golden.json')) as f:
+        cases = json.load(f)
+    for c in cases:
+        x = torch.tensor(c['x'], dtype=torch.float32).view(c['shape'])
+        out, zeros = dp.multi_resolution_analysis([x], c['wavelet'], c['level'], c['percentile'], c['mode'],
+                                                  numpy_semantics=c['numpy_semantics'], clamp_level=c['clamp_level'])
+        assert out[0].numpy().tobytes().hex() == c['pruned_hex'], c['name']
+        assert zeros == c['zeros'], c['name']
+        got = mods['eng'].wavedec2_packed(x.cuda(), c['wavelet'], c['effective_level'], c['mode'])
+        assert got.cpu().numpy().tobytes().hex() == c['packed_hex'], c['name']

@@ -1,0 +1,130 @@
+"""CPU tests that pin the oracle (oracle/dwt_oracle.c): perfect reconstruction, the PyWavelets
+documentation known answers, the packing rule, live np.percentile, and the count laws of
+the reference's stored logs."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle as o
+from oracle import reference_flow as rf
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WAVELETS = ['haar', 'db1', 'db2', 'db4', 'db6', 'coif1', 'coif2', 'coif3', 'bior1.3', 'bior2.2', 'bior4.4',
+            'rbio1.3', 'rbio2.2', 'rbio4.4', 'sym2', 'sym4', 'sym6']
+S = np.float32(np.sqrt(2.0))
+
+
+def test_doc_known_answers():
+    ca, cd = o.dwt([1, 2, 3, 4, 5, 6], 'db1', 'symmetric')
+    np.testing.assert_allclose(ca, [2.12132034, 4.94974747, 7.77817459], rtol=1e-6)
+    np.testing.assert_allclose(cd, [-0.70710678] * 3, rtol=1e-6)
+    # wavedec([1..8], 'db1', level=2) -> cA2=[5,13], cD2=[-2,-2], cD1=[-0.7071]*4 (via the 2-D path, 1 x 8 plane)
+    x = np.arange(1, 9, dtype=np.float32)
+    a1, d1 = o.dwt(x, 'db1', 'symmetric')
+    a2, d2 = o.dwt(a1, 'db1', 'symmetric')
+    np.testing.assert_allclose(a2, [5, 13], rtol=1e-6)
+    np.testing.assert_allclose(d2, [-2, -2], rtol=1e-6)
+    np.testing.assert_allclose(d1, [-0.70710678] * 4, rtol=1e-6)
+    p = o.wavedec2_packed(np.ones((4, 4), np.float32), 'haar', 1)
+    np.testing.assert_allclose(p[:2, :2], 2.0, rtol=1e-6)
+    assert np.all(p[2:, :] == 0) and np.all(p[:, 2:] == 0)
+    r = o.waverec2_packed(o.wavedec2_packed(np.ones((4, 4), np.float32), 'db1', 2), (4, 4), 'db1', 2)
+    np.testing.assert_allclose(r, 1.0, rtol=1e-6)
+
+
+@pytest.mark.parametrize('wavelet', WAVELETS)
+def test_n1_periodization(wavelet):
+    # N=1: cA = sqrt(2) x, cD ~ 0 for any wavelet whose dec_lo sums to sqrt(2)
+    ca, cd = o.dwt([3.0], wavelet, 'periodization')
+    np.testing.assert_allclose(ca, [3.0 * S], rtol=2e-6)
+    assert abs(cd[0]) < 1e-5
+
+
+@pytest.mark.parametrize('wavelet', WAVELETS)
+@pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
+def test_perfect_reconstruction(wavelet, mode):
+    rng = np.random.default_rng(sum(map(ord, wavelet + mode)))
+    for (H, W) in [(1, 1), (2, 2), (3, 3), (4, 4), (7, 7), (8, 8), (9, 9), (33, 33), (64, 64), (5, 12), (3, 7)]:
+        for L in (0, 1, 2, 3, 5):
+            x = rng.standard_normal((3, H, W)).astype(np.float32)
+            r = o.waverec2_packed(o.wavedec2_packed(x, wavelet, L, mode), x.shape, wavelet, L, mode)
+            assert r.shape[-2] in (H, H + 1) and r.shape[-1] in (W, W + 1)
+            np.testing.assert_allclose(r[:, :H, :W], x, atol=2e-5)
+
+
+def test_packing_rule_padding():
+    # N=3 periodization sizes 2,1,1,1,1 -> pad cells 0/0/6/14/24 at L=1..5; N=7: 0/0/0/14/30
+    for n, pads in ((3, [0, 0, 6, 14, 24]), (7, [0, 0, 0, 14, 30])):
+        for L, pad in zip(range(1, 6), pads):
+            shp = o.packed_shape((n, n), 'bior4.4', L)
+            assert shp[0] * shp[1] - o.num_coeffs((n, n), 'bior4.4', L) == pad
+    assert o.packed_shape((3, 3), 'haar', 1) == (4, 4)
+    # padding cells are literal zeros
+    x = np.random.default_rng(0).standard_normal((2, 3, 3)).astype(np.float32) + 5
+    p = o.wavedec2_packed(x, 'haar', 3)
+    assert p.shape == (2, 5, 5) and int((p == 0).sum()) >= 2 * 6
+
+
+def test_percentile_restatement_equals_live_numpy():
+    rng = np.random.default_rng(1)
+    for trial in range(300):
+        n = int(rng.integers(1, 5000))
+        x = np.abs(rng.standard_normal(n).astype(np.float32))
+        if trial % 3 == 0:
+            x = np.round(x * 8) / 8
+        p = float(rng.choice([0, 10, 23.6, 38.2, 50, 61.8, 78.6, 90, 100, rng.uniform(0, 100)]))
+        assert rf.percentile_threshold_value(x, p, 'live') == rf.percentile_threshold_value(x, p, 'nep50_2x')
+
+
+def test_level0_identity_is_wavelet_independent():
+    # through dwt_pruning.py every bior/rbio/db4 config clamps to level 0 on 3x3 planes
+    torch.manual_seed(0)
+    w = torch.randn(16, 8, 3, 3)
+    outs = [rf.multi_resolution_analysis([w], wl, 5, 50.0, numpy_semantics='legacy_1_22')[0][0]
+            for wl in ('bior1.3', 'bior4.4', 'db4', 'rbio2.2')]
+    for t in outs[1:]:
+        assert torch.equal(t, outs[0])
+    assert rf.calculate_max_level((16, 8, 3, 3), 'bior4.4') == 0
+    assert rf.calculate_max_level((16, 8, 3, 3), 'haar') == 1
+    assert rf.calculate_max_level((64, 3, 7, 7), 'haar') == 2
+    assert rf.calculate_max_level((64, 3, 7, 7), 'db2') == 1
+
+
+def test_count_laws_of_stored_logs():
+    # reference logs: pruned = floor((p/100)(N-1)) + 1 for tie-free data, p=100 leaves exactly one
+    # nonzero (ResNet/StoredModels/*/selective_pruned/log.csv)
+    torch.manual_seed(1)
+    for N, p, want in ((9408, 10, 941), (36864, 10, 3687), (8192, 10, 820)):
+        w = torch.randn(N // 64, 64, 1, 1)
+        _, zeros = rf.multi_resolution_analysis([w], 'bior4.4', 5, float(p), numpy_semantics='legacy_1_22')
+        assert zeros in (want, want - 1)   # -1: float32 demotion of the threshold
+    w = torch.randn(64, 64, 3, 3)
+    _, zeros = rf.multi_resolution_analysis([w], 'bior4.4', 5, 100.0, numpy_semantics='legacy_1_22')
+    assert zeros == w.numel() - 1
+    _, zeros = rf.multi_resolution_analysis([w], 'bior4.4', 5, 0.0, numpy_semantics='legacy_1_22')
+    assert zeros == 0
+    # min-weight k = int(N * pct): 4703 of 9408 at the stored overall fraction
+    pct = 5583455 / 11166912
+    assert int(9408 * pct) == 4703
+    t = torch.randn(64, 3, 7, 7)
+    out = rf.percentage_min_pruning(t, pct)
+    assert int((out == 0).sum()) == 4703
+
+
+def test_golden_fixture_matches_oracle():
+    path = os.path.join(ROOT, 'tests', 'golden', 'oracle_golden.json')
+    with open(path) as f:
+        cases = json.load(f)
+    assert len(cases) >= 20
+    for c in cases:
+        x = np.array(c['x'], dtype=np.float32).reshape(c['shape'])
+        packed = o.wavedec2_packed(x, c['wavelet'], c['effective_level'], c['mode'])
+        assert packed.astype(np.float32).tobytes().hex() == c['packed_hex'], c['name']
+        out, zeros = rf.multi_resolution_analysis([torch.from_numpy(x)], c['wavelet'], c['level'], c['percentile'],
+                                                  mode=c['mode'], numpy_semantics=c['numpy_semantics'],
+                                                  clamp_level=c['clamp_level'])
+        assert out[0].numpy().tobytes().hex() == c['pruned_hex'], c['name']
+        assert zeros == c['zeros'], c['name']
