@@ -119,6 +119,17 @@ int wt_plan_run(WtPlan* plan, void* stream);
  */
 int wt_plan_results(WtPlan* plan, void* stream, int64_t* counts, int64_t* nonzero_before,
                     float* thresholds);
+/*
+ * Optional device-side timing of the phases of wt_plan_run (memset, [h2d], one entry per analysis
+ * launch group, select, one per synthesis launch group, [d2h]).  When enabled, wt_plan_run records
+ * a cudaEvent on `stream` between phases; wt_plan_phase_times waits for the last run and returns
+ * the number of phases (<= max_phases; negative = error), filling ms[i], launches[i] (kernels in
+ * phase i) and the NUL-terminated names (names + i*name_stride).  Used by bench.py for the live
+ * per-kernel durations; leave it off on the production path (each event costs ~1 us of stream time).
+ */
+int wt_plan_set_timing(WtPlan* plan, int enable);
+int wt_plan_phase_times(WtPlan* plan, int max_phases, float* ms, int* launches, char* names,
+                        int name_stride);
 /* device address of the int64 [n_layers][4] result block {numel, nonzero, zeros, nonzero_before} */
 int wt_plan_counts_device(WtPlan* plan, const int64_t** counts_dev);
 

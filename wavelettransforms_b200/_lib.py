@@ -24,6 +24,7 @@ EXPORTS = [
     'wt_version', 'wt_last_error', 'wt_wavelet_lookup', 'wt_wavelet_filters', 'wt_dwt_max_level', 'wt_dwt_coeff_len',
     'wt_packed_shape', 'wt_percentile_plan', 'wt_plan_create', 'wt_plan_destroy', 'wt_plan_device_bytes',
     'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device',
+    'wt_plan_set_timing', 'wt_plan_phase_times',
     'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
     'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32',
 ]
@@ -59,6 +60,8 @@ def lib():
     L.wt_plan_run.argtypes = [vp, vp]
     L.wt_plan_results.argtypes = [vp, vp, P(i64), P(i64), P(fl)]
     L.wt_plan_counts_device.argtypes = [vp, P(vp)]
+    L.wt_plan_set_timing.argtypes = [vp, ci]
+    L.wt_plan_phase_times.argtypes = [vp, ci, P(fl), P(ci), ctypes.c_char_p, ci]
     L.wt_dwt_prune_f32.argtypes = [P(WtLayerDesc), ci, ci, ci, ci, dbl, ci, vp, P(i64), P(i64), P(fl)]
     L.wt_select_abs_f32.argtypes = [vp, i64, i64, i64, i64, vp, vp]
     L.wt_wavedec2_packed_f32.argtypes = [vp, i64, ci, ci, ci, ci, ci, vp, vp]
@@ -168,6 +171,20 @@ class Plan:
         check(lib().wt_plan_results(self._h, ctypes.c_void_p(stream), counts, nzb, thr))
         c = np.array(counts[:3 * self.n], dtype=np.int64).reshape(self.n, 3)
         return c, np.array(nzb[:self.n], dtype=np.int64), np.array(thr[:self.n], dtype=np.float32)
+
+    def set_timing(self, enable=True):
+        check(lib().wt_plan_set_timing(self._h, 1 if enable else 0))
+
+    def phase_times(self, max_phases=256):
+        """[(name, ms, kernel launches)] of the last run (waits for it); needs set_timing(True)"""
+        ms = (ctypes.c_float * max_phases)()
+        ln = (ctypes.c_int * max_phases)()
+        names = ctypes.create_string_buffer(max_phases * 64)
+        n = lib().wt_plan_phase_times(self._h, max_phases, ms, ln, names, 64)
+        if n < 0:
+            check(n)
+        raw = names.raw
+        return [(raw[i * 64:(i + 1) * 64].split(b'\0', 1)[0].decode(), float(ms[i]), int(ln[i])) for i in range(n)]
 
     @property
     def device_bytes(self):

@@ -207,6 +207,14 @@ struct WtPlan {
     std::vector<long long> ncoef, zeros;  // per layer: explicit coefficients / implicit padding zeros
     float *tmp0 = nullptr, *tmp1 = nullptr;
     int n_launches = 0;
+
+    // optional per-phase device timing (wt_plan_set_timing): events[i] is recorded before phase i,
+    // events.back() after the last one
+    int timing = 0;
+    std::vector<cudaEvent_t> events;
+    std::vector<std::string> phase_names;
+    std::vector<int> phase_launches;
+    size_t n_phases = 0;
 };
 
 static size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
@@ -289,6 +297,7 @@ static int upload_tables(WtPlan* P) {
 
 extern "C" int wt_plan_destroy(WtPlan* P) {
     if (!P) return WT_OK;
+    for (cudaEvent_t e : P->events) cudaEventDestroy(e);
     if (P->dev) cudaFree(P->dev);
     delete P;
     return WT_OK;
@@ -446,7 +455,28 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int n = (int)P->layers.size();
     int launches = 0;
+    P->n_phases = 0;
+    int mark_rc = WT_OK, mark_launches = 0;
+    // closes the previous phase (launch count) and opens phase `name` (nullptr = just close)
+    auto mark = [&](const char* name) {
+        if (!P->timing || mark_rc) return;
+        if (P->n_phases) P->phase_launches[P->n_phases - 1] = launches - mark_launches;
+        mark_launches = launches;
+        const size_t slot = P->n_phases;
+        if (P->events.size() <= slot) {
+            cudaEvent_t e;
+            if (cudaEventCreate(&e) != cudaSuccess) { mark_rc = WT_E_CUDA; return; }
+            P->events.push_back(e);
+            P->phase_names.push_back("");
+            P->phase_launches.push_back(0);
+        }
+        if (cudaEventRecord(P->events[slot], stream) != cudaSuccess) { mark_rc = WT_E_CUDA; return; }
+        if (name) { P->phase_names[slot] = name; ++P->n_phases; }
+    };
+    char label[64];
+    mark("memset");
     WT_CUDA(cudaMemsetAsync(P->zero_block, 0, P->zero_bytes, stream));
+    if (P->host_io) mark("h2d");
     if (P->host_io)
         for (int i = 0; i < n; ++i)
             if (P->path[i] != PATH_EMPTY)
@@ -455,22 +485,28 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     int rc;
     // 1. analysis
     for (auto& c : P->small) {
+        snprintf(label, sizeof(label), "small_analysis_%dx%d", c.H, c.W);
+        mark(label);
         rc = wt_small_analysis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev, stream);
         if (rc) return rc;
         if (c.n_tiles) ++launches;
     }
     for (auto& g : P->generic) {
+        snprintf(label, sizeof(label), "generic_analysis_layer%d", g.layer);
+        mark(label);
         rc = wt_generic_analysis(P->bank, P->mode, g, P->counts_dev, stream, &launches);
         if (rc) return rc;
     }
     // 2. threshold: exact percentile select (+ fused level-0 apply), or plain compare
     if (P->thr_kind == WT_THRESHOLD_PERCENTILE) {
         if (!P->sel_jobs.empty()) {
+            mark(P->sel_args.any_apply ? "select_apply" : "select");
             rc = wt_select_launch(P->sel_args, stream);
             if (rc) return rc;
             ++launches;
         }
     } else {
+        if (!P->level0_abs.empty()) mark("threshold_level0");
         for (int i : P->level0_abs) {
             rc = wt_apply_threshold_launch(P->d_in[i], P->d_out[i], layer_numel(P->layers[i]), nullptr, (float)P->thr_value,
                                            P->counts_dev + (size_t)i * 4, stream);
@@ -480,22 +516,54 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     }
     // 3. synthesis with the threshold applied on load
     for (auto& c : P->small) {
+        snprintf(label, sizeof(label), "small_synthesis_%dx%d", c.H, c.W);
+        mark(label);
         rc = wt_small_synthesis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->thresholds_dev,
                                        P->counts_dev, stream);
         if (rc) return rc;
         if (c.n_tiles) ++launches;
     }
     for (auto& g : P->generic) {
+        snprintf(label, sizeof(label), "generic_synthesis_layer%d", g.layer);
+        mark(label);
         rc = wt_generic_synthesis(P->bank, P->mode, g, P->thresholds_dev, P->counts_dev, stream, &launches);
         if (rc) return rc;
     }
+    if (P->host_io) mark("d2h");
     if (P->host_io)
         for (int i = 0; i < n; ++i)
             if (P->path[i] != PATH_EMPTY)
                 WT_CUDA(cudaMemcpyAsync(P->layers[i].out, P->d_out[i], (size_t)layer_numel(P->layers[i]) * sizeof(float),
                                         cudaMemcpyDeviceToHost, stream));
+    mark(nullptr);
+    WT_CHECK(mark_rc == WT_OK, WT_E_CUDA, "wt_plan_run: cudaEvent failure while timing phases");
     P->n_launches = launches;
     return WT_OK;
+}
+
+extern "C" int wt_plan_set_timing(WtPlan* P, int enable) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    P->timing = enable ? 1 : 0;
+    if (!enable) P->n_phases = 0;
+    return WT_OK;
+}
+
+extern "C" int wt_plan_phase_times(WtPlan* P, int max_phases, float* ms, int* launches, char* names, int name_stride) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    const int n = (int)P->n_phases;
+    if (n == 0) return 0;
+    WT_CUDA(cudaEventSynchronize(P->events[n]));
+    for (int i = 0; i < n && i < max_phases; ++i) {
+        float t = 0.f;
+        WT_CUDA(cudaEventElapsedTime(&t, P->events[i], P->events[i + 1]));
+        if (ms) ms[i] = t;
+        if (launches) launches[i] = P->phase_launches[i];
+        if (names && name_stride > 0) {
+            strncpy(names + (size_t)i * name_stride, P->phase_names[i].c_str(), name_stride - 1);
+            names[(size_t)i * name_stride + name_stride - 1] = 0;
+        }
+    }
+    return n < max_phases ? n : max_phases;
 }
 
 extern "C" int wt_plan_counts_device(WtPlan* P, const int64_t** counts_dev) {
