@@ -8,6 +8,7 @@
 // optional host-I/O staging) and replays a fixed launch sequence with no host synchronisation.
 #include <math.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -204,12 +205,15 @@ struct WtPlan {
 
     // per-layer device pointers actually used by the kernels (staging for host I/O)
     std::vector<float*> d_in, d_out, d_coef;
+    std::vector<unsigned int*> d_cand;  // candidate-key lists of the select fast path
+    std::vector<unsigned int> cand_cap;
     std::vector<long long> ncoef, zeros;  // per layer: explicit coefficients / implicit padding zeros
     float *tmp0 = nullptr, *tmp1 = nullptr;
     int n_launches = 0;
 
     // optional per-phase device timing (wt_plan_set_timing): events[i] is recorded before phase i,
     // events.back() after the last one
+    unsigned long long* stamps_dev = nullptr;  // WT_SELECT_STAMPS tuning aid
     int timing = 0;
     std::vector<cudaEvent_t> events;
     std::vector<std::string> phase_names;
@@ -271,6 +275,8 @@ static int build_tables(WtPlan* P) {
             if (rc) return rc;
             j.k0 = k0; j.k1 = k1; j.gamma = gamma;
             j.lerp_mode = (P->sem == WT_NUMPY_LEGACY_1_22) ? WT_LERP_LEGACY : WT_LERP_NEP50;
+            j.cand = P->d_cand[i];
+            j.cand_cap = P->cand_cap[i];
             j.tile_begin = sel_tiles;
             const long long nt = (j.n + WT_SEL_TILE - 1) / WT_SEL_TILE;
             WT_CHECK(sel_tiles + nt < 2147483647LL, WT_E_UNSUPPORTED, "too many select tiles");
@@ -298,6 +304,7 @@ static int upload_tables(WtPlan* P) {
 extern "C" int wt_plan_destroy(WtPlan* P) {
     if (!P) return WT_OK;
     for (cudaEvent_t e : P->events) cudaEventDestroy(e);
+    if (P->stamps_dev) cudaFree(P->stamps_dev);
     if (P->dev) cudaFree(P->dev);
     delete P;
     return WT_OK;
@@ -331,11 +338,12 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     P->path.assign(n_layers, PATH_EMPTY);
     P->d_in.assign(n_layers, nullptr); P->d_out.assign(n_layers, nullptr); P->d_coef.assign(n_layers, nullptr);
     P->ncoef.assign(n_layers, 0); P->zeros.assign(n_layers, 0);
+    P->d_cand.assign(n_layers, nullptr); P->cand_cap.assign(n_layers, 0);
     const int F = P->bank.F;
 
     // ---- classify + size ----
     size_t bytes = 0;
-    std::vector<size_t> off_coef(n_layers, 0), off_io(n_layers, 0);
+    std::vector<size_t> off_coef(n_layers, 0), off_io(n_layers, 0), off_cand(n_layers, 0);
     long long tmp_elems = 0;
     int n_sel = 0;
     for (int i = 0; i < n_layers; ++i) {
@@ -377,6 +385,13 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     const size_t zero_bytes = bytes - off_zero;
     for (int i = 0; i < n_layers; ++i)
         if (P->path[i] == PATH_SMALL || P->path[i] == PATH_GENERIC) off_coef[i] = take((size_t)P->ncoef[i] * sizeof(float));
+    if (threshold_kind == WT_THRESHOLD_PERCENTILE)
+        for (int i = 0; i < n_layers; ++i)
+            if (P->path[i] != PATH_EMPTY) {
+                const long long pop = (P->path[i] == PATH_LEVEL0) ? layer_numel(P->layers[i]) : P->ncoef[i];
+                P->cand_cap[i] = wt_select_cand_cap(pop);
+                off_cand[i] = take((size_t)P->cand_cap[i] * sizeof(unsigned int));
+            }
     const size_t off_tmp0 = take((size_t)tmp_elems * sizeof(float));
     const size_t off_tmp1 = take((size_t)tmp_elems * sizeof(float));
     if (host_io)
@@ -400,11 +415,17 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     P->sel_args.n_jobs = n_sel;
     P->sel_args.thresholds = P->thresholds_dev;
     P->sel_args.counts = P->counts_dev;
+    if (getenv("WT_SELECT_STAMPS")) {
+        if (cudaMalloc((void**)&P->stamps_dev, (size_t)WT_SEL_STAMP_CTAS * 16 * 8) == cudaSuccess)
+            cudaMemset(P->stamps_dev, 0, (size_t)WT_SEL_STAMP_CTAS * 16 * 8);
+        P->sel_args.stamps = P->stamps_dev;
+    }
     P->tmp0 = reinterpret_cast<float*>(P->dev + off_tmp0);
     P->tmp1 = reinterpret_cast<float*>(P->dev + off_tmp1);
     for (int i = 0; i < n_layers; ++i) {
         if (P->path[i] == PATH_EMPTY) continue;
         if (P->path[i] != PATH_LEVEL0) P->d_coef[i] = reinterpret_cast<float*>(P->dev + off_coef[i]);
+        if (P->cand_cap[i]) P->d_cand[i] = reinterpret_cast<unsigned int*>(P->dev + off_cand[i]);
         if (host_io) {
             P->d_in[i] = P->d_out[i] = reinterpret_cast<float*>(P->dev + off_io[i]);
         } else {
@@ -583,6 +604,25 @@ extern "C" int wt_plan_results(WtPlan* P, void* stream_, int64_t* counts, int64_
         WT_CUDA(cudaMemcpyAsync(thr.data(), P->thresholds_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, stream));
     }
     WT_CUDA(cudaStreamSynchronize(stream));
+    if (P->stamps_dev && !P->sel_jobs.empty()) {
+        std::vector<unsigned long long> st((size_t)WT_SEL_STAMP_CTAS * 16);
+        WT_CUDA(cudaMemcpy(st.data(), P->stamps_dev, st.size() * 8, cudaMemcpyDeviceToHost));
+        WT_CUDA(cudaMemset(P->stamps_dev, 0, st.size() * 8));
+        unsigned long long t0 = ~0ull;
+        int g = 0;
+        for (int c = 0; c < WT_SEL_STAMP_CTAS; ++c) if (st[c * 16]) { t0 = std::min(t0, st[c * 16]); g = c + 1; }
+        double mx[16] = {0}, sum[16] = {0};
+        for (int c = 0; c < g; ++c)
+            for (int k = 0; k < 16; ++k) {
+                double v = (k < 6) ? (double)(st[c * 16 + k] - t0) * 1e-3 : (double)st[c * 16 + k] * 1e-3;
+                mx[k] = std::max(mx[k], v);
+                sum[k] += v / g;
+            }
+        fprintf(stderr, "[wt select %d CTAs, us, mean/max] endP1 %.1f/%.1f endP2 %.1f/%.1f endP3 %.1f/%.1f sync3 %.1f/%.1f end %.1f/%.1f"
+                " || acc: span1 %.1f/%.1f flush1 %.1f/%.1f scan1 %.1f/%.1f span2 %.1f/%.1f flush2 %.1f/%.1f P3 %.1f/%.1f scan3 %.1f/%.1f apply %.1f/%.1f\n",
+                g, sum[1], mx[1], sum[2], mx[2], sum[3], mx[3], sum[4], mx[4], sum[5], mx[5], sum[6], mx[6], sum[7], mx[7],
+                sum[8], mx[8], sum[9], mx[9], sum[10], mx[10], sum[11], mx[11], sum[12], mx[12], sum[13], mx[13]);
+    }
     for (int i = 0; i < n; ++i) {
         if (counts) {
             counts[i * 3 + 0] = layer_numel(P->layers[i]);

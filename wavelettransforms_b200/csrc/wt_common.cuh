@@ -58,12 +58,14 @@ void wt_level_sizes(int n, int F, int mode, int level, int* sizes);
 #define WT_SEL_BINS1 4096  // key bits 30..19
 #define WT_SEL_BINS2 1024  // key bits 18..9
 #define WT_SEL_BINS3 512   // key bits  8..0
+#define WT_SEL_COARSE (WT_SEL_BINS1 / 32)
 
 enum { WT_LERP_LEGACY = 0, WT_LERP_NEP50 = 1, WT_LERP_ABSOLUTE = 2 };
 
 struct WtSelJob {
     const float* x;
-    float* out;  // nullable
+    float* out;          // nullable
+    unsigned int* cand;  // candidate keys of the fast path (nullable: then the job takes the 3-pass path)
     long long n;
     long long zeros;
     long long k0, k1;
@@ -72,14 +74,18 @@ struct WtSelJob {
     int lerp_mode;
     int tile_begin;  // first tile of this job in the flattened tile space
     int n_tiles;
-    int layer;  // index into the counts / thresholds arrays
-    int pad;
+    int layer;       // index into the counts / thresholds arrays
+    unsigned int cand_cap;  // capacity of cand[] in keys
 };
 
-struct WtSelState {  // per job, device
-    unsigned int prefix[2];
-    unsigned long long rem[2];
-    float a, b, t;
+struct WtSelState {  // per job, device; written by the CTA that holds the job's first tile
+    unsigned int prefix1[2];       // 12-bit digits of rank k0 / k1 (after P1)
+    unsigned int prefix2[2];       // 22-bit prefixes (after P2)
+    unsigned long long rem1[2];    // ranks inside those digits
+    unsigned long long rem2[2];
+    float a, b, t;                 // sorted[k0], sorted[k1], threshold
+    unsigned int cand_count;       // keys appended to cand[] by P2
+    int overflow;                  // 1: more candidates than cand_cap -> P3 re-reads the tensor
     int pad;
 };
 
@@ -91,16 +97,27 @@ struct WtSelArgs {
     unsigned long long* hist1;  // [n_jobs][BINS1]
     unsigned long long* hist2;  // [n_jobs][2][BINS2]
     unsigned long long* hist3;  // [n_jobs][2][BINS3]
-    unsigned int* done;         // [n_jobs][4]
+    unsigned long long* hist1c; // [n_jobs][BINS1 / 32]: coarse sums of hist1 (32 fine bins each)
+    unsigned long long* stamps; // nullable tuning aid: [grid][16] per-CTA phase stamps / accumulated ns
     float* thresholds;          // [n_layers]
     long long* counts;          // [n_layers][4] {numel, nonzero, zeros, nonzero_before}
     int any_apply;              // at least one job has out != nullptr
 };
 
+// candidate capacity (keys) the plan reserves for a population of n explicit values
+static inline unsigned int wt_select_cand_cap(long long n) {
+    long long c = n / 8;
+    if (c > (1LL << 19)) c = 1LL << 19;
+    if (c < 4096) c = 4096;
+    if (c > n) c = n;
+    return (unsigned int)c;
+}
+
 size_t wt_select_scratch_bytes(int n_jobs);  // hist1+hist2+hist3+done+state, contiguous, memset to 0 before launch
 // lays out args over a zeroed scratch block
 void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
+#define WT_SEL_STAMP_CTAS 2048
 
 // ---- level-0 apply for absolute thresholds and generic elementwise helpers (wt_select.cu) --------
 int wt_apply_threshold_launch(const float* x, float* out, long long n, const float* thr_dev, float thr_host,

@@ -4,18 +4,23 @@
 // Replaces np.percentile(np.abs(coeff_arr), p) + np.where(|c| < t, 0, c)
 // (/root/reference/ResNet/dwt_pruning.py:27,31) and the zero count of dwt_pruning.py:88.
 //
-// Algorithm: 3-pass most-significant-digit radix select on the 31-bit pattern of |x|
-// (12 + 10 + 9 bits).  The pattern order equals the numeric order for non-NaN floats.  Two ranks
-// (k0 = floor(virtual index), k1 = k0 + 1) are tracked together so the interpolation of
-// np.percentile can be reproduced from the exact sorted[k0] and sorted[k1].  Implicit zeros
-// (coeffs_to_array padding) are added to digit 0 of every pass whose prefix is 0.
+// Keys are the 31-bit patterns of |x| (pattern order = numeric order for non-NaN floats).  Two
+// ranks (k0 = floor(virtual index), k1 = k0 + 1) are tracked together so np.percentile's
+// interpolation can be reproduced from the exact sorted[k0] and sorted[k1].  Implicit zeros
+// (coeffs_to_array padding) are added to digit 0 wherever the prefix is 0.
 //
-// Grid: persistent, one contiguous range of 4096-element tiles per CTA, all CTAs co-resident
-// (cooperative launch); a grid barrier separates the passes.  Per pass each CTA histograms into
-// shared memory, flushes the non-empty bins with global atomics, and the CTA that retires the last
-// tile of a job scans that job's histogram (threadfence + ticket), so no extra barrier is needed.
-// Pass 1 streams the tensors from HBM; passes 2, 3 and the apply phase re-read them from L2
-// (126 MB on B200) when the group fits.
+// MSD radix select, 12 + 10 + 9 key bits, on a persistent grid: every CTA owns one contiguous
+// range of 4096-element tiles (cut into per-job segments), grid barriers separate the phases, and
+// NO phase has a serial tail: after a barrier every CTA scans the (small, L2-resident) global
+// histogram of its own job redundantly instead of waiting for one elected CTA to do it.
+//   P1  histogram of key bits 30..19 (streams the tensors from HBM) -> global hist1
+//   P2  scan hist1 -> digit of both ranks; histogram of bits 18..9 of the matching keys -> hist2,
+//       and the matching keys (about 2 % of a Gaussian tensor) are compacted into the job's
+//       candidate list through a shared-memory staging buffer (tensors re-read from L2)
+//   P3  scan hist2 -> 22-bit prefixes; histogram of bits 8..0 over the CANDIDATE LIST only -> hist3
+//   P4  scan hist3 -> sorted[k0], sorted[k1] -> threshold; level-0 jobs: out = |x| < t ? 0 : x + counts
+// A job whose candidates do not fit its list (heavy ties, e.g. half the tensor exactly zero) re-reads
+// the tensor in P3 instead of the list.
 #include <cooperative_groups.h>
 
 #include "wt_common.cuh"
@@ -24,7 +29,24 @@ namespace cg = cooperative_groups;
 
 namespace {
 
+constexpr int T = WT_SEL_THREADS;
+constexpr int UNROLL = 4;  // float4 loads in flight per thread
+
 __device__ __forceinline__ unsigned int abs_key(float v) { return __float_as_uint(v) & 0x7fffffffu; }
+
+// tuning aid (WT_SELECT_STAMPS): 16 u64 slots per CTA; slots 0..5 phase boundaries, 6.. accumulated ns
+__device__ __forceinline__ unsigned long long now_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+struct Acc {
+    unsigned long long* slot;  // nullptr when stamps are off
+    unsigned long long t0;
+    __device__ __forceinline__ void begin() { if (slot && threadIdx.x == 0) t0 = now_ns(); }
+    __device__ __forceinline__ void end(int i) { if (slot && threadIdx.x == 0) slot[i] += now_ns() - t0; }
+    __device__ __forceinline__ void stamp(int i) { if (slot && threadIdx.x == 0) slot[i] = now_ns(); }
+};
 
 __device__ __forceinline__ int find_job(const WtSelJob* __restrict__ jobs, int n_jobs, int tile) {
     int lo = 0, hi = n_jobs - 1;
@@ -50,68 +72,29 @@ __device__ __forceinline__ void bin_one(unsigned int key, unsigned int* sh, unsi
     }
 }
 
-// exclusive block scan of one value per thread (512 threads), returns the exclusive prefix and the total
-__device__ __forceinline__ unsigned long long block_excl_scan(unsigned long long v, unsigned long long* warp_sums,
-                                                              unsigned long long* total) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    unsigned long long inc = v;
+// Calls op(float) on x[0..len): float4 loads, UNROLL of them in flight per thread.
+template <class Op>
+__device__ __forceinline__ void span_for_each(const float* __restrict__ x, long long len, Op op) {
+    if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
+        const long long nvec = len >> 2;
+        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
+        for (long long v = threadIdx.x; v < nvec; v += (long long)T * UNROLL) {
+            float4 r[UNROLL];
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= d) inc += o;
-    }
-    if (lane == 31) warp_sums[wid] = inc;
-    __syncthreads();
-    if (wid == 0) {
-        unsigned long long w = (lane < WT_SEL_THREADS / 32) ? warp_sums[lane] : 0ull;
-        unsigned long long winc = w;
+            for (int u = 0; u < UNROLL; ++u)
+                if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            unsigned long long o = __shfl_up_sync(0xffffffffu, winc, d);
-            if (lane >= d) winc += o;
+            for (int u = 0; u < UNROLL; ++u)
+                if (v + (long long)u * T < nvec) { op(r[u].x); op(r[u].y); op(r[u].z); op(r[u].w); }
         }
-        if (lane < WT_SEL_THREADS / 32) warp_sums[lane] = winc - w;  // exclusive warp offsets
-        if (lane == WT_SEL_THREADS / 32 - 1) warp_sums[WT_SEL_THREADS / 32] = winc;
+        for (long long i = (nvec << 2) + threadIdx.x; i < len; i += T) op(__ldg(&x[i]));
+    } else {
+        for (long long i = threadIdx.x; i < len; i += T) op(__ldg(&x[i]));
     }
-    __syncthreads();
-    unsigned long long excl = warp_sums[wid] + inc - v;
-    *total = warp_sums[WT_SEL_THREADS / 32];
-    __syncthreads();
-    return excl;
 }
 
-// find the digit holding `rank` in hist[0..NB) (+ zeros in bin 0); result through shared memory
-template <int NB>
-__device__ void scan_find(const unsigned long long* hist, unsigned long long zeros, unsigned long long rank,
-                          unsigned long long* warp_sums, unsigned int* res_digit, unsigned long long* res_rem) {
-    constexpr int PER = (NB + WT_SEL_THREADS - 1) / WT_SEL_THREADS;
-    unsigned long long c[PER];
-    unsigned long long s = 0;
-#pragma unroll
-    for (int i = 0; i < PER; ++i) {
-        int b = threadIdx.x * PER + i;
-        unsigned long long v = (b < NB) ? __ldcg(&hist[b]) : 0ull;
-        if (b == 0) v += zeros;
-        c[i] = v;
-        s += v;
-    }
-    unsigned long long total;
-    unsigned long long excl = block_excl_scan(s, warp_sums, &total);
-    if (rank >= total) rank = total ? total - 1 : 0;  // defensive; cannot happen for a consistent plan
-    if (s > 0 && excl <= rank && rank < excl + s) {
-        unsigned long long run = excl;
-#pragma unroll
-        for (int i = 0; i < PER; ++i) {
-            if (rank < run + c[i]) {
-                *res_digit = threadIdx.x * PER + i;
-                *res_rem = rank - run;
-                break;
-            }
-            run += c[i];
-        }
-    }
-    __syncthreads();
-}
+__device__ __forceinline__ unsigned long long load_bin(const unsigned long long* h, int b) { return __ldcg(&h[b]); }
+
 
 __device__ __forceinline__ float lerp_threshold(float a, float b, double gamma, int mode) {
     if (mode == WT_LERP_LEGACY) {
@@ -130,111 +113,254 @@ __device__ __forceinline__ float lerp_threshold(float a, float b, double gamma, 
     }
 }
 
+constexpr unsigned int STAGE_FLUSH = 2048;                        // flush the staging buffer once it holds more keys
+constexpr unsigned int STAGE = STAGE_FLUSH + T * UNROLL * 4;      // one more iteration always fits
+
 struct Shared {
     unsigned int hist[WT_SEL_BINS1];
-    unsigned long long warp_sums[WT_SEL_THREADS / 32 + 1];
+    unsigned int stage[STAGE];  // P2: candidate keys on their way to the job's global list
+    unsigned long long warp_sums[2][T / 32 + 1];
     unsigned long long res_rem[2];
+    unsigned long long res_cnt[2];
     unsigned int res_digit[2];
-    int is_last;
+    unsigned int s_cnt;   // keys in the staging buffer
+    unsigned int s_base;  // where they go in the global candidate list
+    int s_flag;
 };
 
+
+struct Found {
+    unsigned int d0, d1;          // digit holding rank0 / rank1
+    unsigned long long r0, r1;    // rank inside that digit
+    unsigned long long c0, c1;    // EXPLICIT keys in that digit (implicit zeros excluded)
+};
+
+// Locates both ranks in one go: h0 (+ z0 implicit zeros in bin 0) holds rank0, h1 (+ z1) holds rank1;
+// h1 == h0 when the two ranks share a histogram.  Every thread returns the same result.
+template <int NB, bool ALWAYS_SAME, class H>
+__device__ Found scan_find_pair(const H* h0, const H* h1, unsigned long long z0, unsigned long long z1,
+                                unsigned long long rank0, unsigned long long rank1, Shared& sh) {
+    constexpr int PER = (NB + T - 1) / T;
+    const bool same = ALWAYS_SAME || (h0 == h1);
+    unsigned long long c0[PER], c1[ALWAYS_SAME ? 1 : PER];  // ALWAYS_SAME: c1 is never materialised
+    unsigned long long s0 = 0, s1 = 0;
+#define WT_C1(i) (ALWAYS_SAME ? c0[i] : c1[ALWAYS_SAME ? 0 : (i)])
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+        const int b = threadIdx.x * PER + i;
+        c0[i] = (b < NB) ? load_bin(h0, b) : 0ull;
+        if (!ALWAYS_SAME) c1[ALWAYS_SAME ? 0 : i] = same ? 0ull : ((b < NB) ? load_bin(h1, b) : 0ull);
+    }
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+        if (!ALWAYS_SAME && same) c1[ALWAYS_SAME ? 0 : i] = c0[i];
+        if (threadIdx.x * PER + i == 0) {  // ALWAYS_SAME implies z0 == z1
+            c0[i] += z0;
+            if (!ALWAYS_SAME) c1[ALWAYS_SAME ? 0 : i] += z1;
+        }
+        s0 += c0[i];
+        s1 += WT_C1(i);
+    }
+    // fused exclusive block scan of (s0, s1)
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned long long i0 = s0, i1 = s1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        unsigned long long o0 = __shfl_up_sync(0xffffffffu, i0, d), o1 = __shfl_up_sync(0xffffffffu, i1, d);
+        if (lane >= d) { i0 += o0; i1 += o1; }
+    }
+    if (lane == 31) { sh.warp_sums[0][wid] = i0; sh.warp_sums[1][wid] = i1; }
+    __syncthreads();
+    if (wid == 0) {
+        unsigned long long w0 = (lane < T / 32) ? sh.warp_sums[0][lane] : 0ull, w1 = (lane < T / 32) ? sh.warp_sums[1][lane] : 0ull;
+        unsigned long long a0 = w0, a1 = w1;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned long long o0 = __shfl_up_sync(0xffffffffu, a0, d), o1 = __shfl_up_sync(0xffffffffu, a1, d);
+            if (lane >= d) { a0 += o0; a1 += o1; }
+        }
+        if (lane < T / 32) { sh.warp_sums[0][lane] = a0 - w0; sh.warp_sums[1][lane] = a1 - w1; }
+        if (lane == T / 32 - 1) { sh.warp_sums[0][T / 32] = a0; sh.warp_sums[1][T / 32] = a1; }
+    }
+    __syncthreads();
+    const unsigned long long e0 = sh.warp_sums[0][wid] + i0 - s0, e1 = sh.warp_sums[1][wid] + i1 - s1;
+    const unsigned long long tot0 = sh.warp_sums[0][T / 32], tot1 = sh.warp_sums[1][T / 32];
+    if (rank0 >= tot0) rank0 = tot0 ? tot0 - 1 : 0;  // defensive; cannot happen for a consistent plan
+    if (rank1 >= tot1) rank1 = tot1 ? tot1 - 1 : 0;
+    if (s0 > 0 && e0 <= rank0 && rank0 < e0 + s0) {
+        unsigned long long run = e0;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            if (rank0 < run + c0[i]) {
+                const int b = threadIdx.x * PER + i;
+                sh.res_digit[0] = b;
+                sh.res_rem[0] = rank0 - run;
+                sh.res_cnt[0] = c0[i] - (b == 0 ? z0 : 0ull);
+                break;
+            }
+            run += c0[i];
+        }
+    }
+    if (s1 > 0 && e1 <= rank1 && rank1 < e1 + s1) {
+        unsigned long long run = e1;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            if (rank1 < run + WT_C1(i)) {
+                const int b = threadIdx.x * PER + i;
+                sh.res_digit[1] = b;
+                sh.res_rem[1] = rank1 - run;
+                sh.res_cnt[1] = WT_C1(i) - (b == 0 ? z1 : 0ull);
+                break;
+            }
+            run += WT_C1(i);
+        }
+    }
+    __syncthreads();
+    Found f;
+    f.d0 = sh.res_digit[0]; f.d1 = sh.res_digit[1];
+    f.r0 = sh.res_rem[0]; f.r1 = sh.res_rem[1];
+    f.c0 = sh.res_cnt[0]; f.c1 = sh.res_cnt[1];
+    __syncthreads();  // the next call may overwrite the result slots
+    return f;
+#undef WT_C1
+}
+
 template <int PASS>
-__device__ void flush_and_maybe_scan(const WtSelArgs& a, Shared& sh, int j, const WtSelJob& job, int my_tiles,
-                                     unsigned int p0, unsigned int p1, bool two) {
+__device__ __forceinline__ unsigned long long* global_hist(const WtSelArgs& a, int j) {
+    constexpr int NB = PASS == 1 ? WT_SEL_BINS1 : (PASS == 2 ? WT_SEL_BINS2 : WT_SEL_BINS3);
+    return PASS == 1 ? a.hist1 + (size_t)j * NB : (PASS == 2 ? a.hist2 + (size_t)j * 2 * NB : a.hist3 + (size_t)j * 2 * NB);
+}
+
+__device__ __forceinline__ void clear_hist(Shared& sh, int n) {
+    __syncthreads();
+    for (int b = threadIdx.x; b < n; b += T) sh.hist[b] = 0u;
+    __syncthreads();
+}
+
+// add the non-empty bins of the CTA's shared histogram to the job's global histogram
+template <int PASS>
+__device__ __forceinline__ void flush_hist(const WtSelArgs& a, Shared& sh, int j) {
     constexpr int NB = PASS == 1 ? WT_SEL_BINS1 : (PASS == 2 ? WT_SEL_BINS2 : WT_SEL_BINS3);
     constexpr int NBT = PASS == 1 ? NB : 2 * NB;
-    unsigned long long* gh = PASS == 1 ? a.hist1 + (size_t)j * NB
-                                       : (PASS == 2 ? a.hist2 + (size_t)j * 2 * NB : a.hist3 + (size_t)j * 2 * NB);
+    unsigned long long* gh = global_hist<PASS>(a, j);
     __syncthreads();
-    for (int b = threadIdx.x; b < NBT; b += WT_SEL_THREADS) {
+    for (int b = threadIdx.x; b < NBT; b += T) {
         unsigned int v = sh.hist[b];
         if (v) atomicAdd(&gh[b], (unsigned long long)v);
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned int ticket = atomicAdd(&a.done[j * 4 + (PASS - 1)], (unsigned int)my_tiles);
-        sh.is_last = (ticket + (unsigned int)my_tiles == (unsigned int)job.n_tiles);
-    }
-    __syncthreads();
-    if (!sh.is_last) return;
-    __threadfence();
-    // this CTA retired the job's last tile of the pass: locate the digit of both ranks
-    WtSelState* st = &a.state[j];
-    unsigned long long rank0 = PASS == 1 ? (unsigned long long)job.k0 : __ldcg(&st->rem[0]);
-    unsigned long long rank1 = PASS == 1 ? (unsigned long long)job.k1 : __ldcg(&st->rem[1]);
-    unsigned long long z0 = (PASS == 1 || p0 == 0u) ? (unsigned long long)job.zeros : 0ull;
-    unsigned long long z1 = (PASS == 1 || p1 == 0u) ? (unsigned long long)job.zeros : 0ull;
-    scan_find<NB>(gh, z0, rank0, sh.warp_sums, &sh.res_digit[0], &sh.res_rem[0]);
-    scan_find<NB>(two ? gh + NB : gh, z1, rank1, sh.warp_sums, &sh.res_digit[1], &sh.res_rem[1]);
-    if (threadIdx.x == 0) {
-        constexpr int BITS = PASS == 1 ? 12 : (PASS == 2 ? 10 : 9);
-        unsigned int n0 = PASS == 1 ? sh.res_digit[0] : ((p0 << BITS) | sh.res_digit[0]);
-        unsigned int n1 = PASS == 1 ? sh.res_digit[1] : ((p1 << BITS) | sh.res_digit[1]);
-        st->prefix[0] = n0;
-        st->prefix[1] = n1;
-        st->rem[0] = sh.res_rem[0];
-        st->rem[1] = sh.res_rem[1];
-        if (PASS == 3) {
-            float av = __uint_as_float(n0), bv = __uint_as_float(n1);
-            float t = lerp_threshold(av, bv, job.gamma, job.lerp_mode);
-            st->a = av;
-            st->b = bv;
-            st->t = t;
-            a.thresholds[job.layer] = t;
+        if (PASS == 1) {  // a warp covers 32 consecutive fine bins = one coarse bin
+            unsigned int s = v;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+            if ((threadIdx.x & 31) == 0 && s) atomicAdd(&a.hist1c[(size_t)j * WT_SEL_COARSE + (b >> 5)], (unsigned long long)s);
         }
-        __threadfence();
     }
-    __syncthreads();
 }
 
-template <int PASS>
-__device__ void hist_phase(const WtSelArgs& a, Shared& sh, int t_begin, int t_end) {
-    int cur = -1, my_tiles = 0;
-    WtSelJob job;
-    unsigned int p0 = 0, p1 = 0;
-    bool two = false, vec = false;
-    for (int tile = t_begin; tile < t_end; ++tile) {
-        int j = find_job(a.jobs, a.n_jobs, tile);
-        if (j != cur) {
-            if (cur >= 0) flush_and_maybe_scan<PASS>(a, sh, cur, job, my_tiles, p0, p1, two);
-            cur = j;
-            my_tiles = 0;
-            job = a.jobs[j];
-            if (PASS > 1) {
-                p0 = __ldcg(&a.state[j].prefix[0]);
-                p1 = __ldcg(&a.state[j].prefix[1]);
-                two = (p0 != p1);
+
+// Pass-1 lookup through the coarse histogram: warp 0 scans the 128 coarse sums (4 per lane), then warps 0
+// and 1 scan the 32 fine bins of the coarse bin holding rank0 / rank1.  Two dependent L2 round trips and two
+// barriers instead of a block-wide scan of 4096 bins.  Every thread returns the same result.
+__device__ Found scan_find_two_level(const unsigned long long* __restrict__ coarse, const unsigned long long* __restrict__ fine,
+                                     unsigned long long zeros, unsigned long long rank0, unsigned long long rank1, Shared& sh) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (wid == 0) {
+        unsigned long long c[4], s = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) c[i] = __ldcg(&coarse[lane * 4 + i]);
+        if (lane == 0) c[0] += zeros;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s += c[i];
+        unsigned long long inc = s;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        const unsigned long long total = __shfl_sync(0xffffffffu, inc, 31), excl = inc - s;
+        unsigned long long rk[2] = {rank0, rank1};
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            unsigned long long r = rk[q];
+            if (r >= total) r = total ? total - 1 : 0;  // defensive; cannot happen for a consistent plan
+            if (s > 0 && excl <= r && r < excl + s) {
+                unsigned long long run = excl;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (r < run + c[i]) { sh.res_digit[q] = lane * 4 + i; sh.res_rem[q] = r - run; break; }
+                    run += c[i];
+                }
             }
-            vec = ((reinterpret_cast<uintptr_t>(job.x) & 15u) == 0);
-            for (int b = threadIdx.x; b < WT_SEL_BINS1; b += WT_SEL_THREADS) sh.hist[b] = 0u;
-            __syncthreads();
-        }
-        ++my_tiles;
-        long long base = (long long)(tile - job.tile_begin) * WT_SEL_TILE;
-        long long rem = job.n - base;
-        const float* __restrict__ x = job.x + base;
-        if (vec && rem >= WT_SEL_TILE) {
-            const float4* x4 = reinterpret_cast<const float4*>(x);
-            float4 v0 = __ldg(&x4[threadIdx.x]);
-            float4 v1 = __ldg(&x4[threadIdx.x + WT_SEL_THREADS]);
-            bin_one<PASS>(abs_key(v0.x), sh.hist, p0, p1, two);
-            bin_one<PASS>(abs_key(v0.y), sh.hist, p0, p1, two);
-            bin_one<PASS>(abs_key(v0.z), sh.hist, p0, p1, two);
-            bin_one<PASS>(abs_key(v0.w), sh.hist, p0, p1, two);
-            bin_one<PASS>(abs_key(v1.x), sh.hist, p0, p1, two);
-            bin_one<PASS>(abs_key(v1.y), sh.hist, p0, p1, two);
-            bin_one<PASS>(abs_key(v1.z), sh.hist, p0, p1, two);
-            bin_one<PASS>(abs_key(v1.w), sh.hist, p0, p1, two);
-        } else {
-            int cnt = rem < WT_SEL_TILE ? (int)rem : WT_SEL_TILE;
-            for (int i = threadIdx.x; i < cnt; i += WT_SEL_THREADS)
-                bin_one<PASS>(abs_key(__ldg(&x[i])), sh.hist, p0, p1, two);
         }
     }
-    if (cur >= 0) flush_and_maybe_scan<PASS>(a, sh, cur, job, my_tiles, p0, p1, two);
+    __syncthreads();
+    if (wid < 2) {
+        const unsigned int cb = sh.res_digit[wid];
+        const unsigned long long r = sh.res_rem[wid];
+        const int b = (int)cb * 32 + lane;
+        unsigned long long v = __ldcg(&fine[b]);
+        if (b == 0) v += zeros;
+        unsigned long long inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        const unsigned long long excl = inc - v;
+        __syncwarp();  // every lane has read the coarse result before one of them overwrites it
+        if (v > 0 && excl <= r && r < excl + v) {
+            sh.res_digit[wid] = (unsigned int)b;
+            sh.res_rem[wid] = r - excl;
+            sh.res_cnt[wid] = v - (b == 0 ? zeros : 0ull);
+        }
+    }
+    __syncthreads();
+    Found f;
+    f.d0 = sh.res_digit[0]; f.d1 = sh.res_digit[1];
+    f.r0 = sh.res_rem[0]; f.r1 = sh.res_rem[1];
+    f.c0 = sh.res_cnt[0]; f.c1 = sh.res_cnt[1];
+    __syncthreads();  // the next call may overwrite the result slots
+    return f;
 }
 
+// one call of f(j, job, base, len, tiles) per job overlapped by the CTA's tile range [t_begin, t_end)
+template <class F>
+__device__ __forceinline__ void for_each_segment(const WtSelArgs& a, int t_begin, int t_end, F f) {
+    if (t_begin >= t_end) return;
+    int j = find_job(a.jobs, a.n_jobs, t_begin);
+    int tile = t_begin;
+    while (tile < t_end && j < a.n_jobs) {
+        const WtSelJob job = a.jobs[j];
+        if (tile >= job.tile_begin + job.n_tiles) { ++j; continue; }
+        const int seg_end = min(t_end, job.tile_begin + job.n_tiles);
+        const long long base = (long long)(tile - job.tile_begin) * WT_SEL_TILE;
+        long long end = (long long)(seg_end - job.tile_begin) * WT_SEL_TILE;
+        if (end > job.n) end = job.n;
+        f(j, job, base, end - base, seg_end - tile);
+        tile = seg_end;
+        ++j;
+    }
+}
+
+
+// calls op(key) on cand[0..n) (cand 16-byte aligned): uint4 loads from L2, UNROLL of them in flight per thread
+template <class Op>
+__device__ __forceinline__ void cand_for_each(const unsigned int* __restrict__ cand, unsigned int n, Op op) {
+    const unsigned int nvec = n >> 2;
+    const uint4* __restrict__ c4 = reinterpret_cast<const uint4*>(cand);
+    for (unsigned int v = threadIdx.x; v < nvec; v += T * UNROLL) {
+        uint4 r[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u)
+            if (v + u * T < nvec) r[u] = __ldcg(&c4[v + u * T]);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u)
+            if (v + u * T < nvec) { op(r[u].x); op(r[u].y); op(r[u].z); op(r[u].w); }
+    }
+    for (unsigned int i = (nvec << 2) + threadIdx.x; i < n; i += T) op(__ldcg(&cand[i]));
+}
+
+
+// ---- apply: out = |x| < t ? 0 : x, counts -----------------------------------------------------------------
 __device__ __forceinline__ void block_add3(long long* dst, unsigned int zc, unsigned int nzb, unsigned int cnt,
                                            unsigned int* scratch) {
     // scratch: >= 3 * 16 unsigned ints of shared memory
@@ -250,7 +376,7 @@ __device__ __forceinline__ void block_add3(long long* dst, unsigned int zc, unsi
     __syncthreads();
     if (threadIdx.x == 0) {
         unsigned long long z = 0, nb = 0, c = 0;
-        for (int w = 0; w < WT_SEL_THREADS / 32; ++w) { z += scratch[w]; nb += scratch[16 + w]; c += scratch[32 + w]; }
+        for (int w = 0; w < T / 32; ++w) { z += scratch[w]; nb += scratch[16 + w]; c += scratch[32 + w]; }
         atomicAdd(reinterpret_cast<unsigned long long*>(dst + 1), c - z);
         atomicAdd(reinterpret_cast<unsigned long long*>(dst + 2), z);
         atomicAdd(reinterpret_cast<unsigned long long*>(dst + 3), nb);
@@ -265,69 +391,237 @@ __device__ __forceinline__ float apply_one(float v, float t, unsigned int& zc, u
     return o;
 }
 
-__device__ void apply_phase(const WtSelArgs& a, Shared& sh, int t_begin, int t_end) {
-    int cur = -1;
-    WtSelJob job;
-    float t = 0.f;
-    bool vec = false;
-    unsigned int zc = 0, nzb = 0, cnt = 0;
-    for (int tile = t_begin; tile < t_end; ++tile) {
-        int j = find_job(a.jobs, a.n_jobs, tile);
-        if (j != cur) {
-            if (cur >= 0 && job.out) block_add3(a.counts + (size_t)job.layer * 4, zc, nzb, cnt, sh.hist);
-            zc = nzb = cnt = 0;
-            cur = j;
-            job = a.jobs[j];
-            t = __ldcg(&a.state[j].t);
-            vec = (((reinterpret_cast<uintptr_t>(job.x) | reinterpret_cast<uintptr_t>(job.out)) & 15u) == 0);
+
+// moves the staged keys to the job's candidate list (one global atomic per call); call after a barrier
+__device__ void flush_stage(Shared& sh, unsigned int* g_cnt, unsigned int* __restrict__ cand, unsigned int cap) {
+    const unsigned int ns = sh.s_cnt;
+    if (threadIdx.x == 0) sh.s_base = ns ? atomicAdd(g_cnt, ns) : 0u;
+    __syncthreads();
+    const unsigned int gbase = sh.s_base;
+    for (unsigned int i = threadIdx.x; i < ns; i += T)
+        if (gbase + i < cap) cand[gbase + i] = sh.stage[i];
+    __syncthreads();
+    if (threadIdx.x == 0) sh.s_cnt = 0u;
+    __syncthreads();
+}
+
+// P2 over one span: histogram of key bits 18..9 of the keys whose top digit is p0 / p1, and the same keys
+// into the staging buffer
+__device__ void hist2_compact_span(const float* __restrict__ x, long long len, unsigned int p0, unsigned int p1, bool two,
+                                   Shared& sh, unsigned int* g_cnt, unsigned int* __restrict__ cand, unsigned int cap) {
+    unsigned int* h = sh.hist;
+    auto hit = [&](float v) {
+        const unsigned int key = abs_key(v), top = key >> 19;
+        const bool m0 = (top == p0), m1 = two && (top == p1);
+        if (m0 || m1) {
+            atomicAdd(&h[(m0 ? 0u : 1024u) + ((key >> 9) & 1023u)], 1u);
+            sh.stage[atomicAdd(&sh.s_cnt, 1u)] = key;  // < STAGE: flushed whenever more than STAGE_FLUSH are held
         }
-        if (!job.out) continue;
-        if (tile == job.tile_begin && threadIdx.x == 0) a.counts[(size_t)job.layer * 4] = job.n;
-        long long base = (long long)(tile - job.tile_begin) * WT_SEL_TILE;
-        long long rem = job.n - base;
-        const float* __restrict__ x = job.x + base;
-        float* __restrict__ o = job.out + base;
-        if (vec && rem >= WT_SEL_TILE) {
+    };
+    auto maybe_flush = [&]() {  // CTA-uniform decision between two barriers
+        __syncthreads();
+        if (threadIdx.x == 0) sh.s_flag = (sh.s_cnt > STAGE_FLUSH);
+        __syncthreads();
+        if (sh.s_flag) flush_stage(sh, g_cnt, cand, cap);
+    };
+    long long done = 0;
+    if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
+        const long long nvec = len >> 2;
+        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
+        for (long long v0 = 0; v0 < nvec; v0 += (long long)T * UNROLL) {  // CTA-uniform trip count
+            const long long v = v0 + threadIdx.x;
+            float4 r[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u)
+                if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u)
+                if (v + (long long)u * T < nvec) { hit(r[u].x); hit(r[u].y); hit(r[u].z); hit(r[u].w); }
+            maybe_flush();
+        }
+        done = nvec << 2;
+    }
+    for (long long i0 = done; i0 < len; i0 += T) {  // tail, or everything when x is not 16-byte aligned
+        if (i0 + threadIdx.x < len) hit(__ldg(&x[i0 + threadIdx.x]));
+        maybe_flush();
+    }
+}
+
+// ---- P1: histogram of key bits 30..19 ------------------------------------------------------------------
+__device__ void phase1_hist(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        clear_hist(sh, WT_SEL_BINS1);
+        unsigned int* h = sh.hist;
+        acc.begin();
+        span_for_each(job.x + base, len, [h](float v) { atomicAdd(&h[abs_key(v) >> 19], 1u); });
+        acc.end(6);
+        acc.begin();
+        flush_hist<1>(a, sh, j);
+        acc.end(7);
+    });
+}
+
+// ---- P2: digit of both ranks from hist1; histogram of bits 18..9 + compaction of the matching keys ------
+__device__ void phase2_hist_compact(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        WtSelState* st = &a.state[j];
+        acc.begin();
+        const unsigned long long* gh1 = global_hist<1>(a, j);
+        const Found f = scan_find_two_level(a.hist1c + (size_t)j * WT_SEL_COARSE, gh1, (unsigned long long)job.zeros,
+                                            (unsigned long long)job.k0, (unsigned long long)job.k1, sh);
+        acc.end(8);
+        const unsigned int p0 = f.d0, p1 = f.d1;
+        const bool two = (p0 != p1);
+        // compaction only when every key of the one or two selected digits fits the candidate list
+        const unsigned long long ncand = f.c0 + (two ? f.c1 : 0ull);
+        const bool ovf = (job.cand == nullptr) || (ncand > (unsigned long long)job.cand_cap);
+        if (base == 0 && threadIdx.x == 0) {  // the CTA holding the job's first tile publishes for P3
+            st->prefix1[0] = p0; st->prefix1[1] = p1;
+            st->rem1[0] = f.r0; st->rem1[1] = f.r1;
+            st->overflow = ovf ? 1 : 0;
+        }
+        if (threadIdx.x == 0) sh.s_cnt = 0u;
+        clear_hist(sh, 2 * WT_SEL_BINS2);
+        unsigned int* h = sh.hist;
+        acc.begin();
+        if (ovf) {
+            span_for_each(job.x + base, len, [h, p0, p1, two](float v) { bin_one<2>(abs_key(v), h, p0, p1, two); });
+        } else {
+            hist2_compact_span(job.x + base, len, p0, p1, two, sh, &st->cand_count, job.cand, job.cand_cap);
+        }
+        acc.end(9);
+        acc.begin();
+        flush_hist<2>(a, sh, j);
+        if (!ovf) {
+            __syncthreads();
+            flush_stage(sh, &st->cand_count, job.cand, job.cand_cap);
+        }
+        acc.end(10);
+    });
+}
+
+// candidate-list boundary belonging to tile offset t of a job with n_tiles tiles (multiples of 4 keys)
+__device__ __forceinline__ unsigned int cand_boundary(unsigned int n_c, int t, int n_tiles) {
+    if (t >= n_tiles) return n_c;
+    return (unsigned int)(((unsigned long long)n_c * (unsigned long long)t) / (unsigned long long)n_tiles) & ~3u;
+}
+
+// ---- P3: 22-bit prefixes from hist2; histogram of bits 8..0 over the candidate list ----------------------
+__device__ void phase3_hist_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        WtSelState* st = &a.state[j];
+        const unsigned int p0 = __ldcg(&st->prefix1[0]), p1 = __ldcg(&st->prefix1[1]);
+        const unsigned long long r0 = __ldcg(&st->rem1[0]), r1 = __ldcg(&st->rem1[1]);
+        const bool ovf = __ldcg(&st->overflow) != 0;
+        const bool two = (p0 != p1);
+        const unsigned long long zeros = (unsigned long long)job.zeros;
+        acc.begin();
+        const unsigned long long* gh2 = global_hist<2>(a, j);
+        const Found f = scan_find_pair<WT_SEL_BINS2, false>(gh2, two ? gh2 + WT_SEL_BINS2 : gh2, p0 == 0u ? zeros : 0ull,
+                                                     p1 == 0u ? zeros : 0ull, r0, r1, sh);
+        const unsigned int n0 = (p0 << 10) | f.d0, n1 = (p1 << 10) | f.d1;
+        const bool two2 = (n0 != n1);
+        if (base == 0 && threadIdx.x == 0) {
+            st->prefix2[0] = n0; st->prefix2[1] = n1;
+            st->rem2[0] = f.r0; st->rem2[1] = f.r1;
+        }
+        clear_hist(sh, 2 * WT_SEL_BINS3);
+        unsigned int* h = sh.hist;
+        if (ovf) {
+            span_for_each(job.x + base, len, [h, n0, n1, two2](float v) { bin_one<3>(abs_key(v), h, n0, n1, two2); });
+        } else {
+            unsigned int n_c = __ldcg(&st->cand_count);
+            if (n_c > job.cand_cap) n_c = job.cand_cap;  // cannot happen: the overflow test uses exact counts
+            const int t0 = (int)(base / WT_SEL_TILE);
+            const unsigned int lo = cand_boundary(n_c, t0, job.n_tiles), hi = cand_boundary(n_c, t0 + tiles, job.n_tiles);
+            cand_for_each(job.cand + lo, hi - lo, [h, n0, n1, two2](unsigned int k) { bin_one<3>(k, h, n0, n1, two2); });
+        }
+        flush_hist<3>(a, sh, j);
+        acc.end(11);
+    });
+}
+
+// ---- P4: threshold from hist3; apply: out = |x| < t ? 0 : x, counts ----------------------------------------
+__device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        if (!job.out && base != 0) return;  // select-only job: its first-tile CTA publishes, nobody applies
+        WtSelState* st = &a.state[j];
+        const unsigned int n0 = __ldcg(&st->prefix2[0]), n1 = __ldcg(&st->prefix2[1]);
+        const unsigned long long r0 = __ldcg(&st->rem2[0]), r1 = __ldcg(&st->rem2[1]);
+        const bool two2 = (n0 != n1);
+        const unsigned long long zeros = (unsigned long long)job.zeros;
+        acc.begin();
+        const unsigned long long* gh3 = global_hist<3>(a, j);
+        const Found f = scan_find_pair<WT_SEL_BINS3, false>(gh3, two2 ? gh3 + WT_SEL_BINS3 : gh3, n0 == 0u ? zeros : 0ull,
+                                                     n1 == 0u ? zeros : 0ull, r0, r1, sh);
+        const unsigned int key0 = (n0 << 9) | f.d0, key1 = (n1 << 9) | f.d1;
+        const float t = lerp_threshold(__uint_as_float(key0), __uint_as_float(key1), job.gamma, job.lerp_mode);
+        if (base == 0 && threadIdx.x == 0) {
+            st->a = __uint_as_float(key0);
+            st->b = __uint_as_float(key1);
+            st->t = t;
+            a.thresholds[job.layer] = t;
+            if (job.out) a.counts[(size_t)job.layer * 4] = job.n;
+        }
+        acc.end(12);
+        if (!job.out) return;
+        acc.begin();
+        const float* x = job.x + base;  // may alias out (in-place pruning): no __restrict__, no read-only path
+        float* o = job.out + base;
+        unsigned int zc = 0, nzb = 0;
+        long long done = 0;
+        if (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(o)) & 15u) == 0) {
+            const long long nvec = len >> 2;
             const float4* x4 = reinterpret_cast<const float4*>(x);
             float4* o4 = reinterpret_cast<float4*>(o);
-            float4 v0 = x4[threadIdx.x];
-            float4 v1 = x4[threadIdx.x + WT_SEL_THREADS];
-            v0.x = apply_one(v0.x, t, zc, nzb); v0.y = apply_one(v0.y, t, zc, nzb);
-            v0.z = apply_one(v0.z, t, zc, nzb); v0.w = apply_one(v0.w, t, zc, nzb);
-            v1.x = apply_one(v1.x, t, zc, nzb); v1.y = apply_one(v1.y, t, zc, nzb);
-            v1.z = apply_one(v1.z, t, zc, nzb); v1.w = apply_one(v1.w, t, zc, nzb);
-            o4[threadIdx.x] = v0;
-            o4[threadIdx.x + WT_SEL_THREADS] = v1;
-            cnt += 8;
-        } else {
-            int n = rem < WT_SEL_TILE ? (int)rem : WT_SEL_TILE;
-            for (int i = threadIdx.x; i < n; i += WT_SEL_THREADS) {
-                o[i] = apply_one(x[i], t, zc, nzb);
-                ++cnt;
+            for (long long v = threadIdx.x; v < nvec; v += (long long)T * UNROLL) {
+                float4 r[UNROLL];
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+                    if (v + (long long)u * T < nvec) r[u] = __ldcg(&x4[v + (long long)u * T]);
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u) {
+                    if (v + (long long)u * T < nvec) {
+                        r[u].x = apply_one(r[u].x, t, zc, nzb); r[u].y = apply_one(r[u].y, t, zc, nzb);
+                        r[u].z = apply_one(r[u].z, t, zc, nzb); r[u].w = apply_one(r[u].w, t, zc, nzb);
+                        __stcs(&o4[v + (long long)u * T], r[u]);
+                    }
+                }
             }
+            done = nvec << 2;
         }
-    }
-    if (cur >= 0 && job.out) block_add3(a.counts + (size_t)job.layer * 4, zc, nzb, cnt, sh.hist);
+        for (long long i = done + threadIdx.x; i < len; i += T) o[i] = apply_one(x[i], t, zc, nzb);
+        // every element of the span is visited exactly once: thread 0 contributes the span length
+        block_add3(a.counts + (size_t)job.layer * 4, zc, nzb, threadIdx.x == 0 ? (unsigned int)len : 0u, sh.hist);
+        acc.end(13);
+    });
 }
 
-__global__ void __launch_bounds__(WT_SEL_THREADS) wt_select_kernel(WtSelArgs a, int do_apply) {
-    __shared__ Shared sh;
+__global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs a, int do_apply) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Shared& sh = *reinterpret_cast<Shared*>(smem_raw);
     cg::grid_group grid = cg::this_grid();
-    const long long T = a.n_tiles;
-    const int t_begin = (int)((T * blockIdx.x) / gridDim.x);
-    const int t_end = (int)((T * (blockIdx.x + 1)) / gridDim.x);
-    hist_phase<1>(a, sh, t_begin, t_end);
+    const long long NT = a.n_tiles;
+    const int t_begin = (int)((NT * blockIdx.x) / gridDim.x);
+    const int t_end = (int)((NT * (blockIdx.x + 1)) / gridDim.x);
+    Acc acc;
+    acc.slot = a.stamps ? a.stamps + (size_t)blockIdx.x * 16 : nullptr;
+    acc.t0 = 0;
+    acc.stamp(0);
+    phase1_hist(a, sh, t_begin, t_end, acc);
+    acc.stamp(1);
     grid.sync();
-    hist_phase<2>(a, sh, t_begin, t_end);
+    phase2_hist_compact(a, sh, t_begin, t_end, acc);
+    acc.stamp(2);
     grid.sync();
-    hist_phase<3>(a, sh, t_begin, t_end);
-    if (do_apply) {
-        grid.sync();
-        apply_phase(a, sh, t_begin, t_end);
-    }
+    phase3_hist_cand(a, sh, t_begin, t_end, acc);
+    acc.stamp(3);
+    grid.sync();
+    acc.stamp(4);
+    phase4_apply(a, sh, t_begin, t_end, acc);
+    acc.stamp(5);
 }
 
-// out = |x| < t ? 0 : x with t from device (thr_dev) or host; counts4 += {., nonzero, zeros, nonzero_before}
 __global__ void __launch_bounds__(256) wt_apply_threshold_kernel(const float* __restrict__ x, float* __restrict__ out,
                                                                  long long n, const float* thr_dev, float thr_host,
                                                                  long long* counts4) {
@@ -360,8 +654,8 @@ __global__ void __launch_bounds__(256) wt_apply_threshold_kernel(const float* __
 }  // namespace
 
 size_t wt_select_scratch_bytes(int n_jobs) {
-    size_t per = (size_t)WT_SEL_BINS1 * 8 + 2 * (size_t)WT_SEL_BINS2 * 8 + 2 * (size_t)WT_SEL_BINS3 * 8 + 4 * 4 +
-                 sizeof(WtSelState);
+    size_t per = (size_t)WT_SEL_BINS1 * 8 + 2 * (size_t)WT_SEL_BINS2 * 8 + 2 * (size_t)WT_SEL_BINS3 * 8 +
+                 (size_t)WT_SEL_COARSE * 8 + sizeof(WtSelState);
     return per * (size_t)n_jobs + 256;
 }
 
@@ -370,30 +664,34 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
     a->hist1 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * WT_SEL_BINS1 * 8;
     a->hist2 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * 2 * WT_SEL_BINS2 * 8;
     a->hist3 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * 2 * WT_SEL_BINS3 * 8;
-    a->state = reinterpret_cast<WtSelState*>(p); p += (size_t)n_jobs * sizeof(WtSelState);
-    a->done = reinterpret_cast<unsigned int*>(p);
+    a->hist1c = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * WT_SEL_COARSE * 8;
+    a->state = reinterpret_cast<WtSelState*>(p);
+    a->stamps = nullptr;  // tuning aid, set by the plan when WT_SELECT_STAMPS is in the environment
     a->n_jobs = n_jobs;
 }
 
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
-    static int max_blocks_per_sm = 0;
+    static int blocks_per_sm[64] = {0};  // per device; racing threads compute the same value
     WtDeviceInfo di;
     int rc = wt_device_info(&di);
     if (rc) return rc;
     WT_CHECK(di.coop, WT_E_UNSUPPORTED, "device does not support cooperative launch");
-    if (max_blocks_per_sm == 0) {
+    WT_CHECK(di.device >= 0 && di.device < 64, WT_E_UNSUPPORTED, "device ordinal %d out of range", di.device);
+    const size_t smem = sizeof(Shared);
+    if (blocks_per_sm[di.device] == 0) {
+        WT_CUDA(cudaFuncSetAttribute(wt_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int nb = 0;
-        WT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wt_select_kernel, WT_SEL_THREADS, 0));
+        WT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wt_select_kernel, WT_SEL_THREADS, smem));
         WT_CHECK(nb > 0, WT_E_CUDA, "select kernel does not fit on an SM");
-        max_blocks_per_sm = nb;
+        blocks_per_sm[di.device] = nb;
     }
-    int grid = max_blocks_per_sm * di.sm_count;
+    int grid = blocks_per_sm[di.device] * di.sm_count;
     if (grid > args.n_tiles) grid = args.n_tiles;
     if (grid < 1) grid = 1;
     WtSelArgs a = args;
-    int do_apply = a.any_apply;  // jobs without `out` skip their tiles inside the phase
+    int do_apply = a.any_apply;  // jobs without `out` skip the apply loop inside P4
     void* params[] = {&a, &do_apply};
-    WT_CUDA(cudaLaunchCooperativeKernel((const void*)wt_select_kernel, dim3(grid), dim3(WT_SEL_THREADS), params, 0, stream));
+    WT_CUDA(cudaLaunchCooperativeKernel((const void*)wt_select_kernel, dim3(grid), dim3(WT_SEL_THREADS), params, smem, stream));
     return WT_OK;
 }
 
@@ -410,3 +708,4 @@ int wt_apply_threshold_launch(const float* x, float* out, long long n, const flo
     WT_CUDA(cudaGetLastError());
     return WT_OK;
 }
+
