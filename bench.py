@@ -76,6 +76,7 @@ def parse_args():
     ap.add_argument('--replicas', type=int, default=8, help='rotating model replicas per GPU (defeats L2 reuse)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-variants', action='store_true')
+    ap.add_argument('--sharded-workload', default='resnet152_bior2.2_L3_p50_unclamped', choices=sorted(WORKLOADS))
     ap.add_argument('--cpu-sample-seconds', type=float, default=15.0)
     return ap.parse_args()
 
@@ -473,6 +474,8 @@ def run_ours(args):
         'variants': variants,
     }
     del line['config']['model']
+    if not args.no_variants:
+        line['layer_sharded'] = time_layer_sharded(args.sharded_workload, min(args.steps, 100), min(args.warmup, 5), world, dev)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line['cpu_baseline'] = run_cpu_baseline(args.workload, args.cpu_sample_seconds)
     wl.close()
@@ -481,6 +484,59 @@ def run_ours(args):
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
+
+
+def time_layer_sharded(name, steps, warmup, world, dev):
+    """one model, conv layers dealt to the ranks (LPT), each rank prunes its own, ONE all-gather reassembles
+    the pruned weights on every rank (north_star / SURVEY 8(e)); strong scaling, device time, max over ranks"""
+    from wavelettransforms_b200 import _lib, engine, sharded, workloads
+    arch, wavelet, level, pct, clamp = WORKLOADS[name]
+    census = workloads.conv_census(arch)
+    levels = effective_levels(census, wavelet, level, clamp)
+    rank = torch.distributed.get_rank() if world > 1 else 0
+    layout = sharded.ShardLayout([s for _, s in census], world)
+    mine = layout.owned(rank)
+    host = workloads.random_init_weights(census, seed=0)
+    elems = sum(layout.numels)
+    R = 4   # rotating replicas of the OWNED layers (L2 policy as in the main leg)
+    flats, plans = [], []
+    for _ in range(R):
+        flat = torch.zeros(world * layout.shard_elems, dtype=torch.float32, device=dev)
+        xs = [host[i].to(dev) for i in mine]
+        items = [(x.data_ptr(), layout.view(flat, i).data_ptr()) + engine.plane_geometry(x.shape) + (levels[i],)
+                 for x, i in zip(xs, mine)]
+        plans.append((_lib.Plan(items, wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, pct, NUMPY_SEMANTICS), xs))
+        flats.append(flat)
+    stream = int(torch.cuda.current_stream().cuda_stream)
+
+    def step(i, gather):
+        r = i % R
+        if mine:
+            plans[r][0].run(stream)
+        if gather and world > 1:
+            torch.distributed.all_gather_into_tensor(flats[r], flats[r][rank * layout.shard_elems:(rank + 1) * layout.shard_elems])
+
+    out = {}
+    for label, gather in (('prune_only', False), ('prune_allgather', True)):
+        for i in range(warmup):
+            step(i, gather)
+        torch.cuda.synchronize()
+        barrier(world)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            step(warmup + i, gather)
+        e1.record()
+        torch.cuda.synchronize()
+        barrier(world)
+        ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
+        out[label] = {'value': elems * steps / (ms * 1e-3), 'ms_per_step': ms / steps}
+    for p, _ in plans:
+        p.close()
+    out.update(workload=name, scaling='strong', layers=len(census), elems=elems, lpt_balance=layout.balance,
+               allgather_bytes_per_rank=layout.shard_elems * 4 * max(world - 1, 0))
+    return out
 
 
 def load_traffic(kernel):

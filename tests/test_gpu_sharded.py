@@ -1,0 +1,51 @@
+"""GPU twin of tests/test_sharded.py: the layer-sharded path with libwtprune's kernels storing straight into
+the all-gather send buffer.  One GPU => world_size 1 over NCCL (the collective code path still runs); with
+N GPUs the same test can be launched under torchrun."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def pg():
+    created = False
+    if not dist.is_initialized():
+        s = socket.socket()
+        s.bind(('127.0.0.1', 0))
+        port = s.getsockname()[1]
+        s.close()
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        os.environ.setdefault('MASTER_PORT', str(port))
+        torch.cuda.set_device(int(os.environ.get('LOCAL_RANK', '0')))
+        dist.init_process_group('nccl', rank=int(os.environ.get('RANK', '0')), world_size=int(os.environ.get('WORLD_SIZE', '1')))
+        created = True
+    yield dist.group.WORLD
+    if created:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('wavelet,level,clamp', [('bior4.4', 5, True), ('haar', 5, True), ('bior2.2', 3, False)])
+def test_sharded_gpu_matches_reference_flow(wtlib, oracle_lib, pg, wavelet, level, clamp):
+    from oracle import reference_flow as rf
+    from wavelettransforms_b200 import sharded, workloads
+    census = workloads.conv_census('resnet18')[:9]
+    host = workloads.random_init_weights(census, seed=3)
+    dev = torch.device('cuda', torch.cuda.current_device())
+    ws = [w.to(dev) for w in host]
+    pruned, counts, flat, layout = sharded.prune_model_sharded(ws, wavelet, level, 50.0, clamp_level=clamp,
+                                                               numpy_semantics='legacy_1_22', group=pg)
+    torch.cuda.synchronize()
+    for i, w in enumerate(host):
+        want, zeros = rf.multi_resolution_analysis([w], wavelet, level, 50.0, numpy_semantics='legacy_1_22', clamp_level=clamp)
+        assert np.array_equal(pruned[i].cpu().numpy().view(np.uint32), want[0].numpy().view(np.uint32)), census[i][0]
+        assert counts[i, 0] == w.numel() and counts[i, 2] == zeros and counts[i, 1] == w.numel() - zeros
+        assert counts[i, 3] == int(torch.count_nonzero(w))
+    # inputs untouched (multi_resolution_analysis never modifies its input, dwt_pruning.py:84-85)
+    for w, x in zip(host, ws):
+        assert torch.equal(w, x.cpu())

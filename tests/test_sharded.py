@@ -1,0 +1,106 @@
+"""Layer-sharded pruning (wavelettransforms_b200/sharded.py): host logic on CPU with gloo, world_size 2 and 3,
+the oracle's reference flow standing in for the kernels.  The GPU twin is tests/test_gpu_sharded.py."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+SHAPES = [(8, 3, 7, 7), (16, 8, 3, 3), (16, 16, 3, 3), (32, 16, 1, 1), (32, 16, 3, 3), (32, 32, 3, 3), (5, 3, 3, 3)]
+
+
+def _weights():
+    g = torch.Generator().manual_seed(7)
+    return [torch.randn(s, generator=g) * 0.05 for s in SHAPES]
+
+
+def _oracle_fn(wavelet, pct, clamp):
+    from oracle import reference_flow as rf
+
+    def fn(xs, outs, levels):
+        c = np.zeros((len(xs), 4), dtype=np.int64)
+        for i, (x, o, lv) in enumerate(zip(xs, outs, levels)):
+            # per-layer call, the level is already clamped by the caller
+            res, zeros = rf.multi_resolution_analysis([x], wavelet, lv, pct, numpy_semantics='legacy_1_22', clamp_level=False)
+            o.copy_(res[0])
+            c[i] = (x.numel(), x.numel() - zeros, zeros, int(torch.count_nonzero(x)))
+        return c
+    return fn
+
+
+def _worker(rank, world, port, wavelet, level, pct, clamp, out_q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from oracle import reference_flow as rf
+        from wavelettransforms_b200 import sharded
+        ws = _weights()
+        levels = [min(level, rf.calculate_max_level(w.shape, wavelet)) if clamp else level for w in ws]
+        pruned, counts, flat, layout = sharded.prune_sharded(ws, levels, _oracle_fn(wavelet, pct, clamp))
+        out_q.put((rank, [p.clone().numpy() for p in pruned], counts, layout.owner))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world', [2, 3])
+@pytest.mark.parametrize('wavelet,level,clamp', [('haar', 2, True), ('bior2.2', 2, False)])
+def test_sharded_equals_single_process(oracle_lib, world, wavelet, level, clamp):
+    from oracle import reference_flow as rf
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, wavelet, level, 50.0, clamp, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    ws = _weights()
+    want, want_counts = [], []
+    for w in ws:
+        lv = min(level, rf.calculate_max_level(w.shape, wavelet)) if clamp else level
+        res, zeros = rf.multi_resolution_analysis([w], wavelet, lv, 50.0, numpy_semantics='legacy_1_22', clamp_level=False)
+        want.append(res[0].numpy())
+        want_counts.append((w.numel(), w.numel() - zeros, zeros, int(torch.count_nonzero(w))))
+    owners = results[0][3]
+    assert set(owners) == set(range(world))          # every rank got work
+    for rank, pruned, counts, owner in results:
+        assert owner == owners                        # same deterministic assignment on every rank
+        assert np.array_equal(counts, np.array(want_counts, dtype=np.int64))
+        for got, exp in zip(pruned, want):            # every layer present on every rank after the all-gather
+            assert np.array_equal(got.view(np.uint32), exp.view(np.uint32))
+
+
+def test_layout_and_lpt():
+    from wavelettransforms_b200 import sharded, workloads
+    census = workloads.conv_census('resnet18')
+    shapes = [s for _, s in census]
+    for world in (1, 2, 4, 8):
+        lay = sharded.ShardLayout(shapes, world)
+        assert sorted(sum((lay.owned(r) for r in range(world)), [])) == list(range(len(shapes)))
+        # slots of one shard do not overlap and stay inside the shard
+        for r in range(world):
+            spans = sorted((lay.offset[i], lay.offset[i] + lay.numels[i]) for i in lay.owned(r))
+            for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+                assert a1 <= b0
+            assert all(e <= lay.shard_elems for _, e in spans)
+            assert all(s % 64 == 0 for s, _ in spans)
+        assert max(lay.load) >= sum(lay.numels) / world
+    # ResNet-18's largest layer is 21 % of the model => 8-way balance ~0.59
+    lay8 = sharded.ShardLayout(shapes, 8)
+    assert max(lay8.load) == 2359296 and abs(lay8.balance - 0.5917) < 0.01
+    assert workloads.lpt_assignment([5, 5, 4, 3, 3], 2) == [0, 1, 0, 1, 1]
