@@ -214,6 +214,19 @@ struct WtPlan {
     // optional per-phase device timing (wt_plan_set_timing): events[i] is recorded before phase i,
     // events.back() after the last one
     unsigned long long* stamps_dev = nullptr;  // WT_SELECT_STAMPS tuning aid
+    // the small-plane size classes (1x1, 3x3, 7x7 ...) are independent launches: they run concurrently on
+    // auxiliary streams forked from / joined to the caller's stream by events
+    std::vector<cudaStream_t> aux;
+    std::vector<cudaEvent_t> ev_join;
+    cudaEvent_t ev_fork = nullptr;
+
+    // host-I/O plans are a pipeline over groups of layers: child g is a device-I/O plan over the staging
+    // copies of its layers; H2D of group g+1, the kernels of group g and D2H of group g-1 overlap
+    std::vector<WtPlan*> children;
+    std::vector<std::vector<int>> child_layers;  // parent layer index of every child layer
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    std::vector<cudaEvent_t> ev_in, ev_k;
+    cudaEvent_t ev_start = nullptr, ev_done = nullptr;
     int timing = 0;
     std::vector<cudaEvent_t> events;
     std::vector<std::string> phase_names;
@@ -303,10 +316,137 @@ static int upload_tables(WtPlan* P) {
 
 extern "C" int wt_plan_destroy(WtPlan* P) {
     if (!P) return WT_OK;
+    for (WtPlan* c : P->children) wt_plan_destroy(c);
+    for (cudaEvent_t e : P->ev_in) cudaEventDestroy(e);
+    for (cudaEvent_t e : P->ev_k) cudaEventDestroy(e);
+    if (P->ev_start) cudaEventDestroy(P->ev_start);
+    if (P->ev_done) cudaEventDestroy(P->ev_done);
+    if (P->s_in) cudaStreamDestroy(P->s_in);
+    if (P->s_out) cudaStreamDestroy(P->s_out);
     for (cudaEvent_t e : P->events) cudaEventDestroy(e);
+    for (cudaEvent_t e : P->ev_join) cudaEventDestroy(e);
+    if (P->ev_fork) cudaEventDestroy(P->ev_fork);
+    for (cudaStream_t q : P->aux) cudaStreamDestroy(q);
     if (P->stamps_dev) cudaFree(P->stamps_dev);
     if (P->dev) cudaFree(P->dev);
     delete P;
+    return WT_OK;
+}
+
+// ---- host-I/O plans: a copy/compute pipeline over groups of layers ----------------------------------------
+#define WT_PIPE_MAX_GROUPS 16
+
+static int create_host_pipeline(const WtLayerDesc* layers, int n_layers, int wavelet_id, int mode, int threshold_kind,
+                                double threshold_value, int numpy_semantics, WtPlan** plan_out) {
+    WtPlan* P = new WtPlan();
+    int rc = wt_get_bank(wavelet_id, &P->bank);
+    if (rc) { delete P; return rc; }
+    if (cudaGetDevice(&P->device) != cudaSuccess) {
+        delete P;
+        wt_set_error("no usable CUDA device (libwtprune has no CPU fallback): %s", cudaGetErrorString(cudaGetLastError()));
+        return WT_E_CUDA;
+    }
+    P->wavelet_id = wavelet_id; P->mode = mode; P->thr_kind = threshold_kind; P->thr_value = threshold_value;
+    P->sem = numpy_semantics; P->host_io = 1;
+    P->layers.assign(layers, layers + n_layers);
+    P->path.assign(n_layers, PATH_EMPTY);
+    P->d_in.assign(n_layers, nullptr);
+    size_t bytes = 0, total = 0;
+    std::vector<size_t> off(n_layers, 0);
+    std::vector<int> live;
+    for (int i = 0; i < n_layers; ++i) {
+        const WtLayerDesc& L = P->layers[i];
+        if (L.batch < 0 || L.H < 0 || L.W < 0) { delete P; wt_set_error("layer %d: negative shape", i); return WT_E_INVALID; }
+        const long long numel = layer_numel(L);
+        if (numel == 0) continue;
+        if (L.in == nullptr || L.out == nullptr) { delete P; wt_set_error("layer %d: NULL tensor pointer", i); return WT_E_INVALID; }
+        P->path[i] = PATH_LEVEL0;  // "not empty"; the children classify for real
+        off[i] = bytes;
+        bytes = align_up(bytes + (size_t)numel * sizeof(float));
+        total += (size_t)numel * sizeof(float);
+        live.push_back(i);
+    }
+    P->dev_bytes = bytes;
+    cudaError_t e = cudaMalloc((void**)&P->dev, std::max(bytes, (size_t)256));
+    if (e != cudaSuccess) {
+        wt_set_error("cudaMalloc(%zu) failed: %s (libwtprune has no CPU fallback)", bytes, cudaGetErrorString(e));
+        delete P;
+        return WT_E_CUDA;
+    }
+    for (int i : live) P->d_in[i] = reinterpret_cast<float*>(P->dev + off[i]);
+    // contiguous groups of about total / G bytes, in layer order
+    int gmax = WT_PIPE_MAX_GROUPS;
+    if (const char* env = getenv("WT_PIPE_GROUPS")) gmax = std::max(1, atoi(env));
+    const int G = std::max(1, std::min<int>(gmax, (int)live.size()));
+    const size_t target = (total + G - 1) / G;
+    std::vector<std::vector<int>> groups;
+    size_t acc = 0;
+    for (int i : live) {
+        if (groups.empty() || (acc >= target && (int)groups.size() < G)) { groups.emplace_back(); acc = 0; }
+        groups.back().push_back(i);
+        acc += (size_t)layer_numel(P->layers[i]) * sizeof(float);
+    }
+    rc = WT_OK;
+    for (auto& g : groups) {
+        std::vector<WtLayerDesc> d;
+        for (int i : g) {
+            WtLayerDesc c = P->layers[i];
+            c.in = P->d_in[i];
+            c.out = P->d_in[i];  // pruned in place inside the staging copy
+            d.push_back(c);
+        }
+        WtPlan* child = nullptr;
+        rc = wt_plan_create(d.data(), (int)d.size(), wavelet_id, mode, threshold_kind, threshold_value, numpy_semantics, 0, &child);
+        if (rc) break;
+        P->children.push_back(child);
+        P->child_layers.push_back(g);
+    }
+    if (!rc) {
+        bool ok = cudaStreamCreateWithFlags(&P->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&P->s_out, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&P->ev_start, cudaEventDisableTiming) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&P->ev_done, cudaEventDisableTiming) == cudaSuccess;
+        for (size_t g = 0; ok && g < groups.size(); ++g) {
+            cudaEvent_t a, b;
+            ok = cudaEventCreateWithFlags(&a, cudaEventDisableTiming) == cudaSuccess;
+            if (ok) P->ev_in.push_back(a);
+            ok = ok && cudaEventCreateWithFlags(&b, cudaEventDisableTiming) == cudaSuccess;
+            if (ok) P->ev_k.push_back(b);
+        }
+        if (!ok) { wt_set_error("creating the pipeline's streams / events failed: %s", cudaGetErrorString(cudaGetLastError())); rc = WT_E_CUDA; }
+    }
+    if (rc) { wt_plan_destroy(P); return rc; }
+    *plan_out = P;
+    return WT_OK;
+}
+
+// H2D on s_in, kernels on the caller's stream, D2H on s_out; the caller's stream ends ordered after the last D2H
+static int run_host_pipeline(WtPlan* P, cudaStream_t stream) {
+    WT_CUDA(cudaEventRecord(P->ev_start, stream));
+    WT_CUDA(cudaStreamWaitEvent(P->s_in, P->ev_start, 0));
+    WT_CUDA(cudaStreamWaitEvent(P->s_out, P->ev_start, 0));
+    const size_t G = P->children.size();
+    for (size_t g = 0; g < G; ++g) {
+        for (int i : P->child_layers[g])
+            WT_CUDA(cudaMemcpyAsync(P->d_in[i], P->layers[i].in, (size_t)layer_numel(P->layers[i]) * sizeof(float),
+                                    cudaMemcpyHostToDevice, P->s_in));
+        WT_CUDA(cudaEventRecord(P->ev_in[g], P->s_in));
+    }
+    int launches = 0;
+    for (size_t g = 0; g < G; ++g) {
+        WT_CUDA(cudaStreamWaitEvent(stream, P->ev_in[g], 0));
+        int rc = wt_plan_run(P->children[g], stream);
+        if (rc) return rc;
+        launches += P->children[g]->n_launches;
+        WT_CUDA(cudaEventRecord(P->ev_k[g], stream));
+        WT_CUDA(cudaStreamWaitEvent(P->s_out, P->ev_k[g], 0));
+        for (int i : P->child_layers[g])
+            WT_CUDA(cudaMemcpyAsync(P->layers[i].out, P->d_in[i], (size_t)layer_numel(P->layers[i]) * sizeof(float),
+                                    cudaMemcpyDeviceToHost, P->s_out));
+    }
+    WT_CUDA(cudaEventRecord(P->ev_done, P->s_out));
+    WT_CUDA(cudaStreamWaitEvent(stream, P->ev_done, 0));
+    P->n_launches = launches;
     return WT_OK;
 }
 
@@ -324,6 +464,9 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     if (threshold_kind == WT_THRESHOLD_PERCENTILE)
         WT_CHECK(threshold_value >= 0.0 && threshold_value <= 100.0, WT_E_INVALID,
                  "Percentiles must be in the range [0, 100]");
+    if (host_io)
+        return create_host_pipeline(layers, n_layers, wavelet_id, mode, threshold_kind, threshold_value, numpy_semantics,
+                                    plan_out);
     WtPlan* P = new WtPlan();
     int rc = wt_get_bank(wavelet_id, &P->bank);
     if (rc) { delete P; return rc; }
@@ -433,6 +576,18 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
             P->d_out[i] = P->layers[i].out;
         }
     }
+    if (P->small.size() > 1) {
+        bool ok = cudaEventCreateWithFlags(&P->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+        for (size_t k = 1; ok && k < P->small.size(); ++k) {
+            cudaStream_t q;
+            cudaEvent_t ev;
+            ok = cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking) == cudaSuccess;
+            if (ok) P->aux.push_back(q);
+            ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
+            if (ok) P->ev_join.push_back(ev);
+        }
+        if (!ok) { wt_set_error("creating the plan's auxiliary streams failed: %s", cudaGetErrorString(cudaGetLastError())); wt_plan_destroy(P); return WT_E_CUDA; }
+    }
     rc = build_tables(P);
     if (!rc) rc = upload_tables(P);
     if (!rc) {
@@ -444,7 +599,12 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     return WT_OK;
 }
 
-extern "C" size_t wt_plan_device_bytes(const WtPlan* P) { return P ? P->dev_bytes : 0; }
+extern "C" size_t wt_plan_device_bytes(const WtPlan* P) {
+    if (!P) return 0;
+    size_t b = P->dev_bytes;
+    for (const WtPlan* c : P->children) b += c->dev_bytes;
+    return b;
+}
 extern "C" int wt_plan_num_launches(const WtPlan* P) { return P ? P->n_launches : 0; }
 
 extern "C" int wt_plan_set_io(WtPlan* P, const WtLayerDesc* layers, int n_layers) {
@@ -474,6 +634,7 @@ extern "C" int wt_plan_set_io(WtPlan* P, const WtLayerDesc* layers, int n_layers
 extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (P->host_io) return run_host_pipeline(P, stream);
     const int n = (int)P->layers.size();
     int launches = 0;
     P->n_phases = 0;
@@ -505,10 +666,30 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
                                         cudaMemcpyHostToDevice, stream));
     int rc;
     // 1. analysis
-    for (auto& c : P->small) {
+    // size classes fork onto the auxiliary streams (kept serial on the caller's stream while phases are timed)
+    const bool forked = !P->timing && !P->aux.empty();
+    auto fork = [&]() -> int {
+        if (!forked) return WT_OK;
+        WT_CUDA(cudaEventRecord(P->ev_fork, stream));
+        for (cudaStream_t q : P->aux) WT_CUDA(cudaStreamWaitEvent(q, P->ev_fork, 0));
+        return WT_OK;
+    };
+    auto join = [&]() -> int {
+        if (!forked) return WT_OK;
+        for (size_t k = 0; k < P->aux.size(); ++k) {
+            WT_CUDA(cudaEventRecord(P->ev_join[k], P->aux[k]));
+            WT_CUDA(cudaStreamWaitEvent(stream, P->ev_join[k], 0));
+        }
+        return WT_OK;
+    };
+    auto class_stream = [&](size_t k) { return (forked && k > 0) ? P->aux[k - 1] : stream; };
+    if ((rc = fork())) return rc;
+    for (size_t k = 0; k < P->small.size(); ++k) {
+        auto& c = P->small[k];
         snprintf(label, sizeof(label), "small_analysis_%dx%d", c.H, c.W);
         mark(label);
-        rc = wt_small_analysis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev, stream);
+        rc = wt_small_analysis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev,
+                                      class_stream(k));
         if (rc) return rc;
         if (c.n_tiles) ++launches;
     }
@@ -518,6 +699,7 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         rc = wt_generic_analysis(P->bank, P->mode, g, P->counts_dev, stream, &launches);
         if (rc) return rc;
     }
+    if ((rc = join())) return rc;
     // 2. threshold: exact percentile select (+ fused level-0 apply), or plain compare
     if (P->thr_kind == WT_THRESHOLD_PERCENTILE) {
         if (!P->sel_jobs.empty()) {
@@ -536,11 +718,13 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         }
     }
     // 3. synthesis with the threshold applied on load
-    for (auto& c : P->small) {
+    if ((rc = fork())) return rc;
+    for (size_t k = 0; k < P->small.size(); ++k) {
+        auto& c = P->small[k];
         snprintf(label, sizeof(label), "small_synthesis_%dx%d", c.H, c.W);
         mark(label);
         rc = wt_small_synthesis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->thresholds_dev,
-                                       P->counts_dev, stream);
+                                       P->counts_dev, class_stream(k));
         if (rc) return rc;
         if (c.n_tiles) ++launches;
     }
@@ -550,6 +734,7 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         rc = wt_generic_synthesis(P->bank, P->mode, g, P->thresholds_dev, P->counts_dev, stream, &launches);
         if (rc) return rc;
     }
+    if ((rc = join())) return rc;
     if (P->host_io) mark("d2h");
     if (P->host_io)
         for (int i = 0; i < n; ++i)
@@ -589,6 +774,7 @@ extern "C" int wt_plan_phase_times(WtPlan* P, int max_phases, float* ms, int* la
 
 extern "C" int wt_plan_counts_device(WtPlan* P, const int64_t** counts_dev) {
     WT_CHECK(P != nullptr && counts_dev != nullptr, WT_E_INVALID, "NULL argument");
+    WT_CHECK(!P->host_io, WT_E_UNSUPPORTED, "host-I/O plans keep their counts per layer group: use wt_plan_results");
     *counts_dev = reinterpret_cast<const int64_t*>(P->counts_dev);
     return WT_OK;
 }
@@ -597,6 +783,26 @@ extern "C" int wt_plan_results(WtPlan* P, void* stream_, int64_t* counts, int64_
     WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int n = (int)P->layers.size();
+    if (P->host_io) {
+        for (int i = 0; i < n; ++i) {
+            if (counts) { counts[i * 3 + 0] = layer_numel(P->layers[i]); counts[i * 3 + 1] = counts[i * 3 + 2] = 0; }
+            if (nonzero_before) nonzero_before[i] = 0;
+            if (thresholds) thresholds[i] = (P->thr_kind == WT_THRESHOLD_ABSOLUTE) ? (float)P->thr_value : 0.0f;
+        }
+        for (size_t g = 0; g < P->children.size(); ++g) {
+            const std::vector<int>& idx = P->child_layers[g];
+            std::vector<int64_t> c(idx.size() * 3), nb(idx.size());
+            std::vector<float> th(idx.size());
+            int rc = wt_plan_results(P->children[g], stream_, c.data(), nb.data(), th.data());
+            if (rc) return rc;
+            for (size_t k = 0; k < idx.size(); ++k) {
+                if (counts) for (int q = 0; q < 3; ++q) counts[idx[k] * 3 + q] = c[k * 3 + q];
+                if (nonzero_before) nonzero_before[idx[k]] = nb[k];
+                if (thresholds) thresholds[idx[k]] = th[k];
+            }
+        }
+        return WT_OK;
+    }
     std::vector<long long> c4((size_t)n * 4);
     std::vector<float> thr(n);
     if (n) {
