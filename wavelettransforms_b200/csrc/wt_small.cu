@@ -29,8 +29,19 @@ __host__ __device__ constexpr int per_index(int idx, int n) {
     return m == n ? n - 1 : m;
 }
 
+// Compile-time zero-tap masks of a filter bank (bit j set = tap j is exactly 0.0f).  A product with a
+// zero tap is +-0 and the accumulators start at +0.0f and can never become -0.0f (x + (-x) = +0 under
+// round-to-nearest), so skipping those terms leaves every result bit-identical for finite inputs; the
+// launcher derives the masks from the actual taps, so a specialised instantiation is only used when they match.
+template <unsigned DL, unsigned DH, unsigned RL, unsigned RH>
+struct ZeroTaps {
+    static constexpr unsigned dl = DL, dh = DH, rl = RL, rh = RH;
+};
+using NoZeroTaps = ZeroTaps<0, 0, 0, 0>;
+#define WT_TAP(mask, j) ((((mask) >> (j)) & 1u) == 0u)
+
 // single-level 2-D analysis of an H x W plane held in registers (dwt2: axis -2 first, then -1)
-template <int H, int W, int F>
+template <int H, int W, int F, class Z>
 __device__ __forceinline__ void dwt2_regs(const float (&x)[H * W], const WtBank& bk, float (&aa)[half_up(H) * half_up(W)],
                                           float (&da)[half_up(H) * half_up(W)], float (&ad)[half_up(H) * half_up(W)],
                                           float (&dd)[half_up(H) * half_up(W)]) {
@@ -44,8 +55,8 @@ __device__ __forceinline__ void dwt2_regs(const float (&x)[H * W], const WtBank&
 #pragma unroll
             for (int j = 0; j < F; ++j) {
                 const float v = x[per_index(F / 2 + 2 * o - j, H) * W + c];
-                sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
-                sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+                if (WT_TAP(Z::dl, j)) sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
+                if (WT_TAP(Z::dh, j)) sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
             }
             lo[o * W + c] = sl;
             hi[o * W + c] = sh;
@@ -60,10 +71,14 @@ __device__ __forceinline__ void dwt2_regs(const float (&x)[H * W], const WtBank&
             for (int j = 0; j < F; ++j) {
                 const int m = per_index(F / 2 + 2 * o - j, W);
                 const float vl = lo[r * W + m], vh = hi[r * W + m];
-                saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
-                sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
-                sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
-                sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
+                if (WT_TAP(Z::dl, j)) {
+                    saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
+                    sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
+                }
+                if (WT_TAP(Z::dh, j)) {
+                    sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
+                    sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
+                }
             }
             aa[r * W2 + o] = saa;
             ad[r * W2 + o] = sad;
@@ -75,7 +90,7 @@ __device__ __forceinline__ void dwt2_regs(const float (&x)[H * W], const WtBank&
 
 // one output sample of the periodization synthesis of (a, d), coefficient length N, taken from
 // register arrays with element stride S starting at offset OFF (direct accumulation)
-template <int N, int F, int O, int S, int OFF, int LEN>
+template <int N, int F, int O, int S, int OFF, int LEN, class Z>
 __device__ __forceinline__ float idwt_per_sample(const float (&a)[LEN], const float (&d)[LEN], const WtBank& bk) {
     constexpr int start = F / 4;
     constexpr int shift = ((F / 2) % 2 == 0) ? 1 : 0;
@@ -84,52 +99,54 @@ __device__ __forceinline__ float idwt_per_sample(const float (&a)[LEN], const fl
     constexpr int par = q & 1;
     float acc = 0.0f;
 #pragma unroll
-    for (int j = 0; j < F / 2; ++j) acc = __fadd_rn(acc, __fmul_rn(bk.rec_lo[2 * j + par], a[OFF + cpmod(i - j, N) * S]));
+    for (int j = 0; j < F / 2; ++j)
+        if (WT_TAP(Z::rl, 2 * j + par)) acc = __fadd_rn(acc, __fmul_rn(bk.rec_lo[2 * j + par], a[OFF + cpmod(i - j, N) * S]));
 #pragma unroll
-    for (int j = 0; j < F / 2; ++j) acc = __fadd_rn(acc, __fmul_rn(bk.rec_hi[2 * j + par], d[OFF + cpmod(i - j, N) * S]));
+    for (int j = 0; j < F / 2; ++j)
+        if (WT_TAP(Z::rh, 2 * j + par)) acc = __fadd_rn(acc, __fmul_rn(bk.rec_hi[2 * j + par], d[OFF + cpmod(i - j, N) * S]));
     return acc;
 }
 
-template <int H, int W, int F, int R, int C>
+template <int H, int W, int F, int R, int C, class Z>
 struct RowSynth {  // axis -1 pass: lo[r][c], hi[r][c] for r < H2, c < W (row-major, W columns kept)
     static constexpr int H2 = half_up(H), W2 = half_up(W);
     __device__ __forceinline__ static void run(const float (&aa)[H2 * W2], const float (&da)[H2 * W2],
                                                const float (&ad)[H2 * W2], const float (&dd)[H2 * W2], const WtBank& bk,
                                                float (&lo)[H2 * W], float (&hi)[H2 * W]) {
-        lo[R * W + C] = idwt_per_sample<W2, F, C, 1, R * W2, H2 * W2>(aa, ad, bk);
-        hi[R * W + C] = idwt_per_sample<W2, F, C, 1, R * W2, H2 * W2>(da, dd, bk);
-        if constexpr (C + 1 < W) RowSynth<H, W, F, R, C + 1>::run(aa, da, ad, dd, bk, lo, hi);
-        else if constexpr (R + 1 < H2) RowSynth<H, W, F, R + 1, 0>::run(aa, da, ad, dd, bk, lo, hi);
+        lo[R * W + C] = idwt_per_sample<W2, F, C, 1, R * W2, H2 * W2, Z>(aa, ad, bk);
+        hi[R * W + C] = idwt_per_sample<W2, F, C, 1, R * W2, H2 * W2, Z>(da, dd, bk);
+        if constexpr (C + 1 < W) RowSynth<H, W, F, R, C + 1, Z>::run(aa, da, ad, dd, bk, lo, hi);
+        else if constexpr (R + 1 < H2) RowSynth<H, W, F, R + 1, 0, Z>::run(aa, da, ad, dd, bk, lo, hi);
     }
 };
 
-template <int H, int W, int F, int R, int C>
+template <int H, int W, int F, int R, int C, class Z>
 struct ColSynth {  // axis -2 pass: x[r][c] for r < H, c < W
     static constexpr int H2 = half_up(H);
     __device__ __forceinline__ static void run(const float (&lo)[H2 * W], const float (&hi)[H2 * W], const WtBank& bk,
                                                float (&x)[H * W]) {
-        x[R * W + C] = idwt_per_sample<H2, F, R, W, C, H2 * W>(lo, hi, bk);
-        if constexpr (C + 1 < W) ColSynth<H, W, F, R, C + 1>::run(lo, hi, bk, x);
-        else if constexpr (R + 1 < H) ColSynth<H, W, F, R + 1, 0>::run(lo, hi, bk, x);
+        x[R * W + C] = idwt_per_sample<H2, F, R, W, C, H2 * W, Z>(lo, hi, bk);
+        if constexpr (C + 1 < W) ColSynth<H, W, F, R, C + 1, Z>::run(lo, hi, bk, x);
+        else if constexpr (R + 1 < H) ColSynth<H, W, F, R + 1, 0, Z>::run(lo, hi, bk, x);
     }
 };
 
 // single-level 2-D synthesis cropped to H x W (idwt2: axis -1 first, then axis -2)
-template <int H, int W, int F>
+template <int H, int W, int F, class Z>
 __device__ __forceinline__ void idwt2_regs(const float (&aa)[half_up(H) * half_up(W)], const float (&da)[half_up(H) * half_up(W)],
                                            const float (&ad)[half_up(H) * half_up(W)], const float (&dd)[half_up(H) * half_up(W)],
                                            const WtBank& bk, float (&x)[H * W]) {
     constexpr int H2 = half_up(H);
     float lo[H2 * W], hi[H2 * W];
-    RowSynth<H, W, F, 0, 0>::run(aa, da, ad, dd, bk, lo, hi);
-    ColSynth<H, W, F, 0, 0>::run(lo, hi, bk, x);
+    RowSynth<H, W, F, 0, 0, Z>::run(aa, da, ad, dd, bk, lo, hi);
+    ColSynth<H, W, F, 0, 0, Z>::run(lo, hi, bk, x);
 }
 
 // ------------------------------------------------------------------------------------------------
 // multi-level recursion.  Coefficient numbering: level-1 details (da, ad, dd) first, then level 2,
 // ..., finally cA_L; all offsets are compile-time at the depth where the recursion stops.
 // ------------------------------------------------------------------------------------------------
-template <int H, int W, int F, int DEPTH, int BASE>
+template <int H, int W, int F, int DEPTH, int BASE, class Z>
 struct SmallPlane {
     static constexpr int H2 = half_up(H), W2 = half_up(W), NB = H2 * W2;
 
@@ -142,14 +159,14 @@ struct SmallPlane {
         }
         if constexpr (DEPTH > 0) {
             float aa[NB], da[NB], ad[NB], dd[NB];
-            dwt2_regs<H, W, F>(x, bk, aa, da, ad, dd);
+            dwt2_regs<H, W, F, Z>(x, bk, aa, da, ad, dd);
 #pragma unroll
             for (int i = 0; i < NB; ++i) {
                 put(BASE + i, da[i]);
                 put(BASE + NB + i, ad[i]);
                 put(BASE + 2 * NB + i, dd[i]);
             }
-            SmallPlane<H2, W2, F, DEPTH - 1, BASE + 3 * NB>::analyze(aa, level - 1, bk, put);
+            SmallPlane<H2, W2, F, DEPTH - 1, BASE + 3 * NB, Z>::analyze(aa, level - 1, bk, put);
         }
     }
 
@@ -170,8 +187,8 @@ struct SmallPlane {
             }
             // the deeper reconstruction is already cropped to H2 x W2: that is waverec2's
             // "drop the extra approximation sample" rule
-            SmallPlane<H2, W2, F, DEPTH - 1, BASE + 3 * NB>::synthesize(aa, level - 1, bk, get);
-            idwt2_regs<H, W, F>(aa, da, ad, dd, bk, x);
+            SmallPlane<H2, W2, F, DEPTH - 1, BASE + 3 * NB, Z>::synthesize(aa, level - 1, bk, get);
+            idwt2_regs<H, W, F, Z>(aa, da, ad, dd, bk, x);
         }
     }
 };
@@ -254,7 +271,7 @@ __device__ __forceinline__ void stage_out(float* g, const float* s, int cnt) {
 // ------------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------------
-template <int H, int W, int F>
+template <int H, int W, int F, class Z>
 __global__ void __launch_bounds__(WT_SMALL_THREADS)
 wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __restrict__ jobs, int n_jobs,
                          long long* __restrict__ counts) {
@@ -280,7 +297,7 @@ wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __
         float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
         const long long stride = job.batch;
         auto put = [&](int idx, float v) { cbase[(long long)idx * stride] = v; };
-        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0>::analyze(x, job.level, bk, put);
+        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::analyze(x, job.level, bk, put);
     }
     // nonzeros of the input (dwt_pruning_NoEntropy.py:58) and numel
 #pragma unroll
@@ -295,7 +312,7 @@ wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __
     }
 }
 
-template <int H, int W, int F>
+template <int H, int W, int F, class Z>
 __global__ void __launch_bounds__(WT_SMALL_THREADS)
 wt_small_synthesis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __restrict__ jobs, int n_jobs,
                           const float* __restrict__ thresholds, long long* __restrict__ counts) {
@@ -318,7 +335,7 @@ wt_small_synthesis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* _
             const float c = __ldg(&cbase[(long long)idx * stride]);
             return (fabsf(c) < t) ? 0.0f : c;  // np.where(|c| < t, 0, c), strict (dwt_pruning.py:31)
         };
-        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0>::synthesize(x, job.level, bk, get);
+        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::synthesize(x, job.level, bk, get);
 #pragma unroll
         for (int i = 0; i < HW; ++i) {
             s_out[threadIdx.x * HW + i] = x[i];
@@ -339,12 +356,46 @@ wt_small_synthesis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* _
     }
 }
 
+// zero-tap masks of the actual float32 taps
+struct TapMasks {
+    unsigned dl, dh, rl, rh;
+};
+TapMasks tap_masks(const WtBank& b) {
+    TapMasks m = {0, 0, 0, 0};
+    for (int j = 0; j < b.F; ++j) {
+        if (b.dec_lo[j] == 0.0f) m.dl |= 1u << j;
+        if (b.dec_hi[j] == 0.0f) m.dh |= 1u << j;
+        if (b.rec_lo[j] == 0.0f) m.rl |= 1u << j;
+        if (b.rec_hi[j] == 0.0f) m.rh |= 1u << j;
+    }
+    return m;
+}
+
+// (F, masks) of the biorthogonal banks with zero-padded filters: bior1.3, bior2.2, bior4.4, rbio1.3, rbio2.2, rbio4.4
+#define WT_ZERO_TAP_BANKS(X)          \
+    X(6, 0x0, 0x33, 0x33, 0x0)        \
+    X(6, 0x1, 0x31, 0x31, 0x1)        \
+    X(10, 0x1, 0x301, 0x301, 0x1)     \
+    X(6, 0x33, 0x0, 0x0, 0x33)        \
+    X(6, 0x23, 0x20, 0x20, 0x23)      \
+    X(10, 0x203, 0x200, 0x200, 0x203)
+
 template <int H, int W>
 int launch_analysis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, int n_tiles, long long* counts,
                        cudaStream_t stream) {
-#define WT_CASE(FL)                                                                                                  \
-    case FL:                                                                                                         \
-        wt_small_analysis_kernel<H, W, FL><<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts);    \
+    const TapMasks m = tap_masks(bank);
+#define WT_SPEC(FL, DL, DH, RL, RH)                                                                                       \
+    if (bank.F == FL && m.dl == DL && m.dh == DH && m.rl == RL && m.rh == RH) {                                         \
+        wt_small_analysis_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH>>                                                     \
+            <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts);                                       \
+        WT_CUDA(cudaGetLastError());                                                                                     \
+        return WT_OK;                                                                                                    \
+    }
+    WT_ZERO_TAP_BANKS(WT_SPEC)
+#undef WT_SPEC
+#define WT_CASE(FL)                                                                                                       \
+    case FL:                                                                                                              \
+        wt_small_analysis_kernel<H, W, FL, NoZeroTaps><<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts); \
         break;
     switch (bank.F) {
         WT_CASE(2) WT_CASE(4) WT_CASE(6) WT_CASE(8) WT_CASE(10) WT_CASE(12) WT_CASE(18)
@@ -360,10 +411,20 @@ int launch_analysis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, i
 template <int H, int W>
 int launch_synthesis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, int n_tiles, const float* thresholds,
                         long long* counts, cudaStream_t stream) {
-#define WT_CASE(FL)                                                                                                  \
-    case FL:                                                                                                         \
-        wt_small_synthesis_kernel<H, W, FL>                                                                          \
-            <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, thresholds, counts);                      \
+    const TapMasks m = tap_masks(bank);
+#define WT_SPEC(FL, DL, DH, RL, RH)                                                                                       \
+    if (bank.F == FL && m.dl == DL && m.dh == DH && m.rl == RL && m.rh == RH) {                                         \
+        wt_small_synthesis_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH>>                                                    \
+            <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, thresholds, counts);                           \
+        WT_CUDA(cudaGetLastError());                                                                                     \
+        return WT_OK;                                                                                                    \
+    }
+    WT_ZERO_TAP_BANKS(WT_SPEC)
+#undef WT_SPEC
+#define WT_CASE(FL)                                                                                                       \
+    case FL:                                                                                                              \
+        wt_small_synthesis_kernel<H, W, FL, NoZeroTaps>                                                                  \
+            <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, thresholds, counts);                           \
         break;
     switch (bank.F) {
         WT_CASE(2) WT_CASE(4) WT_CASE(6) WT_CASE(8) WT_CASE(10) WT_CASE(12) WT_CASE(18)
