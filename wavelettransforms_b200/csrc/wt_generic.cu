@@ -14,16 +14,26 @@
 namespace {
 
 constexpr int GEN_THREADS = 256;
-constexpr int SMEM_FLOATS = 11000;  // 44 KB of dynamic shared memory per CTA
+constexpr int SMEM_FLOATS = 24000;  // up to 96 KB of dynamic shared memory per CTA (2 CTAs per SM)
+
+// 4-byte asynchronous global -> shared copy (SASS LDGSTS): a thread issues its whole share of a tile
+// back to back and waits once, so the staging loop is not bound by one load latency per element
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ int pmodi(int a, int m) {
     int r = a % m;
     return r < 0 ? r + m : r;
 }
 
-// analysis: index of the boundary-extended signal
-__device__ __forceinline__ int ext_index(int idx, int n, int mode) {
-    if (mode == WT_MODE_PERIODIZATION) {
+// analysis: index of the boundary-extended signal (interior indices take the first branch)
+template <int MODE>
+__device__ __forceinline__ int ext_index(int idx, int n) {
+    if ((unsigned)idx < (unsigned)n) return idx;
+    if (MODE == WT_MODE_PERIODIZATION) {
         int np = n + (n & 1);
         int m = pmodi(idx, np);
         return m == n ? n - 1 : m;
@@ -39,65 +49,88 @@ struct AnaParams {
     int t2r, t2c, tiles_r, tiles_c, pb, ir, ic;
 };
 
+constexpr int NWARP = GEN_THREADS / 32;
+
+// One CTA: all four sub-bands of a t2r x t2c tile for `pb` planes.  Filter length and mode are template
+// constants (taps come straight from the constant bank, loops fully unrolled); warps walk rows, lanes walk
+// columns (no integer division anywhere, shared-memory accesses conflict-free: the axis -2 result is stored
+// with even and odd columns de-interleaved so that the stride-2 reads of the axis -1 pass are unit-stride).
+template <int F, int MODE>
 __global__ void __launch_bounds__(GEN_THREADS)
 wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ AnaParams P) {
     extern __shared__ float smem[];
-    const int F = bk.F;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tile_c = blockIdx.x % P.tiles_c;
     const int tile_r = (blockIdx.x / P.tiles_c) % P.tiles_r;
     const long long pg = blockIdx.x / (P.tiles_c * P.tiles_r);
     const long long p0 = pg * P.pb;
     const int np = (int)min((long long)P.pb, P.batch - p0);
     const int o0 = tile_r * P.t2r, c0 = tile_c * P.t2c;
-    const int base = (P.mode == WT_MODE_PERIODIZATION) ? F / 2 : 1;
+    constexpr int base = (MODE == WT_MODE_PERIODIZATION) ? F / 2 : 1;
     const int r_start = base + 2 * o0 - (F - 1), c_start = base + 2 * c0 - (F - 1);
     const int ir = P.ir, ic = P.ic, t2r = P.t2r, t2c = P.t2c;
-    float* s_in = smem;                          // [pb][ir][ic]
-    float* s_lo = s_in + (size_t)P.pb * ir * ic;  // [pb][t2r][ic]
-    float* s_hi = s_lo + (size_t)P.pb * t2r * ic;
+    const int half = (ic + 1) >> 1, lw = 2 * half;
+    float* s_in = smem;                            // [pb][ir][ic]
+    float* s_lo = s_in + (size_t)P.pb * ir * ic;    // [pb][t2r][lw]: even columns, then odd columns
+    float* s_hi = s_lo + (size_t)P.pb * t2r * lw;
+    const int rows_valid = min(t2r, P.h2 - o0), cols_valid = min(t2c, P.w2 - c0);
 
-    for (int idx = threadIdx.x; idx < np * ir * ic; idx += GEN_THREADS) {
-        const int cc = idx % ic, rr = (idx / ic) % ir, p = idx / (ic * ir);
-        const int sr = ext_index(r_start + rr, P.h, P.mode), sc = ext_index(c_start + cc, P.w, P.mode);
-        s_in[idx] = __ldg(P.in.p + (p0 + p) * P.in.pstride + (long long)sr * P.in.rstride + sc);
+    for (int p = 0; p < np; ++p) {
+        const float* __restrict__ plane = P.in.p + (p0 + p) * P.in.pstride;
+        for (int rr = warp; rr < ir; rr += NWARP) {
+            const float* __restrict__ row = plane + (long long)ext_index<MODE>(r_start + rr, P.h) * P.in.rstride;
+            float* dst = s_in + ((size_t)p * ir + rr) * ic;
+            for (int cc = lane; cc < ic; cc += 32) cp_async4(dst + cc, row + ext_index<MODE>(c_start + cc, P.w));
+        }
     }
+    cp_async_wait_all();
     __syncthreads();
     // axis -2
-    for (int idx = threadIdx.x; idx < np * t2r * ic; idx += GEN_THREADS) {
-        const int cc = idx % ic, ol = (idx / ic) % t2r, p = idx / (ic * t2r);
-        if (o0 + ol >= P.h2) continue;
-        const float* col = s_in + (size_t)p * ir * ic + cc;
-        float sl = 0.0f, sh = 0.0f;
-        for (int j = 0; j < F; ++j) {
-            const float v = col[(2 * ol + F - 1 - j) * ic];
-            sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
-            sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+    for (int p = 0; p < np; ++p) {
+        for (int ol = warp; ol < rows_valid; ol += NWARP) {
+            const float* top = s_in + ((size_t)p * ir + 2 * ol + F - 1) * ic;  // tap j reads row 2*ol + F-1-j
+            float* lo = s_lo + ((size_t)p * t2r + ol) * lw;
+            float* hi = s_hi + ((size_t)p * t2r + ol) * lw;
+            for (int cc = lane; cc < ic; cc += 32) {
+                float sl = 0.0f, sh = 0.0f;
+#pragma unroll
+                for (int j = 0; j < F; ++j) {
+                    const float v = top[cc - j * ic];
+                    sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
+                    sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+                }
+                const int d = (cc & 1) * half + (cc >> 1);
+                lo[d] = sl;
+                hi[d] = sh;
+            }
         }
-        s_lo[idx] = sl;
-        s_hi[idx] = sh;
     }
     __syncthreads();
-    // axis -1
-    for (int idx = threadIdx.x; idx < np * t2r * t2c; idx += GEN_THREADS) {
-        const int cl = idx % t2c, ol = (idx / t2c) % t2r, p = idx / (t2c * t2r);
-        const int o = o0 + ol, c = c0 + cl;
-        if (o >= P.h2 || c >= P.w2) continue;
-        const float* rl = s_lo + ((size_t)p * t2r + ol) * ic;
-        const float* rh = s_hi + ((size_t)p * t2r + ol) * ic;
-        float saa = 0.0f, sad = 0.0f, sda = 0.0f, sdd = 0.0f;
-        for (int j = 0; j < F; ++j) {
-            const int m = 2 * cl + F - 1 - j;
-            const float vl = rl[m], vh = rh[m];
-            saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
-            sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
-            sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
-            sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
-        }
+    // axis -1: column m = 2*cl + F-1-j lives at [(m & 1) * half + (m >> 1)] = [parity_j * half + cl + shift_j]
+    for (int p = 0; p < np; ++p) {
         const long long pl = p0 + p;
-        P.aa.p[pl * P.aa.pstride + (long long)o * P.aa.rstride + c] = saa;
-        P.ad.p[pl * P.ad.pstride + (long long)o * P.ad.rstride + c] = sad;
-        P.da.p[pl * P.da.pstride + (long long)o * P.da.rstride + c] = sda;
-        P.dd.p[pl * P.dd.pstride + (long long)o * P.dd.rstride + c] = sdd;
+        for (int ol = warp; ol < rows_valid; ol += NWARP) {
+            const float* rl = s_lo + ((size_t)p * t2r + ol) * lw;
+            const float* rh = s_hi + ((size_t)p * t2r + ol) * lw;
+            const long long o = o0 + ol;
+            for (int cl = lane; cl < cols_valid; cl += 32) {
+                float saa = 0.0f, sad = 0.0f, sda = 0.0f, sdd = 0.0f;
+#pragma unroll
+                for (int j = 0; j < F; ++j) {
+                    const int idx = ((F - 1 - j) & 1) * half + cl + ((F - 1 - j) >> 1);
+                    const float vl = rl[idx], vh = rh[idx];
+                    saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
+                    sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
+                    sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
+                    sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
+                }
+                const int c = c0 + cl;
+                P.aa.p[pl * P.aa.pstride + o * P.aa.rstride + c] = saa;
+                P.ad.p[pl * P.ad.pstride + o * P.ad.rstride + c] = sad;
+                P.da.p[pl * P.da.pstride + o * P.da.rstride + c] = sda;
+                P.dd.p[pl * P.dd.pstride + o * P.dd.rstride + c] = sdd;
+            }
+        }
     }
 }
 
@@ -113,9 +146,10 @@ struct SynParams {
 };
 
 // virtual coefficient index and tap parity that produce output sample o
-__device__ __forceinline__ void syn_index(int o, int F, int mode, int* iv, int* par) {
-    if (mode == WT_MODE_PERIODIZATION) {
-        const int shift = ((F / 2) % 2 == 0) ? 1 : 0;
+template <int F, int MODE>
+__device__ __forceinline__ void syn_index(int o, int* iv, int* par) {
+    if (MODE == WT_MODE_PERIODIZATION) {
+        constexpr int shift = ((F / 2) % 2 == 0) ? 1 : 0;
         const int q = o - shift;  // >= -1
         *iv = F / 4 + (q >> 1);
         *par = q & 1;
@@ -125,98 +159,130 @@ __device__ __forceinline__ void syn_index(int o, int F, int mode, int* iv, int* 
     }
 }
 
-__device__ __forceinline__ int syn_map(int v, int n, int mode) {
-    if (mode == WT_MODE_PERIODIZATION) return pmodi(v, n);
-    return v < 0 ? 0 : (v >= n ? n - 1 : v);
+template <int MODE>
+__device__ __forceinline__ int syn_map(int v, int n) {
+    if ((unsigned)v < (unsigned)n) return v;
+    if (MODE == WT_MODE_PERIODIZATION) return pmodi(v, n);
+    return v < 0 ? 0 : n - 1;
 }
 
-__device__ __forceinline__ float syn_sample(const float* a, const float* d, int stride, int top, int par, const WtBank& bk,
-                                            int mode) {
-    // a[top - j*stride] is the coefficient paired with tap 2j+par
-    const int hf = bk.F / 2;
-    if (mode == WT_MODE_PERIODIZATION) {
+// a[top - j*stride] is the coefficient paired with tap 2j+par
+template <int F, int MODE>
+__device__ __forceinline__ float syn_sample(const float* a, const float* d, int stride, int top, int par, const WtBank& bk) {
+    constexpr int hf = F / 2;
+    if (MODE == WT_MODE_PERIODIZATION) {  // direct accumulation, lo taps then hi taps
         float acc = 0.0f;
-        for (int j = 0; j < hf; ++j) acc = __fadd_rn(acc, __fmul_rn(bk.rec_lo[2 * j + par], a[top - j * stride]));
-        for (int j = 0; j < hf; ++j) acc = __fadd_rn(acc, __fmul_rn(bk.rec_hi[2 * j + par], d[top - j * stride]));
+#pragma unroll
+        for (int j = 0; j < hf; ++j)
+            acc = __fadd_rn(acc, __fmul_rn(par ? bk.rec_lo[2 * j + 1] : bk.rec_lo[2 * j], a[top - j * stride]));
+#pragma unroll
+        for (int j = 0; j < hf; ++j)
+            acc = __fadd_rn(acc, __fmul_rn(par ? bk.rec_hi[2 * j + 1] : bk.rec_hi[2 * j], d[top - j * stride]));
         return acc;
     }
     float sl = 0.0f, sh = 0.0f;
-    for (int j = 0; j < hf; ++j) sl = __fadd_rn(sl, __fmul_rn(bk.rec_lo[2 * j + par], a[top - j * stride]));
-    for (int j = 0; j < hf; ++j) sh = __fadd_rn(sh, __fmul_rn(bk.rec_hi[2 * j + par], d[top - j * stride]));
+#pragma unroll
+    for (int j = 0; j < hf; ++j) sl = __fadd_rn(sl, __fmul_rn(par ? bk.rec_lo[2 * j + 1] : bk.rec_lo[2 * j], a[top - j * stride]));
+#pragma unroll
+    for (int j = 0; j < hf; ++j) sh = __fadd_rn(sh, __fmul_rn(par ? bk.rec_hi[2 * j + 1] : bk.rec_hi[2 * j], d[top - j * stride]));
     return __fadd_rn(__fadd_rn(0.0f, sl), sh);
 }
 
+// One CTA: a tr x tc tile of the reconstructed plane for `pb` planes (idwt2: axis -1 first, then axis -2), the
+// threshold applied while the four sub-band tiles are staged, crop and zero count fused into the store.
+template <int F, int MODE>
 __global__ void __launch_bounds__(GEN_THREADS)
 wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ SynParams P) {
     extern __shared__ float smem[];
-    const int F = bk.F, hf = F / 2;
+    constexpr int hf = F / 2;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tile_c = blockIdx.x % P.tiles_c;
     const int tile_r = (blockIdx.x / P.tiles_c) % P.tiles_r;
     const long long pg = blockIdx.x / (P.tiles_c * P.tiles_r);
     const long long p0 = pg * P.pb;
     const int np = (int)min((long long)P.pb, P.batch - p0);
     const int R0 = tile_r * P.tr, C0 = tile_c * P.tc;
-    const int cr = P.cr, cc = P.cc, tr = P.tr, tc = P.tc;
+    const int cr = P.cr, cc = P.cc, tc = P.tc;
     int iv0, par0;
-    syn_index(R0, F, P.mode, &iv0, &par0);
+    syn_index<F, MODE>(R0, &iv0, &par0);
     const int row_lo = iv0 - (hf - 1);
-    syn_index(C0, F, P.mode, &iv0, &par0);
+    syn_index<F, MODE>(C0, &iv0, &par0);
     const int col_lo = iv0 - (hf - 1);
     const size_t band = (size_t)P.pb * cr * cc;
     float* s_aa = smem;
     float* s_da = s_aa + band;
     float* s_ad = s_da + band;
     float* s_dd = s_ad + band;
-    float* s_lo = s_dd + band;                       // [pb][cr][tc]
+    float* s_lo = s_dd + band;  // [pb][cr][tc]
     float* s_hi = s_lo + (size_t)P.pb * cr * tc;
     const float t = P.use_thr ? (P.thr_dev ? __ldg(P.thr_dev) : P.thr_host) : 0.0f;
+    const bool thr = P.use_thr != 0, thr_a = thr && P.thr_a != 0;
+    const int rows_valid = min(P.tr, P.oh - R0), cols_valid = min(tc, P.ow - C0);
 
-    for (int idx = threadIdx.x; idx < np * cr * cc; idx += GEN_THREADS) {
-        const int c2 = idx % cc, r2 = (idx / cc) % cr, p = idx / (cc * cr);
-        const int sr = syn_map(row_lo + r2, P.h2, P.mode), sc = syn_map(col_lo + c2, P.w2, P.mode);
+    for (int p = 0; p < np; ++p) {
         const long long pl = p0 + p;
-        float vaa = __ldg(P.aa.p + pl * P.aa.pstride + (long long)sr * P.aa.rstride + sc);
-        float vda = __ldg(P.da.p + pl * P.da.pstride + (long long)sr * P.da.rstride + sc);
-        float vad = __ldg(P.ad.p + pl * P.ad.pstride + (long long)sr * P.ad.rstride + sc);
-        float vdd = __ldg(P.dd.p + pl * P.dd.pstride + (long long)sr * P.dd.rstride + sc);
-        if (P.use_thr) {
-            if (P.thr_a && fabsf(vaa) < t) vaa = 0.0f;
-            if (fabsf(vda) < t) vda = 0.0f;
-            if (fabsf(vad) < t) vad = 0.0f;
-            if (fabsf(vdd) < t) vdd = 0.0f;
+        for (int r2 = warp; r2 < cr; r2 += NWARP) {
+            const long long sr = syn_map<MODE>(row_lo + r2, P.h2);
+            const float* __restrict__ raa = P.aa.p + pl * P.aa.pstride + sr * P.aa.rstride;
+            const float* __restrict__ rda = P.da.p + pl * P.da.pstride + sr * P.da.rstride;
+            const float* __restrict__ rad = P.ad.p + pl * P.ad.pstride + sr * P.ad.rstride;
+            const float* __restrict__ rdd = P.dd.p + pl * P.dd.pstride + sr * P.dd.rstride;
+            const size_t off = ((size_t)p * cr + r2) * cc;
+            for (int c2 = lane; c2 < cc; c2 += 32) {
+                const int sc = syn_map<MODE>(col_lo + c2, P.w2);
+                cp_async4(s_aa + off + c2, raa + sc);
+                cp_async4(s_da + off + c2, rda + sc);
+                cp_async4(s_ad + off + c2, rad + sc);
+                cp_async4(s_dd + off + c2, rdd + sc);
+            }
         }
-        s_aa[idx] = vaa;
-        s_da[idx] = vda;
-        s_ad[idx] = vad;
-        s_dd[idx] = vdd;
+    }
+    cp_async_wait_all();
+    if (thr) {  // np.where(|c| < t, 0, c): every thread sweeps exactly the elements it copied
+        for (int p = 0; p < np; ++p) {
+            for (int r2 = warp; r2 < cr; r2 += NWARP) {
+                const size_t off = ((size_t)p * cr + r2) * cc;
+                for (int c2 = lane; c2 < cc; c2 += 32) {
+                    if (thr_a && fabsf(s_aa[off + c2]) < t) s_aa[off + c2] = 0.0f;
+                    if (fabsf(s_da[off + c2]) < t) s_da[off + c2] = 0.0f;
+                    if (fabsf(s_ad[off + c2]) < t) s_ad[off + c2] = 0.0f;
+                    if (fabsf(s_dd[off + c2]) < t) s_dd[off + c2] = 0.0f;
+                }
+            }
+        }
     }
     __syncthreads();
     // axis -1 first (idwt2)
-    for (int idx = threadIdx.x; idx < np * cr * tc; idx += GEN_THREADS) {
-        const int cl = idx % tc, r2 = (idx / tc) % cr, p = idx / (tc * cr);
-        const int c = C0 + cl;
-        if (c >= P.ow) continue;
-        int iv, par;
-        syn_index(c, F, P.mode, &iv, &par);
-        const int top = iv - col_lo;
-        const size_t rowoff = ((size_t)p * cr + r2) * cc;
-        s_lo[idx] = syn_sample(s_aa + rowoff, s_ad + rowoff, 1, top, par, bk, P.mode);
-        s_hi[idx] = syn_sample(s_da + rowoff, s_dd + rowoff, 1, top, par, bk, P.mode);
+    for (int p = 0; p < np; ++p) {
+        for (int r2 = warp; r2 < cr; r2 += NWARP) {
+            const size_t rowoff = ((size_t)p * cr + r2) * cc;
+            const size_t dst = ((size_t)p * cr + r2) * tc;
+            for (int cl = lane; cl < cols_valid; cl += 32) {
+                int iv, par;
+                syn_index<F, MODE>(C0 + cl, &iv, &par);
+                const int top = iv - col_lo;
+                s_lo[dst + cl] = syn_sample<F, MODE>(s_aa + rowoff, s_ad + rowoff, 1, top, par, bk);
+                s_hi[dst + cl] = syn_sample<F, MODE>(s_da + rowoff, s_dd + rowoff, 1, top, par, bk);
+            }
+        }
     }
     __syncthreads();
     unsigned int zc = 0, wr = 0;
-    for (int idx = threadIdx.x; idx < np * tr * tc; idx += GEN_THREADS) {
-        const int cl = idx % tc, rl = (idx / tc) % tr, p = idx / (tc * tr);
-        const int r = R0 + rl, c = C0 + cl;
-        if (r >= P.oh || c >= P.ow) continue;
-        int iv, par;
-        syn_index(r, F, P.mode, &iv, &par);
-        const int top = iv - row_lo;
-        const size_t off = (size_t)p * cr * tc + cl;
-        const float v = syn_sample(s_lo + off, s_hi + off, tc, top * tc, par, bk, P.mode);
-        P.out.p[(p0 + p) * P.out.pstride + (long long)r * P.out.rstride + c] = v;
-        zc += (v == 0.0f);
-        ++wr;
+    for (int p = 0; p < np; ++p) {
+        float* __restrict__ plane = P.out.p + (p0 + p) * P.out.pstride;
+        for (int rl = warp; rl < rows_valid; rl += NWARP) {
+            int iv, par;
+            syn_index<F, MODE>(R0 + rl, &iv, &par);
+            const int top = (iv - row_lo) * tc;
+            float* __restrict__ orow = plane + (long long)(R0 + rl) * P.out.rstride + C0;
+            const size_t off = (size_t)p * cr * tc;
+            for (int cl = lane; cl < cols_valid; cl += 32) {
+                const float v = syn_sample<F, MODE>(s_lo + off + cl, s_hi + off + cl, tc, top, par, bk);
+                orow[cl] = v;
+                zc += (v == 0.0f);
+                ++wr;
+            }
+        }
     }
     if (P.counts4) {
 #pragma unroll
@@ -224,7 +290,7 @@ wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_cons
             zc += __shfl_down_sync(0xffffffffu, zc, d);
             wr += __shfl_down_sync(0xffffffffu, wr, d);
         }
-        if ((threadIdx.x & 31) == 0) {
+        if (lane == 0 && wr) {
             atomicAdd(reinterpret_cast<unsigned long long*>(P.counts4 + 2), (unsigned long long)zc);
             atomicAdd(reinterpret_cast<unsigned long long*>(P.counts4 + 1), (unsigned long long)(wr - zc));
         }
@@ -243,6 +309,23 @@ __global__ void __launch_bounds__(256) wt_count_nonzero_kernel(const float* __re
 }
 
 }  // namespace
+
+// filter length x mode -> template instantiation; WT_GEN_LAUNCH(F, MODE) is defined at the point of use
+#define WT_GEN_CASE(FL)                                                  \
+    case FL:                                                             \
+        if (mode_ == WT_MODE_PERIODIZATION) WT_GEN_LAUNCH(FL, WT_MODE_PERIODIZATION) \
+        else WT_GEN_LAUNCH(FL, WT_MODE_SYMMETRIC)                        \
+        break;
+#define WT_GEN_DISPATCH(F_, mode__)                                                            \
+    {                                                                                          \
+        const int mode_ = (mode__);                                                            \
+        switch (F_) {                                                                          \
+            WT_GEN_CASE(2) WT_GEN_CASE(4) WT_GEN_CASE(6) WT_GEN_CASE(8) WT_GEN_CASE(10) WT_GEN_CASE(12) WT_GEN_CASE(18) \
+            default:                                                                           \
+                wt_set_error("generic path: unsupported filter length %d", (int)(F_));         \
+                return WT_E_UNSUPPORTED;                                                       \
+        }                                                                                      \
+    }
 
 // ---- host side -----------------------------------------------------------------------------------------
 long long wt_generic_ncoef(int H, int W, int F, int mode, int level) {
@@ -273,13 +356,13 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     P.batch = batch; P.h = h; P.w = w; P.mode = mode;
     P.h2 = wt_dwt_coeff_len(h, bank.F, mode);
     P.w2 = wt_dwt_coeff_len(w, bank.F, mode);
-    P.t2r = std::min(P.h2, 16);
-    P.t2c = std::min(P.w2, 32);
+    P.t2r = std::min(P.h2, 32);
+    P.t2c = std::min(P.w2, 64);
     P.tiles_r = (P.h2 + P.t2r - 1) / P.t2r;
     P.tiles_c = (P.w2 + P.t2c - 1) / P.t2c;
     P.ir = 2 * P.t2r + bank.F - 2;
     P.ic = 2 * P.t2c + bank.F - 2;
-    const long long per_plane = (long long)P.ir * P.ic + 2LL * P.t2r * P.ic;
+    const long long per_plane = (long long)P.ir * P.ic + 2LL * P.t2r * (2 * ((P.ic + 1) / 2));
     long long pb = SMEM_FLOATS / per_plane;
     WT_CHECK(pb >= 1, WT_E_UNSUPPORTED, "generic analysis tile does not fit shared memory");
     pb = std::min(pb, batch);
@@ -290,7 +373,14 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     const long long grid = groups * P.tiles_r * P.tiles_c;
     WT_CHECK(grid < 2147483647LL, WT_E_UNSUPPORTED, "generic analysis grid too large");
     const size_t smem = (size_t)pb * per_plane * sizeof(float);
-    wt_generic_analysis_kernel<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);
+#define WT_GEN_LAUNCH(FL, MD)                                                                                     \
+    {                                                                                                             \
+        auto kern = wt_generic_analysis_kernel<FL, MD>;                                                           \
+        WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
+        kern<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);                                             \
+    }
+    WT_GEN_DISPATCH(bank.F, mode)
+#undef WT_GEN_LAUNCH
     WT_CUDA(cudaGetLastError());
     return WT_OK;
 }
@@ -301,8 +391,8 @@ int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView d
     SynParams P;
     P.aa = aa; P.da = da; P.ad = ad; P.dd = dd; P.out = out;
     P.batch = batch; P.h2 = h2; P.w2 = w2; P.oh = oh; P.ow = ow; P.mode = mode;
-    P.tr = std::min(oh, 32);
-    P.tc = std::min(ow, 64);
+    P.tr = std::min(oh, 64);
+    P.tc = std::min(ow, 128);
     P.tiles_r = (oh + P.tr - 1) / P.tr;
     P.tiles_c = (ow + P.tc - 1) / P.tc;
     P.cr = P.tr / 2 + bank.F / 2 + 2;
@@ -318,7 +408,14 @@ int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView d
     const long long grid = groups * P.tiles_r * P.tiles_c;
     WT_CHECK(grid < 2147483647LL, WT_E_UNSUPPORTED, "generic synthesis grid too large");
     const size_t smem = (size_t)pb * per_plane * sizeof(float);
-    wt_generic_synthesis_kernel<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);
+#define WT_GEN_LAUNCH(FL, MD)                                                                                     \
+    {                                                                                                             \
+        auto kern = wt_generic_synthesis_kernel<FL, MD>;                                                          \
+        WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
+        kern<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);                                             \
+    }
+    WT_GEN_DISPATCH(bank.F, mode)
+#undef WT_GEN_LAUNCH
     WT_CUDA(cudaGetLastError());
     return WT_OK;
 }
