@@ -22,6 +22,10 @@ __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
                  : "memory");
 }
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ int pmodi(int a, int m) {
@@ -47,6 +51,7 @@ struct AnaParams {
     long long batch;
     int h, w, h2, w2, mode;
     int t2r, t2c, tiles_r, tiles_c, pb, ir, ic;
+    int ics;  // staged row width: ic + up to 3 columns so that the staged region starts 16-byte aligned, rounded to 4
 };
 
 constexpr int NWARP = GEN_THREADS / 32;
@@ -68,19 +73,28 @@ wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_const
     const int o0 = tile_r * P.t2r, c0 = tile_c * P.t2c;
     constexpr int base = (MODE == WT_MODE_PERIODIZATION) ? F / 2 : 1;
     const int r_start = base + 2 * o0 - (F - 1), c_start = base + 2 * c0 - (F - 1);
-    const int ir = P.ir, ic = P.ic, t2r = P.t2r, t2c = P.t2c;
+    const int ir = P.ir, ic = P.ic, ics = P.ics, t2r = P.t2r, t2c = P.t2c;
     const int half = (ic + 1) >> 1, lw = 2 * half;
-    float* s_in = smem;                            // [pb][ir][ic]
-    float* s_lo = s_in + (size_t)P.pb * ir * ic;    // [pb][t2r][lw]: even columns, then odd columns
+    const int c_al = (c_start >> 2) << 2;  // floor to a multiple of 4 (arithmetic shift: also for negative starts)
+    const int shift = c_start - c_al;      // logical column cc of the tile lives at staged column cc + shift
+    float* s_in = smem;                             // [pb][ir][ics]
+    float* s_lo = s_in + (size_t)P.pb * ir * ics;    // [pb][t2r][lw]: even columns, then odd columns
     float* s_hi = s_lo + (size_t)P.pb * t2r * lw;
     const int rows_valid = min(t2r, P.h2 - o0), cols_valid = min(t2c, P.w2 - c0);
+    // interior tiles of aligned planes are staged with 16-byte copies
+    const bool vec = c_al >= 0 && c_al + ics <= P.w && (P.in.rstride & 3) == 0 && (P.in.pstride & 3) == 0 &&
+                     (reinterpret_cast<uintptr_t>(P.in.p) & 15u) == 0;
 
     for (int p = 0; p < np; ++p) {
         const float* __restrict__ plane = P.in.p + (p0 + p) * P.in.pstride;
         for (int rr = warp; rr < ir; rr += NWARP) {
             const float* __restrict__ row = plane + (long long)ext_index<MODE>(r_start + rr, P.h) * P.in.rstride;
-            float* dst = s_in + ((size_t)p * ir + rr) * ic;
-            for (int cc = lane; cc < ic; cc += 32) cp_async4(dst + cc, row + ext_index<MODE>(c_start + cc, P.w));
+            float* dst = s_in + ((size_t)p * ir + rr) * ics;
+            if (vec) {
+                for (int v = lane; v < (ics >> 2); v += 32) cp_async16(dst + 4 * v, row + c_al + 4 * v);
+            } else {
+                for (int cc = lane; cc < ics; cc += 32) cp_async4(dst + cc, row + ext_index<MODE>(c_al + cc, P.w));
+            }
         }
     }
     cp_async_wait_all();
@@ -88,14 +102,14 @@ wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_const
     // axis -2
     for (int p = 0; p < np; ++p) {
         for (int ol = warp; ol < rows_valid; ol += NWARP) {
-            const float* top = s_in + ((size_t)p * ir + 2 * ol + F - 1) * ic;  // tap j reads row 2*ol + F-1-j
+            const float* top = s_in + ((size_t)p * ir + 2 * ol + F - 1) * ics + shift;  // tap j reads row 2*ol + F-1-j
             float* lo = s_lo + ((size_t)p * t2r + ol) * lw;
             float* hi = s_hi + ((size_t)p * t2r + ol) * lw;
             for (int cc = lane; cc < ic; cc += 32) {
                 float sl = 0.0f, sh = 0.0f;
 #pragma unroll
                 for (int j = 0; j < F; ++j) {
-                    const float v = top[cc - j * ic];
+                    const float v = top[cc - j * ics];
                     sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
                     sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
                 }
@@ -139,6 +153,7 @@ struct SynParams {
     long long batch;
     int h2, w2, oh, ow, mode;
     int tr, tc, tiles_r, tiles_c, pb, cr, cc;
+    int ccs;  // staged row width of the sub-band tiles (cc + alignment slack, multiple of 4)
     const float* thr_dev;
     float thr_host;
     int use_thr, thr_a;
@@ -202,12 +217,13 @@ wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_cons
     const long long p0 = pg * P.pb;
     const int np = (int)min((long long)P.pb, P.batch - p0);
     const int R0 = tile_r * P.tr, C0 = tile_c * P.tc;
-    const int cr = P.cr, cc = P.cc, tc = P.tc;
+    const int cr = P.cr, cc = P.ccs, tc = P.tc;  // cc: staged row width
     int iv0, par0;
     syn_index<F, MODE>(R0, &iv0, &par0);
     const int row_lo = iv0 - (hf - 1);
     syn_index<F, MODE>(C0, &iv0, &par0);
-    const int col_lo = iv0 - (hf - 1);
+    const int col_lo0 = iv0 - (hf - 1);
+    const int col_lo = (col_lo0 >> 2) << 2;  // staged region starts 16-byte aligned (floor, also for negative starts)
     const size_t band = (size_t)P.pb * cr * cc;
     float* s_aa = smem;
     float* s_da = s_aa + band;
@@ -219,6 +235,11 @@ wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_cons
     const bool thr = P.use_thr != 0, thr_a = thr && P.thr_a != 0;
     const int rows_valid = min(P.tr, P.oh - R0), cols_valid = min(tc, P.ow - C0);
 
+    auto aligned_view = [](const WtView& v) {
+        return (reinterpret_cast<uintptr_t>(v.p) & 15u) == 0 && (v.rstride & 3) == 0 && (v.pstride & 3) == 0;
+    };
+    const bool vec = col_lo >= 0 && col_lo + cc <= P.w2 && aligned_view(P.aa) && aligned_view(P.da) && aligned_view(P.ad) &&
+                     aligned_view(P.dd);
     for (int p = 0; p < np; ++p) {
         const long long pl = p0 + p;
         for (int r2 = warp; r2 < cr; r2 += NWARP) {
@@ -228,6 +249,14 @@ wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_cons
             const float* __restrict__ rad = P.ad.p + pl * P.ad.pstride + sr * P.ad.rstride;
             const float* __restrict__ rdd = P.dd.p + pl * P.dd.pstride + sr * P.dd.rstride;
             const size_t off = ((size_t)p * cr + r2) * cc;
+            if (vec) {
+                for (int v = lane; v < (cc >> 2); v += 32) {
+                    cp_async16(s_aa + off + 4 * v, raa + col_lo + 4 * v);
+                    cp_async16(s_da + off + 4 * v, rda + col_lo + 4 * v);
+                    cp_async16(s_ad + off + 4 * v, rad + col_lo + 4 * v);
+                    cp_async16(s_dd + off + 4 * v, rdd + col_lo + 4 * v);
+                }
+            } else
             for (int c2 = lane; c2 < cc; c2 += 32) {
                 const int sc = syn_map<MODE>(col_lo + c2, P.w2);
                 cp_async4(s_aa + off + c2, raa + sc);
@@ -242,7 +271,8 @@ wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_cons
         for (int p = 0; p < np; ++p) {
             for (int r2 = warp; r2 < cr; r2 += NWARP) {
                 const size_t off = ((size_t)p * cr + r2) * cc;
-                for (int c2 = lane; c2 < cc; c2 += 32) {
+                for (int i = lane; i < (vec ? (cc >> 2) : cc); i += 32)
+                for (int c2 = vec ? 4 * i : i; c2 < (vec ? 4 * i + 4 : i + 1); ++c2) {
                     if (thr_a && fabsf(s_aa[off + c2]) < t) s_aa[off + c2] = 0.0f;
                     if (fabsf(s_da[off + c2]) < t) s_da[off + c2] = 0.0f;
                     if (fabsf(s_ad[off + c2]) < t) s_ad[off + c2] = 0.0f;
@@ -300,8 +330,23 @@ wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_cons
 __global__ void __launch_bounds__(256) wt_count_nonzero_kernel(const float* __restrict__ x, long long n,
                                                                long long* counts4) {
     unsigned int nz = 0;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        nz += (x[i] != 0.0f);
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+    long long done = 0;
+    if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
+        const long long nvec = n >> 2;
+        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
+        for (long long v = tid; v < nvec; v += 4 * nthr) {
+            float4 r[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (v + u * nthr < nvec) r[u] = __ldg(&x4[v + u * nthr]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (v + u * nthr < nvec) nz += (r[u].x != 0.0f) + (r[u].y != 0.0f) + (r[u].z != 0.0f) + (r[u].w != 0.0f);
+        }
+        done = nvec << 2;
+    }
+    for (long long i = done + tid; i < n; i += nthr) nz += (x[i] != 0.0f);
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) nz += __shfl_down_sync(0xffffffffu, nz, d);
     if ((threadIdx.x & 31) == 0 && nz) atomicAdd(reinterpret_cast<unsigned long long*>(counts4 + 3), (unsigned long long)nz);
@@ -358,11 +403,15 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     P.w2 = wt_dwt_coeff_len(w, bank.F, mode);
     P.t2r = std::min(P.h2, 32);
     P.t2c = std::min(P.w2, 64);
+    while ((long long)((P.h2 + P.t2r - 1) / P.t2r) * ((P.w2 + P.t2c - 1) / P.t2c) * batch < 296 && (P.t2r > 4 || P.t2c > 32)) {
+        if (P.t2c > 32 && P.t2c >= 2 * P.t2r) P.t2c /= 2; else if (P.t2r > 4) P.t2r /= 2; else P.t2c /= 2;
+    }
     P.tiles_r = (P.h2 + P.t2r - 1) / P.t2r;
     P.tiles_c = (P.w2 + P.t2c - 1) / P.t2c;
     P.ir = 2 * P.t2r + bank.F - 2;
     P.ic = 2 * P.t2c + bank.F - 2;
-    const long long per_plane = (long long)P.ir * P.ic + 2LL * P.t2r * (2 * ((P.ic + 1) / 2));
+    P.ics = (P.ic + 3 + 3) & ~3;
+    const long long per_plane = (long long)P.ir * P.ics + 2LL * P.t2r * (2 * ((P.ic + 1) / 2));
     long long pb = SMEM_FLOATS / per_plane;
     WT_CHECK(pb >= 1, WT_E_UNSUPPORTED, "generic analysis tile does not fit shared memory");
     pb = std::min(pb, batch);
@@ -395,10 +444,17 @@ int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView d
     P.tc = std::min(ow, 128);
     P.tiles_r = (oh + P.tr - 1) / P.tr;
     P.tiles_c = (ow + P.tc - 1) / P.tc;
+    // small levels: shrink the tile until the grid can fill the GPU (a 512 x 512 level is only 32 big tiles)
+    while ((long long)((oh + P.tr - 1) / P.tr) * ((ow + P.tc - 1) / P.tc) * batch < 296 && (P.tr > 8 || P.tc > 32)) {
+        if (P.tc > 32 && P.tc >= 2 * P.tr) P.tc /= 2; else if (P.tr > 8) P.tr /= 2; else P.tc /= 2;
+    }
+    P.tiles_r = (oh + P.tr - 1) / P.tr;
+    P.tiles_c = (ow + P.tc - 1) / P.tc;
     P.cr = P.tr / 2 + bank.F / 2 + 2;
     P.cc = P.tc / 2 + bank.F / 2 + 2;
+    P.ccs = (P.cc + 3 + 3) & ~3;
     P.thr_dev = thr_dev; P.thr_host = thr_host; P.use_thr = use_thr; P.thr_a = thr_a; P.counts4 = counts4;
-    const long long per_plane = 4LL * P.cr * P.cc + 2LL * P.cr * P.tc;
+    const long long per_plane = 4LL * P.cr * P.ccs + 2LL * P.cr * P.tc;
     long long pb = SMEM_FLOATS / per_plane;
     WT_CHECK(pb >= 1, WT_E_UNSUPPORTED, "generic synthesis tile does not fit shared memory");
     pb = std::min(pb, batch);
