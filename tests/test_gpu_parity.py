@@ -156,3 +156,67 @@ def test_golden_fixture(mods):
         assert zeros == c['zeros'], c['name']
         got = mods['eng'].wavedec2_packed(x.cuda(), c['wavelet'], c['effective_level'], c['mode'])
         assert got.cpu().numpy().tobytes().hex() == c['packed_hex'], c['name']
+
+
+def _level0_case(mods, ws, p, sem='legacy_1_22'):
+    dp, rf = mods['dp'], mods['rf']
+    got, gz = dp.multi_resolution_analysis(ws, 'bior4.4', 5, p, numpy_semantics=sem)
+    want, wz = rf.multi_resolution_analysis(ws, 'bior4.4', 5, p, numpy_semantics=sem)
+    assert gz == wz, (p, gz, wz)
+    for i, (a, b) in enumerate(zip(got, want)):
+        assert_bit_equal(a, b, f'tensor {i} p={p}')
+
+
+def test_select_candidate_paths(mods):
+    """the three routes of wt_select_kernel: short candidate list, staging-buffer flushes inside a span (one digit
+    holding thousands of keys per CTA segment), and overflow (more than n/8 candidates -> P3 re-reads the tensor)"""
+    g = torch.Generator().manual_seed(11)
+    n = 1 << 20
+    base = torch.randn(n, generator=g) * 0.05
+    # (a) dense band: 10 % of the entries inside one 12-bit digit (distinct values), rank inside the band
+    dense = base.clone()
+    idx = torch.randperm(n, generator=g)[: n // 10]
+    dense[idx] = 0.0123 + torch.rand(n // 10, generator=g) * 1e-5
+    q = float((dense.abs() < 0.0123).float().mean() * 100)
+    # (b) overflow: 40 % exact zeros and a percentile that lands inside them, one that lands right after them
+    zeros = base.clone()
+    zeros[torch.randperm(n, generator=g)[: (2 * n) // 5]] = 0.0
+    # (c) rank k0 and k1 in different digits: two well separated groups of equal size
+    two = torch.cat([0.01 + torch.rand(n // 2, generator=g) * 1e-4, 1.0 + torch.rand(n // 2, generator=g)])
+    two = two[torch.randperm(n, generator=g)] * torch.sign(torch.randn(n, generator=g))
+    # (d) heavy ties away from zero
+    ties = base.clone()
+    ties[::3] = 0.03125
+    ties[1::7] = -0.03125
+    tiny = [torch.tensor([0.5]), torch.tensor([-2.0, 1.0]), torch.tensor([0.0, 0.0, 3.0])]
+    for p in (q + 2.0, q + 5.0, 30.0, 40.0, 40.0001, 50.0, 99.9999):
+        _level0_case(mods, [dense.view(1024, 1024), zeros.view(256, 4096), two.view(64, -1), ties.view(-1)] + tiny, p)
+    _level0_case(mods, [dense.view(1024, 1024), two.view(64, -1)], 50.0, sem='nep50_2x')
+
+
+def test_select_many_jobs_unaligned(mods):
+    """many small jobs (several segments per CTA) and storage offsets that break 16-byte alignment"""
+    g = torch.Generator().manual_seed(12)
+    big = torch.randn(300000, generator=g) * 0.02
+    ws = [big[1:100002], big[100003:100003 + 4097], big[150001:150001 + 12291].view(3, 4097)]
+    ws += [torch.randn(s, generator=g) * 0.02 for s in [(3,), (5000,), (8, 8, 1, 1), (16, 16, 1, 1), (33, 7, 1, 1)] * 6]
+    for p in (10.0, 50.0, 90.0):
+        _level0_case(mods, ws, p)
+
+
+def test_select_unaligned_device_pointers(mods):
+    """device tensors whose data pointers are only 4-byte aligned (views at odd offsets): scalar paths of P1/P2/P4"""
+    from wavelettransforms_b200 import _lib
+    eng, rf = mods['eng'], mods['rf']
+    g = torch.Generator().manual_seed(13)
+    big = (torch.randn(400000, generator=g) * 0.02).cuda()
+    xs = [big[1:100002], big[100003:100003 + 4097], big[150001:150001 + 12289]]
+    outs_buf = torch.empty(400000, device='cuda')
+    outs = [outs_buf[3:3 + 100001], outs_buf[100006:100006 + 4097], outs_buf[150002:150002 + 12289]]
+    for p in (25.0, 50.0):
+        res = eng.prune_device_tensors(xs, [0, 0, 0], 'haar', 'periodization', _lib.THRESHOLD_PERCENTILE, p, 'legacy_1_22',
+                                       outs=outs)
+        for x, o, c in zip(xs, res.outputs, res.counts):
+            want, wz = rf.multi_resolution_analysis([x.cpu()], 'bior4.4', 5, p, numpy_semantics='legacy_1_22')
+            assert_bit_equal(o, want[0], 'unaligned')
+            assert int(c[2]) == wz

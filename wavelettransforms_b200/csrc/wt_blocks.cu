@@ -20,14 +20,18 @@ extern "C" int wt_select_abs_f32(const float* x, int64_t n, int64_t implicit_zer
         WT_CUDA(cudaMemsetAsync(ab_out, 0, 2 * sizeof(float), stream));
         return WT_OK;
     }
-    const size_t scr = wt_select_scratch_bytes(1);
+    const size_t scr = (wt_select_scratch_bytes(1) + 255) / 256 * 256;
     const size_t o_job = 0, o_thr = 256, o_cnt = 512, o_scr = 1024;
+    const unsigned int cap = wt_select_cand_cap(n);
+    const size_t o_cand = o_scr + scr;
     char* dev = nullptr;
-    WT_CUDA(cudaMalloc((void**)&dev, o_scr + scr));
+    WT_CUDA(cudaMalloc((void**)&dev, o_cand + (size_t)cap * sizeof(unsigned int)));
     WtSelJob j;
     memset(&j, 0, sizeof(j));
     j.x = x; j.out = nullptr; j.n = n; j.zeros = implicit_zeros; j.k0 = k0; j.k1 = k1; j.gamma = 0.0;
     j.lerp_mode = WT_LERP_NEP50; j.tile_begin = 0;
+    j.cand = reinterpret_cast<unsigned int*>(dev + o_cand);
+    j.cand_cap = cap;
     const long long nt = (n + WT_SEL_TILE - 1) / WT_SEL_TILE;
     int rc = WT_OK;
     if (nt >= 2147483647LL) { wt_set_error("too many tiles"); rc = WT_E_UNSUPPORTED; }
