@@ -474,6 +474,8 @@ def run_ours(args):
         'variants': variants,
     }
     del line['config']['model']
+    if not args.no_variants and world == 1:
+        line['siblings'] = time_siblings(args.steps, dev)
     if not args.no_variants:
         line['layer_sharded'] = time_layer_sharded(args.sharded_workload, min(args.steps, 100), min(args.warmup, 5), world, dev)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -536,6 +538,40 @@ def time_layer_sharded(name, steps, warmup, world, dev):
         p.close()
     out.update(workload=name, scaling='strong', layers=len(census), elems=elems, lpt_balance=layout.balance,
                allgather_bytes_per_rank=layout.shard_elems * 4 * max(world - 1, 0))
+    return out
+
+
+def time_siblings(steps, dev):
+    """BASELINE config 3: the two sibling maskers on ResNet-18 at 50 % (device-resident, in place, every step on a
+    fresh copy of the weights; per-call allocation and the host synchronisation of the entry points included)"""
+    from wavelettransforms_b200 import engine, workloads
+    census = workloads.conv_census('resnet18')
+    host = workloads.random_init_weights(census, seed=0)
+    elems = sum(w.numel() for w in host)
+    n = max(4, min(steps, 32))
+    out = {}
+    for which in ('min_weight', 'random'):
+        copies = [[w.to(dev) for w in host] for _ in range(n + 2)]
+        torch.cuda.synchronize()
+
+        def one(ws):
+            if which == 'min_weight':    # min_weight_pruning.py:66-74 for every layer, one grouped call
+                engine.min_weight_prune_(ws, [int(w.numel() * 0.5) for w in ws])
+            else:                        # random_pruning.py:51-58 per layer (torch.randperm is the RNG)
+                for w in ws:
+                    flat = w.view(-1)
+                    engine.scatter_zero_(flat, torch.randperm(flat.numel(), device=dev)[: flat.numel() // 2])
+        one(copies[0])
+        one(copies[1])
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(n):
+            one(copies[2 + i])
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        out[which] = {'value': elems * n / dt, 'unit': UNIT, 'ms_per_step': dt / n * 1e3, 'steps': n,
+                      'sparsity': 0.5, 'workload': 'resnet18 conv layers, 50 %'}
+        del copies
     return out
 
 

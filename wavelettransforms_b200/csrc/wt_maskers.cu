@@ -185,6 +185,35 @@ __global__ void __launch_bounds__(256) count_kernel(const float* __restrict__ x,
     }
 }
 
+// grow-only device workspace per host thread and device: percentage_min_pruning is called once per model from
+// its own thread (main_pruning.py:191-209), so the entry point neither allocates nor frees on the hot path
+struct Workspace {
+    char* ptr = nullptr;
+    size_t bytes = 0;
+    int device = -1;
+    ~Workspace() { if (ptr) cudaFree(ptr); }  // at thread exit; an error after context teardown is harmless
+};
+thread_local Workspace g_ws;
+
+int workspace(size_t bytes, char** out) {
+    int dev = 0;
+    WT_CUDA(cudaGetDevice(&dev));
+    if (g_ws.ptr == nullptr || g_ws.bytes < bytes || g_ws.device != dev) {
+        if (g_ws.ptr) { cudaFree(g_ws.ptr); g_ws.ptr = nullptr; g_ws.bytes = 0; }
+        const size_t want = bytes + bytes / 4;
+        cudaError_t e = cudaMalloc((void**)&g_ws.ptr, want);
+        if (e != cudaSuccess) {
+            g_ws.ptr = nullptr;
+            wt_set_error("cudaMalloc(%zu) failed: %s (libwtprune has no CPU fallback)", want, cudaGetErrorString(e));
+            return WT_E_CUDA;
+        }
+        g_ws.bytes = want;
+        g_ws.device = dev;
+    }
+    *out = g_ws.ptr;
+    return WT_OK;
+}
+
 int grid_for(long long n, int threads, int per_sm) {
     WtDeviceInfo di;
     if (wt_device_info(&di)) return 1;
@@ -220,6 +249,7 @@ extern "C" int wt_min_weight_prune_f32(float* const* w, const int64_t* n, const 
         s.x = w[i]; s.out = nullptr; s.n = n[i]; s.zeros = 0;
         s.k0 = s.k1 = std::min<long long>(std::max<long long>(k[i] - 1, 0), n[i] - 1);
         s.gamma = 0.0; s.lerp_mode = WT_LERP_NEP50; s.tile_begin = tiles; s.n_tiles = (int)nt; s.layer = (int)sjobs.size();
+        s.cand_cap = wt_select_cand_cap(n[i]);
         tiles += (int)nt;
         jobs.push_back(m);
         sjobs.push_back(s);
@@ -240,16 +270,23 @@ extern "C" int wt_min_weight_prune_f32(float* const* w, const int64_t* n, const 
     const size_t o_tpx = off; off = al(off + (size_t)tiles * sizeof(unsigned long long));
     const size_t o_less = off; off = al(off + (size_t)nj * sizeof(unsigned long long));
     const size_t o_nz = off; off = al(off + (size_t)nj * sizeof(unsigned long long));
+    const size_t zero_end = off;
+    for (int j = 0; j < nj; ++j) {  // candidate lists of the select fast path (not zeroed)
+        const size_t o = off;
+        off = al(off + (size_t)sjobs[j].cand_cap * sizeof(unsigned int));
+        sjobs[j].cand = reinterpret_cast<unsigned int*>(o);  // offset for now, rebased below
+    }
     char* dev = nullptr;
-    WT_CUDA(cudaMalloc((void**)&dev, off));
-    int rc = WT_OK;
+    int rc = workspace(off, &dev);
+    if (rc) return rc;
+    for (int j = 0; j < nj; ++j) sjobs[j].cand = reinterpret_cast<unsigned int*>(dev + reinterpret_cast<size_t>(sjobs[j].cand));
     std::vector<unsigned long long> nz(nj);
     do {
         cudaError_t e;
 #define MW_TRY(x) if ((e = (x)) != cudaSuccess) { wt_set_error("%s failed: %s", #x, cudaGetErrorString(e)); rc = WT_E_CUDA; break; }
         MW_TRY(cudaMemcpyAsync(dev + o_sj, sjobs.data(), nj * sizeof(WtSelJob), cudaMemcpyHostToDevice, stream));
         MW_TRY(cudaMemcpyAsync(dev + o_mj, jobs.data(), nj * sizeof(MwJob), cudaMemcpyHostToDevice, stream));
-        MW_TRY(cudaMemsetAsync(dev + o_zero, 0, off - o_zero, stream));
+        MW_TRY(cudaMemsetAsync(dev + o_zero, 0, zero_end - o_zero, stream));
         WtSelArgs a;
         memset(&a, 0, sizeof(a));
         wt_select_bind(&a, dev + o_scr, nj);
@@ -274,7 +311,6 @@ extern "C" int wt_min_weight_prune_f32(float* const* w, const int64_t* n, const 
         for (int j = 0; j < nj; ++j) nonzero_out[owner[j]] = (int64_t)nz[j];
     } while (0);
     if (rc) cudaStreamSynchronize(stream);
-    cudaFree(dev);
     return rc;
 }
 
