@@ -214,6 +214,7 @@ struct WtPlan {
     // optional per-phase device timing (wt_plan_set_timing): events[i] is recorded before phase i,
     // events.back() after the last one
     unsigned long long* stamps_dev = nullptr;  // WT_SELECT_STAMPS tuning aid
+    int* cta_table_dev = nullptr;              // cost-balanced tile split of the select kernel: [grid + 1] + [grid]
     // the small-plane size classes (1x1, 3x3, 7x7 ...) are independent launches: they run concurrently on
     // auxiliary streams forked from / joined to the caller's stream by events
     std::vector<cudaStream_t> aux;
@@ -306,8 +307,31 @@ static int build_tables(WtPlan* P) {
 }
 
 static int upload_tables(WtPlan* P) {
-    if (!P->sel_jobs.empty())
+    if (!P->sel_jobs.empty()) {
         WT_CUDA(cudaMemcpy(P->sel_jobs_dev, P->sel_jobs.data(), P->sel_jobs.size() * sizeof(WtSelJob), cudaMemcpyHostToDevice));
+        // cost-balanced split of the select's tile space (segments are not free: see WT_SEL_SEGMENT_COST)
+        int grid = 1;
+        int rc = wt_select_grid(P->sel_args.n_tiles, &grid);
+        if (rc) return rc;
+        std::vector<int> table((size_t)2 * grid + 1);
+        wt_select_balance(P->sel_jobs.data(), (int)P->sel_jobs.size(), P->sel_args.n_tiles, grid, table.data(), table.data() + grid + 1);
+        // the table must cover every tile exactly once and name the job of each CTA's first tile
+        bool ok = table[0] == 0 && table[grid] == P->sel_args.n_tiles;
+        for (int c = 0; ok && c < grid; ++c) {
+            ok = table[c] <= table[c + 1];
+            if (ok && table[c] < table[c + 1]) {
+                const WtSelJob& jb = P->sel_jobs[table[grid + 1 + c]];
+                ok = table[c] >= jb.tile_begin && table[c] < jb.tile_begin + jb.n_tiles;
+            }
+        }
+        WT_CHECK(ok, WT_E_CUDA, "internal error: inconsistent select tile split");
+        if (P->cta_table_dev) { cudaFree(P->cta_table_dev); P->cta_table_dev = nullptr; }
+        WT_CUDA(cudaMalloc((void**)&P->cta_table_dev, table.size() * sizeof(int)));
+        WT_CUDA(cudaMemcpy(P->cta_table_dev, table.data(), table.size() * sizeof(int), cudaMemcpyHostToDevice));
+        P->sel_args.cta_tiles = P->cta_table_dev;
+        P->sel_args.cta_job = P->cta_table_dev + grid + 1;
+        P->sel_args.cta_grid = grid;
+    }
     for (auto& c : P->small)
         if (!c.jobs.empty())
             WT_CUDA(cudaMemcpy(c.jobs_dev, c.jobs.data(), c.jobs.size() * sizeof(WtSmallJob), cudaMemcpyHostToDevice));
@@ -328,6 +352,7 @@ extern "C" int wt_plan_destroy(WtPlan* P) {
     if (P->ev_fork) cudaEventDestroy(P->ev_fork);
     for (cudaStream_t q : P->aux) cudaStreamDestroy(q);
     if (P->stamps_dev) cudaFree(P->stamps_dev);
+    if (P->cta_table_dev) cudaFree(P->cta_table_dev);
     if (P->dev) cudaFree(P->dev);
     delete P;
     return WT_OK;

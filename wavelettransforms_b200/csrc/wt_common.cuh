@@ -98,6 +98,9 @@ struct WtSelArgs {
     unsigned long long* hist2;  // [n_jobs][2][BINS2]
     unsigned long long* hist3;  // [n_jobs][2][BINS3]
     unsigned long long* hist1c; // [n_jobs][BINS1 / 32]: coarse sums of hist1 (32 fine bins each)
+    const int* cta_tiles;       // nullable: [cta_grid + 1] first tile of every CTA (cost-balanced split)
+    const int* cta_job;         // nullable: [cta_grid] job of that first tile
+    int cta_grid;               // grid size the two tables were built for
     unsigned long long* stamps; // nullable tuning aid: [grid][16] per-CTA phase stamps / accumulated ns
     float* thresholds;          // [n_layers]
     long long* counts;          // [n_layers][4] {numel, nonzero, zeros, nonzero_before}
@@ -117,6 +120,12 @@ size_t wt_select_scratch_bytes(int n_jobs);  // hist1+hist2+hist3+done+state, co
 // lays out args over a zeroed scratch block
 void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
+// grid wt_select_launch will use for n_tiles tiles on the current device
+int wt_select_grid(int n_tiles, int* grid_out);
+// cost-balanced contiguous split of the tile space over `grid` CTAs: every segment (piece of one job inside one
+// CTA) costs WT_SEL_SEGMENT_COST tiles on top of its tiles.  tiles_out[grid + 1], job_out[grid] (HOST)
+#define WT_SEL_SEGMENT_COST 2
+void wt_select_balance(const WtSelJob* jobs, int n_jobs, int n_tiles, int grid, int* tiles_out, int* job_out);
 #define WT_SEL_STAMP_CTAS 2048
 
 // ---- level-0 apply for absolute thresholds and generic elementwise helpers (wt_select.cu) --------

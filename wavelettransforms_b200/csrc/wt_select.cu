@@ -118,14 +118,11 @@ constexpr unsigned int STAGE = STAGE_FLUSH + T * UNROLL * 4;      // one more it
 
 struct Shared {
     unsigned int hist[WT_SEL_BINS1];
-    unsigned int stage[STAGE];  // P2: candidate keys on their way to the job's global list
+    unsigned int stage[STAGE];  // P2: candidate keys on their way to the job's global list, one slice per warp
     unsigned long long warp_sums[2][T / 32 + 1];
     unsigned long long res_rem[2];
     unsigned long long res_cnt[2];
     unsigned int res_digit[2];
-    unsigned int s_cnt;   // keys in the staging buffer
-    unsigned int s_base;  // where they go in the global candidate list
-    int s_flag;
 };
 
 
@@ -326,7 +323,7 @@ __device__ Found scan_find_two_level(const unsigned long long* __restrict__ coar
 template <class F>
 __device__ __forceinline__ void for_each_segment(const WtSelArgs& a, int t_begin, int t_end, F f) {
     if (t_begin >= t_end) return;
-    int j = find_job(a.jobs, a.n_jobs, t_begin);
+    int j = (a.cta_job && a.cta_grid == (int)gridDim.x) ? __ldg(&a.cta_job[blockIdx.x]) : find_job(a.jobs, a.n_jobs, t_begin);
     int tile = t_begin;
     while (tile < t_end && j < a.n_jobs) {
         const WtSelJob job = a.jobs[j];
@@ -392,37 +389,39 @@ __device__ __forceinline__ float apply_one(float v, float t, unsigned int& zc, u
 }
 
 
-// moves the staged keys to the job's candidate list (one global atomic per call); call after a barrier
-__device__ void flush_stage(Shared& sh, unsigned int* g_cnt, unsigned int* __restrict__ cand, unsigned int cap) {
-    const unsigned int ns = sh.s_cnt;
-    if (threadIdx.x == 0) sh.s_base = ns ? atomicAdd(g_cnt, ns) : 0u;
-    __syncthreads();
-    const unsigned int gbase = sh.s_base;
-    for (unsigned int i = threadIdx.x; i < ns; i += T)
-        if (gbase + i < cap) cand[gbase + i] = sh.stage[i];
-    __syncthreads();
-    if (threadIdx.x == 0) sh.s_cnt = 0u;
-    __syncthreads();
+// P2 over one span: histogram of key bits 18..9 of the keys whose top digit is p0 / p1, and the same keys into
+// the job's candidate list.  Staging is WARP-private (a slice of sh.stage per warp, fill level in a register,
+// positions from a warp prefix sum), so the loop has no CTA barrier and warps overlap each other's load latency;
+// a warp moves its slice to the global list (one global atomic) whenever it holds more than WSTAGE_FLUSH keys.
+constexpr unsigned int WSTAGE_FLUSH = STAGE_FLUSH / (T / 32);
+constexpr unsigned int WSTAGE = STAGE / (T / 32);  // = WSTAGE_FLUSH + 32 * UNROLL * 4: one more iteration always fits
+
+__device__ __forceinline__ void warp_flush(const unsigned int* wbuf, unsigned int& wcount, unsigned int* g_cnt,
+                                           unsigned int* __restrict__ cand, unsigned int cap) {
+    const int lane = threadIdx.x & 31;
+    unsigned int gbase = 0;
+    if (lane == 0) gbase = atomicAdd(g_cnt, wcount);
+    gbase = __shfl_sync(0xffffffffu, gbase, 0);
+    __syncwarp();
+    for (unsigned int i = lane; i < wcount; i += 32)
+        if (gbase + i < cap) cand[gbase + i] = wbuf[i];
+    __syncwarp();
+    wcount = 0;
 }
 
-// P2 over one span: histogram of key bits 18..9 of the keys whose top digit is p0 / p1, and the same keys
-// into the staging buffer
 __device__ void hist2_compact_span(const float* __restrict__ x, long long len, unsigned int p0, unsigned int p1, bool two,
                                    Shared& sh, unsigned int* g_cnt, unsigned int* __restrict__ cand, unsigned int cap) {
     unsigned int* h = sh.hist;
-    auto hit = [&](float v) {
-        const unsigned int key = abs_key(v), top = key >> 19;
-        const bool m0 = (top == p0), m1 = two && (top == p1);
-        if (m0 || m1) {
-            atomicAdd(&h[(m0 ? 0u : 1024u) + ((key >> 9) & 1023u)], 1u);
-            sh.stage[atomicAdd(&sh.s_cnt, 1u)] = key;  // < STAGE: flushed whenever more than STAGE_FLUSH are held
-        }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned int* wbuf = sh.stage + wid * WSTAGE;
+    unsigned int wcount = 0;  // warp-uniform
+    auto matches = [&](unsigned int key) {
+        const unsigned int top = key >> 19;
+        return top == p0 || (two && top == p1);
     };
-    auto maybe_flush = [&]() {  // CTA-uniform decision between two barriers
-        __syncthreads();
-        if (threadIdx.x == 0) sh.s_flag = (sh.s_cnt > STAGE_FLUSH);
-        __syncthreads();
-        if (sh.s_flag) flush_stage(sh, g_cnt, cand, cap);
+    auto keep = [&](unsigned int key, unsigned int pos) {
+        atomicAdd(&h[((key >> 19) == p0 ? 0u : 1024u) + ((key >> 9) & 1023u)], 1u);
+        wbuf[pos] = key;
     };
     long long done = 0;
     if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
@@ -430,21 +429,52 @@ __device__ void hist2_compact_span(const float* __restrict__ x, long long len, u
         const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
         for (long long v0 = 0; v0 < nvec; v0 += (long long)T * UNROLL) {  // CTA-uniform trip count
             const long long v = v0 + threadIdx.x;
+            unsigned int key[UNROLL * 4];
+            unsigned int hitmask = 0;
             float4 r[UNROLL];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u)
                 if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u)
-                if (v + (long long)u * T < nvec) { hit(r[u].x); hit(r[u].y); hit(r[u].z); hit(r[u].w); }
-            maybe_flush();
+            for (int u = 0; u < UNROLL; ++u) {
+                const bool ok = v + (long long)u * T < nvec;
+                key[u * 4 + 0] = abs_key(r[u].x); key[u * 4 + 1] = abs_key(r[u].y);
+                key[u * 4 + 2] = abs_key(r[u].z); key[u * 4 + 3] = abs_key(r[u].w);
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (ok && matches(key[u * 4 + c])) hitmask |= 1u << (u * 4 + c);
+            }
+            const unsigned int nh = __popc(hitmask);
+            unsigned int inc = nh;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            const unsigned int total = __shfl_sync(0xffffffffu, inc, 31);
+            if (total) {  // warp-uniform
+                unsigned int pos = wcount + inc - nh;
+#pragma unroll
+                for (int e = 0; e < UNROLL * 4; ++e)
+                    if (hitmask & (1u << e)) keep(key[e], pos++);
+                wcount += total;
+                if (wcount > WSTAGE_FLUSH) warp_flush(wbuf, wcount, g_cnt, cand, cap);
+            }
         }
         done = nvec << 2;
     }
     for (long long i0 = done; i0 < len; i0 += T) {  // tail, or everything when x is not 16-byte aligned
-        if (i0 + threadIdx.x < len) hit(__ldg(&x[i0 + threadIdx.x]));
-        maybe_flush();
+        const bool ok = i0 + threadIdx.x < len;
+        const unsigned int key = ok ? abs_key(__ldg(&x[i0 + threadIdx.x])) : 0u;
+        const bool hit = ok && matches(key);
+        const unsigned int ballot = __ballot_sync(0xffffffffu, hit);
+        if (ballot) {
+            if (hit) keep(key, wcount + __popc(ballot & ((1u << lane) - 1u)));
+            wcount += __popc(ballot);
+            if (wcount > WSTAGE_FLUSH) warp_flush(wbuf, wcount, g_cnt, cand, cap);
+        }
     }
+    if (wcount) warp_flush(wbuf, wcount, g_cnt, cand, cap);
 }
 
 // ---- P1: histogram of key bits 30..19 ------------------------------------------------------------------
@@ -480,7 +510,6 @@ __device__ void phase2_hist_compact(const WtSelArgs& a, Shared& sh, int t_begin,
             st->rem1[0] = f.r0; st->rem1[1] = f.r1;
             st->overflow = ovf ? 1 : 0;
         }
-        if (threadIdx.x == 0) sh.s_cnt = 0u;
         clear_hist(sh, 2 * WT_SEL_BINS2);
         unsigned int* h = sh.hist;
         acc.begin();
@@ -492,10 +521,6 @@ __device__ void phase2_hist_compact(const WtSelArgs& a, Shared& sh, int t_begin,
         acc.end(9);
         acc.begin();
         flush_hist<2>(a, sh, j);
-        if (!ovf) {
-            __syncthreads();
-            flush_stage(sh, &st->cand_count, job.cand, job.cand_cap);
-        }
         acc.end(10);
     });
 }
@@ -602,8 +627,14 @@ __global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs 
     Shared& sh = *reinterpret_cast<Shared*>(smem_raw);
     cg::grid_group grid = cg::this_grid();
     const long long NT = a.n_tiles;
-    const int t_begin = (int)((NT * blockIdx.x) / gridDim.x);
-    const int t_end = (int)((NT * (blockIdx.x + 1)) / gridDim.x);
+    int t_begin, t_end;
+    if (a.cta_tiles && a.cta_grid == (int)gridDim.x) {  // cost-balanced split built by the plan
+        t_begin = __ldg(&a.cta_tiles[blockIdx.x]);
+        t_end = __ldg(&a.cta_tiles[blockIdx.x + 1]);
+    } else {
+        t_begin = (int)((NT * blockIdx.x) / gridDim.x);
+        t_end = (int)((NT * (blockIdx.x + 1)) / gridDim.x);
+    }
     Acc acc;
     acc.slot = a.stamps ? a.stamps + (size_t)blockIdx.x * 16 : nullptr;
     acc.t0 = 0;
@@ -667,27 +698,77 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
     a->hist1c = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * WT_SEL_COARSE * 8;
     a->state = reinterpret_cast<WtSelState*>(p);
     a->stamps = nullptr;  // tuning aid, set by the plan when WT_SELECT_STAMPS is in the environment
+    a->cta_tiles = nullptr;
+    a->cta_job = nullptr;
+    a->cta_grid = 0;
     a->n_jobs = n_jobs;
 }
 
-int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
+static int select_blocks_per_sm(const WtDeviceInfo& di, int* nb_out) {
     static int blocks_per_sm[64] = {0};  // per device; racing threads compute the same value
-    WtDeviceInfo di;
-    int rc = wt_device_info(&di);
-    if (rc) return rc;
     WT_CHECK(di.coop, WT_E_UNSUPPORTED, "device does not support cooperative launch");
     WT_CHECK(di.device >= 0 && di.device < 64, WT_E_UNSUPPORTED, "device ordinal %d out of range", di.device);
-    const size_t smem = sizeof(Shared);
     if (blocks_per_sm[di.device] == 0) {
-        WT_CUDA(cudaFuncSetAttribute(wt_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WT_CUDA(cudaFuncSetAttribute(wt_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Shared)));
         int nb = 0;
-        WT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wt_select_kernel, WT_SEL_THREADS, smem));
+        WT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wt_select_kernel, WT_SEL_THREADS, sizeof(Shared)));
         WT_CHECK(nb > 0, WT_E_CUDA, "select kernel does not fit on an SM");
         blocks_per_sm[di.device] = nb;
     }
-    int grid = blocks_per_sm[di.device] * di.sm_count;
-    if (grid > args.n_tiles) grid = args.n_tiles;
+    *nb_out = blocks_per_sm[di.device];
+    return WT_OK;
+}
+
+int wt_select_grid(int n_tiles, int* grid_out) {
+    WtDeviceInfo di;
+    int rc = wt_device_info(&di);
+    if (rc) return rc;
+    int nb = 0;
+    if ((rc = select_blocks_per_sm(di, &nb))) return rc;
+    int grid = nb * di.sm_count;
+    if (grid > n_tiles) grid = n_tiles;
     if (grid < 1) grid = 1;
+    *grid_out = grid;
+    return WT_OK;
+}
+
+void wt_select_balance(const WtSelJob* jobs, int n_jobs, int n_tiles, int grid, int* tiles_out, int* job_out) {
+    // total cost with one segment per job, then cut greedily; a cut inside a job adds one more segment
+    long long total = (long long)n_tiles + (long long)WT_SEL_SEGMENT_COST * n_jobs;
+    int cta = 0, j = 0;
+    long long acc = 0, spent = 0;
+    tiles_out[0] = 0;
+    job_out[0] = 0;
+    for (int tile = 0; tile < n_tiles; ++tile) {
+        while (j + 1 < n_jobs && tile >= jobs[j].tile_begin + jobs[j].n_tiles) ++j;
+        const bool new_seg = (tile == tiles_out[cta]) || (tile == jobs[j].tile_begin);
+        acc += 1 + (new_seg ? WT_SEL_SEGMENT_COST : 0);
+        // target for the CTAs still to fill, from the cost still to place
+        const int left_ctas = grid - cta;
+        const long long remaining = total - spent;
+        const long long target = (remaining + left_ctas - 1) / left_ctas;
+        const int tiles_left = n_tiles - (tile + 1);
+        if (cta + 1 < grid && (acc >= target || tiles_left <= (grid - cta - 1))) {
+            if (tiles_left == 0) break;
+            spent += acc;
+            acc = 0;
+            ++cta;
+            tiles_out[cta] = tile + 1;
+            int jn = j;
+            while (jn + 1 < n_jobs && tile + 1 >= jobs[jn].tile_begin + jobs[jn].n_tiles) ++jn;
+            job_out[cta] = jn;
+            if (tile + 1 != jobs[jn].tile_begin) total += WT_SEL_SEGMENT_COST;  // the cut split a job
+        }
+    }
+    for (int c = cta + 1; c <= grid; ++c) tiles_out[c] = n_tiles;  // unused CTAs get empty ranges
+    for (int c = cta + 1; c < grid; ++c) job_out[c] = n_jobs > 0 ? n_jobs - 1 : 0;
+}
+
+int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
+    int grid = 1;
+    int rc = wt_select_grid(args.n_tiles, &grid);
+    if (rc) return rc;
+    const size_t smem = sizeof(Shared);
     WtSelArgs a = args;
     int do_apply = a.any_apply;  // jobs without `out` skip the apply loop inside P4
     void* params[] = {&a, &do_apply};
