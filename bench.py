@@ -58,11 +58,14 @@ WORKLOADS = {
     # deepest real transform the clamped reference ever runs: haar, 3x3 -> L1, 7x7 -> L2
     'resnet18_haar_L5_p50_clamped': ('resnet18', 'haar', 5, 50.0, True),
     'resnet18_bior2.2_L3_p50_unclamped': ('resnet18', 'bior2.2', 3, 50.0, False),
+    # BASELINE.json configs[0]: the reference's own CPU-runnable case (dec_len 6 => clamps to level 0)
+    'resnet18_bior1.3_L1_p50_clamped': ('resnet18', 'bior1.3', 1, 50.0, True),
     'resnet50_bior2.2_L3_p50_unclamped': ('resnet50', 'bior2.2', 3, 50.0, False),
     'resnet152_bior2.2_L3_p50_unclamped': ('resnet152', 'bior2.2', 3, 50.0, False),
 }
 DEFAULT_WORKLOAD = 'resnet18_bior4.4_L5_p50_unclamped'
-VARIANTS = ['resnet18_bior4.4_L5_p50_clamped', 'resnet18_haar_L5_p50_clamped']
+VARIANTS = ['resnet18_bior4.4_L5_p50_clamped', 'resnet18_haar_L5_p50_clamped', 'resnet18_bior2.2_L3_p50_unclamped',
+            'resnet18_bior1.3_L1_p50_clamped']
 NUMPY_SEMANTICS = 'legacy_1_22'  # the reference's pin (requirements.txt:2)
 
 
