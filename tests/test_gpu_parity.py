@@ -220,3 +220,102 @@ def test_select_unaligned_device_pointers(mods):
             want, wz = rf.multi_resolution_analysis([x.cpu()], 'bior4.4', 5, p, numpy_semantics='legacy_1_22')
             assert_bit_equal(o, want[0], 'unaligned')
             assert int(c[2]) == wz
+
+
+def _sample_windows(n, shift):
+    """boolean mask of the elements S0 of the sampled select path reads (wt_select.cu sample_span)"""
+    idx = torch.arange(n)
+    tile = idx >> 12
+    win = (tile * 5 + 3) & ((1 << shift) - 1)
+    return ((idx & 4095) >> (12 - shift)) == win
+
+
+@pytest.fixture
+def sampled_path(monkeypatch):
+    """launches below 40 Mi keys take the radix path by default: force the sampled one (read at every launch)"""
+    monkeypatch.setenv('WT_SELECT_PATH', 'sampled')
+
+
+def test_select_sampled_path_adversarial(mods, sampled_path):
+    """tensors above 128 Ki keys are SAMPLED to guess where the rank lives; the counts of the full pass decide.
+    (a) a sample that lies -- the sampled windows hold values 1000x smaller than the rest -- must hand the job to
+    the radix path and stay exact; (b) the honest large cases across all sample rates; (c) ranks at the extremes"""
+    g = torch.Generator().manual_seed(21)
+    n = 1 << 21
+    x = torch.randn(n, generator=g) * 0.05
+    lie = x.clone()
+    m = _sample_windows(n, 4)
+    lie[m] = lie[m] * 1e-3
+    half = x.clone()
+    half[_sample_windows(n, 4) & (torch.arange(n) % 2 == 0)] *= 1e-2     # a sample that is only biased
+    sizes = [(1 << 17) - 1, 1 << 17, (1 << 18) + 5, (1 << 19) + 4096, (1 << 20) - 3]     # sample_shift 0..4
+    honest = [torch.randn(s, generator=g) * 0.02 for s in sizes]
+    sorted_t = torch.sort(torch.randn(1 << 20, generator=g)).values                    # structure inside the tensor
+    for p in (0.0, 0.001, 10.0, 50.0, 90.0, 99.999, 100.0):
+        _level0_case(mods, [lie.view(-1), half.view(-1), sorted_t.view(-1), lie.view(2048, 1024)] + honest, p)
+    _level0_case(mods, [lie.view(-1)] + honest, 37.5, sem='nep50_2x')
+
+
+def test_select_sampled_path_unaligned_and_zeros(mods, sampled_path):
+    """sampled path on 4-byte aligned storage (scalar window loads) and with implicit zeros shifting the ranks"""
+    eng = mods['eng']
+    g = torch.Generator().manual_seed(22)
+    n = (1 << 20) + 12345
+    big = (torch.randn(n + 8, generator=g) * 0.02).cuda()
+    for off in (0, 1, 3):
+        x = big[off:off + n]
+        s = torch.sort(x.abs()).values.cpu()
+        for z in (0, 1000, n // 3):
+            for k0 in (0, z, z + n // 2, z + n - 2, z + n - 1):
+                k1 = min(k0 + 1, z + n - 1)
+                a, b = eng.select_abs(x, k0, k1, implicit_zeros=z)
+                wa = 0.0 if k0 < z else s[k0 - z].item()
+                wb = 0.0 if k1 < z else s[k1 - z].item()
+                assert (a, b) == (wa, wb), (off, z, k0)
+
+
+@pytest.mark.parametrize('path', ['radix', 'sampled'])
+def test_select_forced_path_subprocess(path):
+    """WT_SELECT_PATH forces one select path for a whole process: every workload shape, same bits as the oracle
+    (coefficient jobs with implicit zeros, exact-zero ties, level-0 apply)"""
+    import subprocess
+    import sys
+    code = r'''
+import sys, numpy as np, torch
+sys.path.insert(0, %r)
+import oracle
+oracle.build()
+from oracle import reference_flow as rf
+from wavelettransforms_b200 import dwt_pruning as dp
+g = torch.Generator().manual_seed(23)
+ws = [torch.randn(s, generator=g) * 0.05 for s in [(256, 128, 3, 3), (1 << 20,), (64, 3, 7, 7), (5,)]]
+ws[1][::2] = 0.0
+for wavelet, level in (('bior4.4', 5), ('haar', 1)):
+    for p in (10.0, 50.0, 90.0):
+        got, gz = dp.multi_resolution_analysis(ws, wavelet, level, p)
+        want, wz = rf.multi_resolution_analysis(ws, wavelet, level, p, numpy_semantics='legacy_1_22')
+        assert gz == wz, (wavelet, p, gz, wz)
+        for a, b in zip(got, want):
+            assert np.array_equal(a.cpu().numpy().view(np.uint32), b.cpu().numpy().view(np.uint32)), (wavelet, p)
+print('forced path ok')
+''' % ROOT
+    env = dict(os.environ, WT_SELECT_PATH=path)
+    r = subprocess.run([sys.executable, '-c', code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and 'forced path ok' in r.stdout, r.stdout + r.stderr
+
+
+def test_select_default_path_at_scale(mods):
+    """44 Mi keys in one launch: the size where the select takes the sampled path on its own (wt_select_path);
+    order statistics against torch.sort on the device, at ranks across the distribution and inside exact-zero ties"""
+    eng = mods['eng']
+    n = 44 << 20
+    g = torch.Generator(device='cuda').manual_seed(31)
+    x = torch.randn(n, device='cuda', generator=g) * 0.02
+    x[::9] = 0.0
+    s = torch.sort(x.abs()).values
+    for k0 in (0, n // 9 - 1, n // 9 + 1, n // 9 + 2, n // 4, n // 2, n - 2, n - 1):
+        k1 = min(k0 + 1, n - 1)
+        a, b = eng.select_abs(x, k0, k1)
+        assert (a, b) == (s[k0].item(), s[k1].item()), k0
+    del s
+    torch.cuda.empty_cache()

@@ -291,6 +291,7 @@ static int build_tables(WtPlan* P) {
             j.lerp_mode = (P->sem == WT_NUMPY_LEGACY_1_22) ? WT_LERP_LEGACY : WT_LERP_NEP50;
             j.cand = P->d_cand[i];
             j.cand_cap = P->cand_cap[i];
+            j.sample_shift = wt_select_sample_shift(j.n);
             j.tile_begin = sel_tiles;
             const long long nt = (j.n + WT_SEL_TILE - 1) / WT_SEL_TILE;
             WT_CHECK(sel_tiles + nt < 2147483647LL, WT_E_UNSUPPORTED, "too many select tiles");
@@ -845,14 +846,27 @@ extern "C" int wt_plan_results(WtPlan* P, void* stream_, int64_t* counts, int64_
         double mx[16] = {0}, sum[16] = {0};
         for (int c = 0; c < g; ++c)
             for (int k = 0; k < 16; ++k) {
-                double v = (k < 6) ? (double)(st[c * 16 + k] - t0) * 1e-3 : (double)st[c * 16 + k] * 1e-3;
+                double v = (k < 7) ? (double)(st[c * 16 + k] - t0) * 1e-3 : (double)st[c * 16 + k] * 1e-3;
+                if (k < 7 && st[c * 16 + k] == 0) v = 0;  // phase not run (radix-only path)
                 mx[k] = std::max(mx[k], v);
                 sum[k] += v / g;
             }
-        fprintf(stderr, "[wt select %d CTAs, us, mean/max] endP1 %.1f/%.1f endP2 %.1f/%.1f endP3 %.1f/%.1f sync3 %.1f/%.1f end %.1f/%.1f"
-                " || acc: span1 %.1f/%.1f flush1 %.1f/%.1f scan1 %.1f/%.1f span2 %.1f/%.1f flush2 %.1f/%.1f P3 %.1f/%.1f scan3 %.1f/%.1f apply %.1f/%.1f\n",
+        fprintf(stderr, "[wt select %d CTAs, us, mean/max] endS0 %.1f/%.1f endS1 %.1f/%.1f endC1 %.1f/%.1f endC2 %.1f/%.1f startP4 %.1f/%.1f end %.1f/%.1f"
+                " || acc: sample %.1f/%.1f flushS %.1f/%.1f scanS %.1f/%.1f stream %.1f/%.1f C1 %.1f/%.1f C2 %.1f/%.1f scan4 %.1f/%.1f apply %.1f/%.1f radix %.1f/%.1f\n",
                 g, sum[1], mx[1], sum[2], mx[2], sum[3], mx[3], sum[4], mx[4], sum[5], mx[5], sum[6], mx[6], sum[7], mx[7],
-                sum[8], mx[8], sum[9], mx[9], sum[10], mx[10], sum[11], mx[11], sum[12], mx[12], sum[13], mx[13]);
+                sum[8], mx[8], sum[9], mx[9], sum[10], mx[10], sum[11], mx[11], sum[12], mx[12], sum[13], mx[13], sum[14], mx[14],
+                sum[15], mx[15]);
+        std::vector<WtSelState> ss(P->sel_jobs.size());
+        WT_CUDA(cudaMemcpy(ss.data(), P->sel_args.state, ss.size() * sizeof(WtSelState), cudaMemcpyDeviceToHost));
+        for (size_t q = 0; q < ss.size(); ++q) {
+            const WtSelJob& jb = P->sel_jobs[q];
+            if (ss[q].failed || getenv("WT_SELECT_STAMPS_ALL"))
+                fprintf(stderr, "  job %zu layer %d n %lld zeros %lld k0 %lld shift %d: bracket %u+%u bins, below %llu, in bracket %u (cap %u), a %g b %g%s",
+                        q, jb.layer, jb.n, jb.zeros, jb.k0, jb.sample_shift, ss[q].lo_bin, ss[q].n_bins, ss[q].below,
+                        ss[q].s_count, jb.cand_cap, ss[q].a, ss[q].b, ss[q].failed ? "  -> RADIX PATH" : "");
+            if (ss[q].failed && ss[q].n_bins == 0) fprintf(stderr, " (sample bins %u..%u)", ss[q].cprefix[0], ss[q].cprefix[1]);
+            if (ss[q].failed || getenv("WT_SELECT_STAMPS_ALL")) fprintf(stderr, "\n");
+        }
     }
     for (int i = 0; i < n; ++i) {
         if (counts) {

@@ -32,6 +32,7 @@ extern "C" int wt_select_abs_f32(const float* x, int64_t n, int64_t implicit_zer
     j.lerp_mode = WT_LERP_NEP50; j.tile_begin = 0;
     j.cand = reinterpret_cast<unsigned int*>(dev + o_cand);
     j.cand_cap = cap;
+    j.sample_shift = wt_select_sample_shift(n);
     const long long nt = (n + WT_SEL_TILE - 1) / WT_SEL_TILE;
     int rc = WT_OK;
     if (nt >= 2147483647LL) { wt_set_error("too many tiles"); rc = WT_E_UNSUPPORTED; }

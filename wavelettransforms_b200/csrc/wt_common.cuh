@@ -59,6 +59,9 @@ void wt_level_sizes(int n, int F, int mode, int level, int* sizes);
 #define WT_SEL_BINS2 1024  // key bits 18..9
 #define WT_SEL_BINS3 512   // key bits  8..0
 #define WT_SEL_COARSE (WT_SEL_BINS1 / 32)
+#define WT_SEL_CBINS1 4096 // candidate pass C1 of the sampled path: top 12 bits of key - lo_key inside the bracket
+#define WT_SEL_CBINS 2048  // candidate pass C2: the next <= 11 bits, one histogram per rank
+#define WT_SEL_CBINS3 256  // candidate pass C3 (brackets wider than 16 bins only): the last <= 8 bits
 
 enum { WT_LERP_LEGACY = 0, WT_LERP_NEP50 = 1, WT_LERP_ABSOLUTE = 2 };
 
@@ -76,6 +79,7 @@ struct WtSelJob {
     int n_tiles;
     int layer;       // index into the counts / thresholds arrays
     unsigned int cand_cap;  // capacity of cand[] in keys
+    int sample_shift;       // sampled path: S0 reads 4096 >> sample_shift elements of every 4096-element tile
 };
 
 struct WtSelState {  // per job, device; written by the CTA that holds the job's first tile
@@ -84,9 +88,17 @@ struct WtSelState {  // per job, device; written by the CTA that holds the job's
     unsigned long long rem1[2];    // ranks inside those digits
     unsigned long long rem2[2];
     float a, b, t;                 // sorted[k0], sorted[k1], threshold
-    unsigned int cand_count;       // keys appended to cand[] by P2
+    unsigned int cand_count;       // radix path: keys appended to cand[] by P2
     int overflow;                  // 1: more candidates than cand_cap -> P3 re-reads the tensor
-    int pad;
+    int failed;                    // sampled path gave up on this job (bracket missed / list overflow): radix path runs
+    // sampled path
+    unsigned long long below;      // explicit keys < lo_bin << 19 (counted by S1)
+    unsigned int s_count;          // keys appended to cand[] by S1 (keys inside the bracket)
+    unsigned int lo_bin, n_bins;   // bracket [lo_bin, lo_bin + n_bins) in 12-bit bins; n_bins == 0: S1 did not compact
+    unsigned int cprefix[2];       // C1 digit of both ranks (published by C2)
+    unsigned long long crem[2];    // ranks inside those digits
+    unsigned int cprefix2[2];      // wide brackets: C1 and C2 digits of both ranks (published by C3)
+    unsigned long long crem2[2];
 };
 
 struct WtSelArgs {
@@ -95,8 +107,11 @@ struct WtSelArgs {
     int n_tiles;
     WtSelState* state;
     unsigned long long* hist1;  // [n_jobs][BINS1]
-    unsigned long long* hist2;  // [n_jobs][2][BINS2]
-    unsigned long long* hist3;  // [n_jobs][2][BINS3]
+    unsigned long long* hist2;  // [n_jobs][CBINS1]  (radix path: [2][BINS2] inside the same slot)
+    unsigned long long* hist3;  // [n_jobs][2][CBINS]  (radix path: [2][BINS3] inside the same slot)
+    int* fail_flag;             // set when any job leaves the sampled path
+    int* wide_flag;             // set when any job's bracket is wider than 16 bins: the grid runs candidate pass C3
+    int path;                   // 0: sampled path with radix fallback, 1: radix path only; set by wt_select_launch
     unsigned long long* hist1c; // [n_jobs][BINS1 / 32]: coarse sums of hist1 (32 fine bins each)
     const int* cta_tiles;       // nullable: [cta_grid + 1] first tile of every CTA (cost-balanced split)
     const int* cta_job;         // nullable: [cta_grid] job of that first tile
@@ -109,22 +124,30 @@ struct WtSelArgs {
 
 // candidate capacity (keys) the plan reserves for a population of n explicit values
 static inline unsigned int wt_select_cand_cap(long long n) {
-    long long c = n / 8;
-    if (c > (1LL << 19)) c = 1LL << 19;
+    long long c = n / 4;
+    if (c > (1LL << 21)) c = 1LL << 21;
     if (c < 4096) c = 4096;
     if (c > n) c = n;
     return (unsigned int)c;
 }
 
+// S0 sample of the sampled path: at least 64 Ki keys, 1/16 of the tensor from 1 Mi keys on
+static inline int wt_select_sample_shift(long long n) {
+    int s = 0;
+    while (s < 4 && (n >> (s + 1)) >= (1LL << 16)) ++s;
+    return s;
+}
 size_t wt_select_scratch_bytes(int n_jobs);  // hist1+hist2+hist3+done+state, contiguous, memset to 0 before launch
 // lays out args over a zeroed scratch block
 void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
+#define WT_SEL_SAMPLED_MIN_TILES 10240  // 40 Mi keys
+int wt_select_path(int n_tiles);  // 0 sampled, 1 radix
 // grid wt_select_launch will use for n_tiles tiles on the current device
 int wt_select_grid(int n_tiles, int* grid_out);
 // cost-balanced contiguous split of the tile space over `grid` CTAs: every segment (piece of one job inside one
 // CTA) costs WT_SEL_SEGMENT_COST tiles on top of its tiles.  tiles_out[grid + 1], job_out[grid] (HOST)
-#define WT_SEL_SEGMENT_COST 2
+#define WT_SEL_SEGMENT_COST 12
 void wt_select_balance(const WtSelJob* jobs, int n_jobs, int n_tiles, int grid, int* tiles_out, int* job_out);
 #define WT_SEL_STAMP_CTAS 2048
 

@@ -250,6 +250,7 @@ extern "C" int wt_min_weight_prune_f32(float* const* w, const int64_t* n, const 
         s.k0 = s.k1 = std::min<long long>(std::max<long long>(k[i] - 1, 0), n[i] - 1);
         s.gamma = 0.0; s.lerp_mode = WT_LERP_NEP50; s.tile_begin = tiles; s.n_tiles = (int)nt; s.layer = (int)sjobs.size();
         s.cand_cap = wt_select_cand_cap(n[i]);
+        s.sample_shift = wt_select_sample_shift(n[i]);
         tiles += (int)nt;
         jobs.push_back(m);
         sjobs.push_back(s);

@@ -9,19 +9,36 @@
 // interpolation can be reproduced from the exact sorted[k0] and sorted[k1].  Implicit zeros
 // (coeffs_to_array padding) are added to digit 0 wherever the prefix is 0.
 //
-// MSD radix select, 12 + 10 + 9 key bits, on a persistent grid: every CTA owns one contiguous
-// range of 4096-element tiles (cut into per-job segments), grid barriers separate the phases, and
-// NO phase has a serial tail: after a barrier every CTA scans the (small, L2-resident) global
-// histogram of its own job redundantly instead of waiting for one elected CTA to do it.
+// Persistent grid: every CTA owns one contiguous range of 4096-element tiles (cut into per-job segments), grid
+// barriers separate the phases, and NO phase has a serial tail: after a barrier every CTA scans the (small,
+// L2-resident) global histogram of its own job redundantly instead of waiting for one elected CTA to do it.
+//
+// SAMPLED PATH (launches of 40 Mi keys and more, see wt_select_path): ONE full pass over the tensors, and that pass has no shared-memory atomics.
+//   S0  12-bit histogram (key bits 30..19) of a SAMPLE: 4096 >> sample_shift elements of every tile, at a window
+//       offset that rotates with the tile index; tensors below 128 Ki keys are read whole (the sample is exact)
+//   S1  every CTA scans the sample histogram -> a bracket of consecutive 12-bit bins that holds both ranks
+//       unless the sample lied (5 sigma of the binomial rank error on each side; exact for whole-tensor samples);
+//       then the one streaming pass: count the keys below the bracket, compact the keys inside it into the job's
+//       candidate list (warp-private staging, no CTA barrier, no histogram)
+//   C1  verify: below <= rank < below + candidates and the list did not overflow -- otherwise the job is handed to
+//       the radix path; histogram of the top 12 bits of key - lo_key inside the bracket over the candidate list
+//   C2  scan -> digit of both ranks; histogram of the next (7..11) bits of the matching candidates
+//   C3  only when some job's bracket is wider than 16 bins (a rank next to a cluster of ties at zero: the bins in
+//       between are many and nearly empty): the last <= 8 bits
+//   P4  scan -> sorted[k0], sorted[k1] -> threshold; level-0 jobs: out = |x| < t ? 0 : x + counts
+// The result is EXACT whatever the sample says: the bracket is only a guess of where to look, the counts decide.
+//
+// RADIX PATH (smaller launches, and any job the sampled path gave up on -- heavy ties away from zero --): MSD radix select, 12 + 10 + 9 key bits, three more phases before P4:
 //   P1  histogram of key bits 30..19 (streams the tensors from HBM) -> global hist1
 //   P2  scan hist1 -> digit of both ranks; histogram of bits 18..9 of the matching keys -> hist2,
 //       and the matching keys (about 2 % of a Gaussian tensor) are compacted into the job's
 //       candidate list through a shared-memory staging buffer (tensors re-read from L2)
 //   P3  scan hist2 -> 22-bit prefixes; histogram of bits 8..0 over the CANDIDATE LIST only -> hist3
-//   P4  scan hist3 -> sorted[k0], sorted[k1] -> threshold; level-0 jobs: out = |x| < t ? 0 : x + counts
-// A job whose candidates do not fit its list (heavy ties, e.g. half the tensor exactly zero) re-reads
-// the tensor in P3 instead of the list.
+//       (a job whose candidates do not fit its list re-reads the tensor instead)
 #include <cooperative_groups.h>
+
+#include <cstdlib>
+#include <cstring>
 
 #include "wt_common.cuh"
 
@@ -225,7 +242,7 @@ __device__ Found scan_find_pair(const H* h0, const H* h1, unsigned long long z0,
 template <int PASS>
 __device__ __forceinline__ unsigned long long* global_hist(const WtSelArgs& a, int j) {
     constexpr int NB = PASS == 1 ? WT_SEL_BINS1 : (PASS == 2 ? WT_SEL_BINS2 : WT_SEL_BINS3);
-    return PASS == 1 ? a.hist1 + (size_t)j * NB : (PASS == 2 ? a.hist2 + (size_t)j * 2 * NB : a.hist3 + (size_t)j * 2 * NB);
+    return PASS == 1 ? a.hist1 + (size_t)j * NB : (PASS == 2 ? a.hist2 + (size_t)j * WT_SEL_CBINS1 : a.hist3 + (size_t)j * 2 * WT_SEL_CBINS);
 }
 
 __device__ __forceinline__ void clear_hist(Shared& sh, int n) {
@@ -254,13 +271,27 @@ __device__ __forceinline__ void flush_hist(const WtSelArgs& a, Shared& sh, int j
 }
 
 
+// the same for nbt bins of the sampled path's candidate histograms
+__device__ __forceinline__ void flush_bins(Shared& sh, unsigned long long* gh, int nbt) {
+    __syncthreads();
+    for (int b = threadIdx.x; b < nbt; b += T) {
+        unsigned int v = sh.hist[b];
+        if (v) atomicAdd(&gh[b], (unsigned long long)v);
+    }
+}
+
 // Pass-1 lookup through the coarse histogram: warp 0 scans the 128 coarse sums (4 per lane), then warps 0
 // and 1 scan the 32 fine bins of the coarse bin holding rank0 / rank1.  Two dependent L2 round trips and two
 // barriers instead of a block-wide scan of 4096 bins.  Every thread returns the same result.
+// n_pop > 0: the histogram is a SAMPLE of n_pop keys and rank0 <= rank1 are ranks in the population: they are
+// scaled to the sample and pushed apart by 5 sigma of the binomial rank error (nothing when the sample is whole).
 __device__ Found scan_find_two_level(const unsigned long long* __restrict__ coarse, const unsigned long long* __restrict__ fine,
-                                     unsigned long long zeros, unsigned long long rank0, unsigned long long rank1, Shared& sh) {
+                                     unsigned long long zeros, unsigned long long rank0, unsigned long long rank1, Shared& sh,
+                                     long long n_pop = 0) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (wid == 0) {
+        if (lane < 2) { sh.res_digit[lane] = 0u; sh.res_rem[lane] = 0ull; sh.res_cnt[lane] = 0ull; }  // empty histogram
+        __syncwarp();
         unsigned long long c[4], s = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) c[i] = __ldcg(&coarse[lane * 4 + i]);
@@ -275,10 +306,19 @@ __device__ Found scan_find_two_level(const unsigned long long* __restrict__ coar
         }
         const unsigned long long total = __shfl_sync(0xffffffffu, inc, 31), excl = inc - s;
         unsigned long long rk[2] = {rank0, rank1};
+        if (n_pop > 0 && total != (unsigned long long)n_pop) {
+            // rank of a population quantile inside a sample of `total` keys: binomial, sigma^2 = total * q * (1 - q)
+            const double f = (double)total / (double)n_pop;
+            const double q0 = ((double)rank0 + 0.5) / (double)n_pop, q1 = ((double)rank1 + 0.5) / (double)n_pop;
+            const double lo = floor((double)rank0 * f - 5.0 * sqrt((double)total * q0 * (1.0 - q0)) - 3.0);
+            const double hi = ceil((double)rank1 * f + 5.0 * sqrt((double)total * q1 * (1.0 - q1)) + 3.0);
+            rk[0] = lo > 0.0 ? (unsigned long long)lo : 0ull;
+            rk[1] = hi > 0.0 ? (unsigned long long)hi : 0ull;
+        }
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
             unsigned long long r = rk[q];
-            if (r >= total) r = total ? total - 1 : 0;  // defensive; cannot happen for a consistent plan
+            if (r >= total) r = total ? total - 1 : 0;  // the padded sample rank may run past the sample
             if (s > 0 && excl <= r && r < excl + s) {
                 unsigned long long run = excl;
 #pragma unroll
@@ -477,29 +517,354 @@ __device__ void hist2_compact_span(const float* __restrict__ x, long long len, u
     if (wcount) warp_flush(wbuf, wcount, g_cnt, cand, cap);
 }
 
+// candidate-list boundary belonging to tile offset t of a job with n_tiles tiles (multiples of 4 keys)
+__device__ __forceinline__ unsigned int cand_boundary(unsigned int n_c, int t, int n_tiles) {
+    if (t >= n_tiles) return n_c;
+    return (unsigned int)(((unsigned long long)n_c * (unsigned long long)t) / (unsigned long long)n_tiles) & ~3u;
+}
+
+// ================================ sampled path ===========================================================
+// true when job j runs (or has been handed to) the radix path
+__device__ __forceinline__ bool radix_job(const WtSelArgs& a, int j) { return a.path != 0 || __ldcg(&a.state[j].failed) != 0; }
+
+// explicit-key ranks of the two order statistics: the implicit zeros sort first, so population rank k is
+// explicit rank k - zeros (clamped: a rank inside the zeros needs no explicit key at all, see final_keys)
+__device__ __forceinline__ void explicit_ranks(const WtSelJob& job, unsigned long long& e0, unsigned long long& e1) {
+    const long long last = job.n - 1;
+    long long r0 = job.k0 - job.zeros, r1 = job.k1 - job.zeros;
+    r0 = r0 < 0 ? 0 : (r0 > last ? last : r0);
+    r1 = r1 < 0 ? 0 : (r1 > last ? last : r1);
+    if (r1 < r0) r1 = r0;
+    e0 = (unsigned long long)r0;
+    e1 = (unsigned long long)r1;
+}
+
+// A bracket of n_bins 12-bit bins spans 19 + ceil(log2(n_bins)) bits of key - lo_key: C1 resolves the top 12 of
+// them, C2 the next min(cand_shift, 11), C3 -- only for brackets wider than 16 bins -- the last cand_shift2 <= 8.
+__device__ __forceinline__ int cand_shift(unsigned int n_bins) { return 7 + (32 - __clz(n_bins - 1u)) * (n_bins > 1u); }
+__device__ __forceinline__ int cand_shift2(int cs) { return cs > 11 ? cs - 11 : 0; }
+
+// S0 over one segment: 12-bit histogram of the sample windows of `tiles` tiles starting at job tile `tile0`
+__device__ __forceinline__ void sample_span(const float* __restrict__ x, long long len, int tile0, int tiles, int s,
+                                            unsigned int* h) {
+    if (s == 0) {
+        span_for_each(x, len, [h](float v) { atomicAdd(&h[abs_key(v) >> 19], 1u); });
+        return;
+    }
+    const int wshift = 12 - s;       // log2(window elements)
+    const int vshift = wshift - 2;   // log2(float4s per window)
+    const unsigned int wmask = (1u << s) - 1u, vmask = (1u << vshift) - 1u;
+    const long long total = (long long)tiles << vshift;
+    const bool aligned = (reinterpret_cast<uintptr_t>(x) & 15u) == 0;
+    for (long long v0 = threadIdx.x; v0 < total; v0 += (long long)T * UNROLL) {
+        float4 r[UNROLL];
+        bool ok[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const long long v = v0 + (long long)u * T;
+            ok[u] = false;
+            if (v < total) {
+                const long long tile = v >> vshift;
+                const unsigned int win = ((unsigned int)(tile0 + (int)tile) * 5u + 3u) & wmask;
+                const long long off = (tile << 12) + ((long long)win << wshift) + (long long)(((unsigned int)v & vmask) << 2);
+                if (off + 4 <= len) {
+                    ok[u] = true;
+                    if (aligned) r[u] = __ldg(reinterpret_cast<const float4*>(x + off));
+                    else r[u] = make_float4(__ldg(x + off), __ldg(x + off + 1), __ldg(x + off + 2), __ldg(x + off + 3));
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            if (ok[u]) {
+                atomicAdd(&h[abs_key(r[u].x) >> 19], 1u); atomicAdd(&h[abs_key(r[u].y) >> 19], 1u);
+                atomicAdd(&h[abs_key(r[u].z) >> 19], 1u); atomicAdd(&h[abs_key(r[u].w) >> 19], 1u);
+            }
+        }
+    }
+}
+
+// ---- S0: sample histogram -> hist1 / hist1c -------------------------------------------------------------
+__device__ void phase_s0_sample(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        clear_hist(sh, WT_SEL_BINS1);
+        acc.begin();
+        sample_span(job.x + base, len, (int)(base / WT_SEL_TILE), tiles, job.sample_shift, sh.hist);
+        acc.end(7);
+        acc.begin();
+        flush_hist<1>(a, sh, j);
+        acc.end(8);
+    });
+}
+
+// S1 over one span: count the keys below lo_key, compact the keys with key - lo_key < width into the job's
+// candidate list.  Same warp-private staging as hist2_compact_span, and nothing else: no shared-memory atomics.
+__device__ void range_compact_span(const float* __restrict__ x, long long len, unsigned int lo_key, unsigned int width,
+                                   Shared& sh, unsigned long long* g_below, unsigned int* g_cnt,
+                                   unsigned int* __restrict__ cand, unsigned int cap) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned int* wbuf = sh.stage + wid * WSTAGE;
+    unsigned int wcount = 0;  // warp-uniform
+    unsigned int nbelow = 0;
+    long long done = 0;
+    if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
+        const long long nvec = len >> 2;
+        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
+        for (long long v0 = 0; v0 < nvec; v0 += (long long)T * UNROLL) {  // CTA-uniform trip count
+            const long long v = v0 + threadIdx.x;
+            unsigned int key[UNROLL * 4];
+            unsigned int hitmask = 0;
+            float4 r[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u)
+                if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                const bool ok = v + (long long)u * T < nvec;
+                key[u * 4 + 0] = abs_key(r[u].x); key[u * 4 + 1] = abs_key(r[u].y);
+                key[u * 4 + 2] = abs_key(r[u].z); key[u * 4 + 3] = abs_key(r[u].w);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    if (ok) {
+                        nbelow += key[u * 4 + c] < lo_key;
+                        if (key[u * 4 + c] - lo_key < width) hitmask |= 1u << (u * 4 + c);
+                    }
+                }
+            }
+            if (__any_sync(0xffffffffu, hitmask != 0u)) {
+                const unsigned int nh = __popc(hitmask);
+                unsigned int inc = nh;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
+                    if (lane >= d) inc += o;
+                }
+                const unsigned int total = __shfl_sync(0xffffffffu, inc, 31);
+                unsigned int pos = wcount + inc - nh;
+#pragma unroll
+                for (int e = 0; e < UNROLL * 4; ++e)
+                    if (hitmask & (1u << e)) wbuf[pos++] = key[e];
+                wcount += total;
+                if (wcount > WSTAGE_FLUSH) warp_flush(wbuf, wcount, g_cnt, cand, cap);
+            }
+        }
+        done = nvec << 2;
+    }
+    for (long long i0 = done; i0 < len; i0 += T) {  // tail, or everything when x is not 16-byte aligned
+        const bool ok = i0 + threadIdx.x < len;
+        const unsigned int key = ok ? abs_key(__ldg(&x[i0 + threadIdx.x])) : 0u;
+        nbelow += ok && key < lo_key;
+        const bool hit = ok && (key - lo_key < width);
+        const unsigned int ballot = __ballot_sync(0xffffffffu, hit);
+        if (ballot) {
+            if (hit) wbuf[wcount + __popc(ballot & ((1u << lane) - 1u))] = key;
+            wcount += __popc(ballot);
+            if (wcount > WSTAGE_FLUSH) warp_flush(wbuf, wcount, g_cnt, cand, cap);
+        }
+    }
+    if (wcount) warp_flush(wbuf, wcount, g_cnt, cand, cap);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) nbelow += __shfl_down_sync(0xffffffffu, nbelow, d);
+    if (lane == 0 && nbelow) atomicAdd(g_below, (unsigned long long)nbelow);
+}
+
+// ---- S1: bracket from the sample histogram; the one full pass: count below, compact the bracket -------------
+__device__ void phase_s1_compact(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        WtSelState* st = &a.state[j];
+        unsigned long long e0, e1;
+        explicit_ranks(job, e0, e1);
+        acc.begin();
+        const Found f = scan_find_two_level(a.hist1c + (size_t)j * WT_SEL_COARSE, global_hist<1>(a, j), 0ull, e0, e1, sh, job.n);
+        acc.end(9);
+        const unsigned int lo_bin = f.d0;
+        unsigned int n_bins = f.d1 - f.d0 + 1u;
+        if (f.d1 < f.d0 || job.cand == nullptr) n_bins = 0u;  // -> radix path
+        if (base == 0 && threadIdx.x == 0) {
+            st->lo_bin = lo_bin; st->n_bins = n_bins;
+            if (n_bins > 16u) *a.wide_flag = 1;
+        }
+        if (n_bins == 0u) return;
+        acc.begin();
+        // a bracket that starts at bin 0 leaves the exact zeros out of the list: they are counted as "below" and a
+        // rank inside them is 0 without looking (the massive tie of this domain: pruned weights, vanishing details)
+        const unsigned int lo_eff = (lo_bin << 19) | (lo_bin == 0u ? 1u : 0u);
+        range_compact_span(job.x + base, len, lo_eff, ((lo_bin + n_bins) << 19) - lo_eff, sh, &st->below, &st->s_count, job.cand,
+                           job.cand_cap);
+        acc.end(10);
+    });
+}
+
+// ---- C1: verify the bracket; histogram of the top 12 bits of key - lo_key over the candidate list -> hist2 ------
+__device__ void phase_c1_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        WtSelState* st = &a.state[j];
+        const unsigned int n_bins = __ldcg(&st->n_bins), n_c = __ldcg(&st->s_count);
+        const unsigned long long below = __ldcg(&st->below);
+        unsigned long long e0, e1;
+        explicit_ranks(job, e0, e1);
+        const bool zlo = __ldcg(&st->lo_bin) == 0u;  // then `below` counts the exact zeros
+        const bool in0 = (zlo && e0 < below) || (below <= e0 && e0 < below + (unsigned long long)n_c);
+        const bool in1 = (zlo && e1 < below) || (below <= e1 && e1 < below + (unsigned long long)n_c);
+        const bool good = n_bins != 0u && n_c <= job.cand_cap && in0 && in1;
+        if (!good) {  // every CTA of the job sees the same counts and takes the same decision
+            if (base == 0) {  // hist1 / hist1c held the sample: the radix path starts from zero
+                unsigned long long* gh1 = global_hist<1>(a, j);
+                for (int b = threadIdx.x; b < WT_SEL_BINS1; b += T) gh1[b] = 0ull;
+                if (threadIdx.x < WT_SEL_COARSE) a.hist1c[(size_t)j * WT_SEL_COARSE + threadIdx.x] = 0ull;
+                if (threadIdx.x == 0) { st->failed = 1; *a.fail_flag = 1; }
+            }
+            return;
+        }
+        acc.begin();
+        if (n_bins > 16u && base == 0) {  // C3 reuses the slot of the sample histogram, dead since the last barrier
+            unsigned long long* gh1 = global_hist<1>(a, j);
+            for (int b = threadIdx.x; b < 2 * WT_SEL_CBINS3; b += T) gh1[b] = 0ull;
+        }
+        clear_hist(sh, WT_SEL_CBINS1);
+        unsigned int* h = sh.hist;
+        const unsigned int lo_key = __ldcg(&st->lo_bin) << 19;
+        const int cs = cand_shift(n_bins);
+        const int t0 = (int)(base / WT_SEL_TILE);
+        const unsigned int lo = cand_boundary(n_c, t0, job.n_tiles), hi = cand_boundary(n_c, t0 + tiles, job.n_tiles);
+        cand_for_each(job.cand + lo, hi - lo, [h, lo_key, cs](unsigned int k) { atomicAdd(&h[(k - lo_key) >> cs], 1u); });
+        flush_bins(sh, global_hist<2>(a, j), WT_SEL_CBINS1);
+        acc.end(11);
+    });
+}
+
+// ---- C2: digit of both ranks from hist2; histogram of the low bits of the matching candidates -> hist3 ---------
+__device__ void phase_c2_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        WtSelState* st = &a.state[j];
+        if (__ldcg(&st->failed)) return;
+        const unsigned int n_c = __ldcg(&st->s_count);
+        const unsigned long long below = __ldcg(&st->below);
+        unsigned long long e0, e1;
+        explicit_ranks(job, e0, e1);
+        acc.begin();
+        const unsigned long long* gh = global_hist<2>(a, j);
+        // a rank inside the exact zeros (bracket from bin 0 only) needs no candidate: final_keys answers 0
+        const Found f = scan_find_pair<WT_SEL_CBINS1, true>(gh, gh, 0ull, 0ull, e0 < below ? 0ull : e0 - below,
+                                                            e1 < below ? 0ull : e1 - below, sh);
+        const unsigned int d0 = f.d0, d1 = f.d1;
+        const bool two = (d0 != d1);
+        if (base == 0 && threadIdx.x == 0) {
+            st->cprefix[0] = d0; st->cprefix[1] = d1;
+            st->crem[0] = f.r0; st->crem[1] = f.r1;
+        }
+        clear_hist(sh, 2 * WT_SEL_CBINS);
+        unsigned int* h = sh.hist;
+        const unsigned int lo_key = __ldcg(&st->lo_bin) << 19;
+        const int t0 = (int)(base / WT_SEL_TILE);
+        const unsigned int lo = cand_boundary(n_c, t0, job.n_tiles), hi = cand_boundary(n_c, t0 + tiles, job.n_tiles);
+        const int cs = cand_shift(__ldcg(&st->n_bins)), cs2 = cand_shift2(cs);
+        const unsigned int low = (1u << (cs - cs2)) - 1u;
+        cand_for_each(job.cand + lo, hi - lo, [h, lo_key, d0, d1, two, cs, cs2, low](unsigned int k) {
+            const unsigned int kk = k - lo_key, top = kk >> cs;
+            if (top == d0) atomicAdd(&h[(kk >> cs2) & low], 1u);
+            else if (two && top == d1) atomicAdd(&h[WT_SEL_CBINS + ((kk >> cs2) & low)], 1u);
+        });
+        flush_bins(sh, a.hist3 + (size_t)j * 2 * WT_SEL_CBINS, 2 * WT_SEL_CBINS);
+        acc.end(12);
+    });
+}
+
+// ---- C3 (only when some bracket is wider than 16 bins): digits from hist3; histogram of the last <= 8 bits ------
+__device__ void phase_c3_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+    for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        WtSelState* st = &a.state[j];
+        const unsigned int n_bins = __ldcg(&st->n_bins);
+        if (__ldcg(&st->failed) || n_bins <= 16u) return;
+        const unsigned int n_c = __ldcg(&st->s_count);
+        const unsigned int d0 = __ldcg(&st->cprefix[0]), d1 = __ldcg(&st->cprefix[1]);
+        const unsigned long long r0 = __ldcg(&st->crem[0]), r1 = __ldcg(&st->crem[1]);
+        const unsigned long long* gh3 = global_hist<3>(a, j);
+        const Found f = scan_find_pair<WT_SEL_CBINS, false>(gh3, d0 != d1 ? gh3 + WT_SEL_CBINS : gh3, 0ull, 0ull, r0, r1, sh);
+        const unsigned int q0 = (d0 << 11) | f.d0, q1 = (d1 << 11) | f.d1;  // wide: C2 resolved exactly 11 bits
+        const bool two = (q0 != q1);
+        if (base == 0 && threadIdx.x == 0) {
+            st->cprefix2[0] = q0; st->cprefix2[1] = q1;
+            st->crem2[0] = f.r0; st->crem2[1] = f.r1;
+        }
+        clear_hist(sh, 2 * WT_SEL_CBINS3);
+        unsigned int* h = sh.hist;
+        const unsigned int lo_key = __ldcg(&st->lo_bin) << 19;
+        const int cs2 = cand_shift2(cand_shift(n_bins));
+        const unsigned int low = (1u << cs2) - 1u;
+        const int t0 = (int)(base / WT_SEL_TILE);
+        const unsigned int lo = cand_boundary(n_c, t0, job.n_tiles), hi = cand_boundary(n_c, t0 + tiles, job.n_tiles);
+        cand_for_each(job.cand + lo, hi - lo, [h, lo_key, q0, q1, two, cs2, low](unsigned int k) {
+            const unsigned int kk = k - lo_key, top = kk >> cs2;
+            if (top == q0) atomicAdd(&h[kk & low], 1u);
+            else if (two && top == q1) atomicAdd(&h[WT_SEL_CBINS3 + (kk & low)], 1u);
+        });
+        flush_bins(sh, global_hist<1>(a, j), 2 * WT_SEL_CBINS3);
+    });
+}
+
+// both order statistics of job j as key patterns, from whichever path finished the job
+__device__ __forceinline__ void final_keys(const WtSelArgs& a, Shared& sh, int j, const WtSelJob& job, unsigned int& key0,
+                                           unsigned int& key1) {
+    WtSelState* st = &a.state[j];
+    if (radix_job(a, j)) {
+        const unsigned int n0 = __ldcg(&st->prefix2[0]), n1 = __ldcg(&st->prefix2[1]);
+        const unsigned long long r0 = __ldcg(&st->rem2[0]), r1 = __ldcg(&st->rem2[1]);
+        const bool two2 = (n0 != n1);
+        const unsigned long long zeros = (unsigned long long)job.zeros;
+        const unsigned long long* gh3 = global_hist<3>(a, j);
+        const Found f = scan_find_pair<WT_SEL_BINS3, false>(gh3, two2 ? gh3 + WT_SEL_BINS3 : gh3, n0 == 0u ? zeros : 0ull,
+                                                     n1 == 0u ? zeros : 0ull, r0, r1, sh);
+        key0 = (n0 << 9) | f.d0;
+        key1 = (n1 << 9) | f.d1;
+    } else {
+        const unsigned int lo_key = __ldcg(&st->lo_bin) << 19;
+        const unsigned int n_bins = __ldcg(&st->n_bins);
+        const int cs = cand_shift(n_bins), cs2 = cand_shift2(cs);
+        unsigned int v0, v1;  // key - lo_key
+        if (n_bins > 16u) {
+            const unsigned int q0 = __ldcg(&st->cprefix2[0]), q1 = __ldcg(&st->cprefix2[1]);
+            const unsigned long long r0 = __ldcg(&st->crem2[0]), r1 = __ldcg(&st->crem2[1]);
+            const unsigned long long* gh = global_hist<1>(a, j);
+            const Found f = scan_find_pair<WT_SEL_CBINS3, false>(gh, q0 != q1 ? gh + WT_SEL_CBINS3 : gh, 0ull, 0ull, r0, r1, sh);
+            v0 = (q0 << cs2) | f.d0;
+            v1 = (q1 << cs2) | f.d1;
+        } else {
+            const unsigned int d0 = __ldcg(&st->cprefix[0]), d1 = __ldcg(&st->cprefix[1]);
+            const unsigned long long r0 = __ldcg(&st->crem[0]), r1 = __ldcg(&st->crem[1]);
+            const unsigned long long* gh3 = global_hist<3>(a, j);
+            const Found f = scan_find_pair<WT_SEL_CBINS, false>(gh3, d0 != d1 ? gh3 + WT_SEL_CBINS : gh3, 0ull, 0ull, r0, r1, sh);
+            v0 = (d0 << cs) | f.d0;
+            v1 = (d1 << cs) | f.d1;
+        }
+        unsigned long long e0, e1;
+        explicit_ranks(job, e0, e1);
+        const unsigned long long ez = lo_key == 0u ? __ldcg(&st->below) : 0ull;  // exact zeros among the explicit keys
+        key0 = (job.k0 < job.zeros || e0 < ez) ? 0u : lo_key + v0;  // a rank inside the zeros is 0
+        key1 = (job.k1 < job.zeros || e1 < ez) ? 0u : lo_key + v1;
+    }
+}
+
+// ================================ radix path ================================================================
 // ---- P1: histogram of key bits 30..19 ------------------------------------------------------------------
 __device__ void phase1_hist(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        if (!radix_job(a, j)) return;
         clear_hist(sh, WT_SEL_BINS1);
         unsigned int* h = sh.hist;
-        acc.begin();
         span_for_each(job.x + base, len, [h](float v) { atomicAdd(&h[abs_key(v) >> 19], 1u); });
-        acc.end(6);
-        acc.begin();
         flush_hist<1>(a, sh, j);
-        acc.end(7);
     });
 }
 
 // ---- P2: digit of both ranks from hist1; histogram of bits 18..9 + compaction of the matching keys ------
 __device__ void phase2_hist_compact(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        if (!radix_job(a, j)) return;
         WtSelState* st = &a.state[j];
-        acc.begin();
         const unsigned long long* gh1 = global_hist<1>(a, j);
         const Found f = scan_find_two_level(a.hist1c + (size_t)j * WT_SEL_COARSE, gh1, (unsigned long long)job.zeros,
                                             (unsigned long long)job.k0, (unsigned long long)job.k1, sh);
-        acc.end(8);
         const unsigned int p0 = f.d0, p1 = f.d1;
         const bool two = (p0 != p1);
         // compaction only when every key of the one or two selected digits fits the candidate list
@@ -512,35 +877,25 @@ __device__ void phase2_hist_compact(const WtSelArgs& a, Shared& sh, int t_begin,
         }
         clear_hist(sh, 2 * WT_SEL_BINS2);
         unsigned int* h = sh.hist;
-        acc.begin();
         if (ovf) {
             span_for_each(job.x + base, len, [h, p0, p1, two](float v) { bin_one<2>(abs_key(v), h, p0, p1, two); });
         } else {
             hist2_compact_span(job.x + base, len, p0, p1, two, sh, &st->cand_count, job.cand, job.cand_cap);
         }
-        acc.end(9);
-        acc.begin();
         flush_hist<2>(a, sh, j);
-        acc.end(10);
     });
-}
-
-// candidate-list boundary belonging to tile offset t of a job with n_tiles tiles (multiples of 4 keys)
-__device__ __forceinline__ unsigned int cand_boundary(unsigned int n_c, int t, int n_tiles) {
-    if (t >= n_tiles) return n_c;
-    return (unsigned int)(((unsigned long long)n_c * (unsigned long long)t) / (unsigned long long)n_tiles) & ~3u;
 }
 
 // ---- P3: 22-bit prefixes from hist2; histogram of bits 8..0 over the candidate list ----------------------
 __device__ void phase3_hist_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
+        if (!radix_job(a, j)) return;
         WtSelState* st = &a.state[j];
         const unsigned int p0 = __ldcg(&st->prefix1[0]), p1 = __ldcg(&st->prefix1[1]);
         const unsigned long long r0 = __ldcg(&st->rem1[0]), r1 = __ldcg(&st->rem1[1]);
         const bool ovf = __ldcg(&st->overflow) != 0;
         const bool two = (p0 != p1);
         const unsigned long long zeros = (unsigned long long)job.zeros;
-        acc.begin();
         const unsigned long long* gh2 = global_hist<2>(a, j);
         const Found f = scan_find_pair<WT_SEL_BINS2, false>(gh2, two ? gh2 + WT_SEL_BINS2 : gh2, p0 == 0u ? zeros : 0ull,
                                                      p1 == 0u ? zeros : 0ull, r0, r1, sh);
@@ -562,7 +917,6 @@ __device__ void phase3_hist_cand(const WtSelArgs& a, Shared& sh, int t_begin, in
             cand_for_each(job.cand + lo, hi - lo, [h, n0, n1, two2](unsigned int k) { bin_one<3>(k, h, n0, n1, two2); });
         }
         flush_hist<3>(a, sh, j);
-        acc.end(11);
     });
 }
 
@@ -571,15 +925,9 @@ __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
         if (!job.out && base != 0) return;  // select-only job: its first-tile CTA publishes, nobody applies
         WtSelState* st = &a.state[j];
-        const unsigned int n0 = __ldcg(&st->prefix2[0]), n1 = __ldcg(&st->prefix2[1]);
-        const unsigned long long r0 = __ldcg(&st->rem2[0]), r1 = __ldcg(&st->rem2[1]);
-        const bool two2 = (n0 != n1);
-        const unsigned long long zeros = (unsigned long long)job.zeros;
         acc.begin();
-        const unsigned long long* gh3 = global_hist<3>(a, j);
-        const Found f = scan_find_pair<WT_SEL_BINS3, false>(gh3, two2 ? gh3 + WT_SEL_BINS3 : gh3, n0 == 0u ? zeros : 0ull,
-                                                     n1 == 0u ? zeros : 0ull, r0, r1, sh);
-        const unsigned int key0 = (n0 << 9) | f.d0, key1 = (n1 << 9) | f.d1;
+        unsigned int key0, key1;
+        final_keys(a, sh, j, job, key0, key1);
         const float t = lerp_threshold(__uint_as_float(key0), __uint_as_float(key1), job.gamma, job.lerp_mode);
         if (base == 0 && threadIdx.x == 0) {
             st->a = __uint_as_float(key0);
@@ -588,7 +936,7 @@ __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_
             a.thresholds[job.layer] = t;
             if (job.out) a.counts[(size_t)job.layer * 4] = job.n;
         }
-        acc.end(12);
+        acc.end(13);
         if (!job.out) return;
         acc.begin();
         const float* x = job.x + base;  // may alias out (in-place pruning): no __restrict__, no read-only path
@@ -618,7 +966,7 @@ __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_
         for (long long i = done + threadIdx.x; i < len; i += T) o[i] = apply_one(x[i], t, zc, nzb);
         // every element of the span is visited exactly once: thread 0 contributes the span length
         block_add3(a.counts + (size_t)job.layer * 4, zc, nzb, threadIdx.x == 0 ? (unsigned int)len : 0u, sh.hist);
-        acc.end(13);
+        acc.end(14);
     });
 }
 
@@ -639,18 +987,37 @@ __global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs 
     acc.slot = a.stamps ? a.stamps + (size_t)blockIdx.x * 16 : nullptr;
     acc.t0 = 0;
     acc.stamp(0);
-    phase1_hist(a, sh, t_begin, t_end, acc);
-    acc.stamp(1);
-    grid.sync();
-    phase2_hist_compact(a, sh, t_begin, t_end, acc);
-    acc.stamp(2);
-    grid.sync();
-    phase3_hist_cand(a, sh, t_begin, t_end, acc);
-    acc.stamp(3);
-    grid.sync();
-    acc.stamp(4);
-    phase4_apply(a, sh, t_begin, t_end, acc);
+    if (a.path == 0) {
+        phase_s0_sample(a, sh, t_begin, t_end, acc);
+        acc.stamp(1);
+        grid.sync();
+        phase_s1_compact(a, sh, t_begin, t_end, acc);
+        acc.stamp(2);
+        grid.sync();
+        phase_c1_cand(a, sh, t_begin, t_end, acc);
+        acc.stamp(3);
+        grid.sync();
+        phase_c2_cand(a, sh, t_begin, t_end, acc);
+        acc.stamp(4);
+        grid.sync();
+        if (__ldcg(a.wide_flag) != 0) {  // grid-uniform: set during S1, three barriers ago
+            phase_c3_cand(a, sh, t_begin, t_end, acc);
+            grid.sync();
+        }
+    }
+    if (a.path != 0 || __ldcg(a.fail_flag) != 0) {  // grid-uniform: the flag was final before the last barrier
+        acc.begin();
+        phase1_hist(a, sh, t_begin, t_end, acc);
+        grid.sync();
+        phase2_hist_compact(a, sh, t_begin, t_end, acc);
+        grid.sync();
+        phase3_hist_cand(a, sh, t_begin, t_end, acc);
+        grid.sync();
+        acc.end(15);
+    }
     acc.stamp(5);
+    phase4_apply(a, sh, t_begin, t_end, acc);
+    acc.stamp(6);
 }
 
 __global__ void __launch_bounds__(256) wt_apply_threshold_kernel(const float* __restrict__ x, float* __restrict__ out,
@@ -685,7 +1052,7 @@ __global__ void __launch_bounds__(256) wt_apply_threshold_kernel(const float* __
 }  // namespace
 
 size_t wt_select_scratch_bytes(int n_jobs) {
-    size_t per = (size_t)WT_SEL_BINS1 * 8 + 2 * (size_t)WT_SEL_BINS2 * 8 + 2 * (size_t)WT_SEL_BINS3 * 8 +
+    size_t per = (size_t)WT_SEL_BINS1 * 8 + (size_t)WT_SEL_CBINS1 * 8 + 2 * (size_t)WT_SEL_CBINS * 8 +
                  (size_t)WT_SEL_COARSE * 8 + sizeof(WtSelState);
     return per * (size_t)n_jobs + 256;
 }
@@ -693,10 +1060,13 @@ size_t wt_select_scratch_bytes(int n_jobs) {
 void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
     char* p = static_cast<char*>(scratch);
     a->hist1 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * WT_SEL_BINS1 * 8;
-    a->hist2 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * 2 * WT_SEL_BINS2 * 8;
-    a->hist3 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * 2 * WT_SEL_BINS3 * 8;
+    a->hist2 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * WT_SEL_CBINS1 * 8;
+    a->hist3 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * 2 * WT_SEL_CBINS * 8;
     a->hist1c = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * WT_SEL_COARSE * 8;
-    a->state = reinterpret_cast<WtSelState*>(p);
+    a->state = reinterpret_cast<WtSelState*>(p); p += (size_t)n_jobs * sizeof(WtSelState);
+    a->fail_flag = reinterpret_cast<int*>(p);  // inside the 256 spare bytes
+    a->wide_flag = a->fail_flag + 1;
+    a->path = -1;  // resolved at launch: wt_select_path()
     a->stamps = nullptr;  // tuning aid, set by the plan when WT_SELECT_STAMPS is in the environment
     a->cta_tiles = nullptr;
     a->cta_job = nullptr;
@@ -732,36 +1102,53 @@ int wt_select_grid(int n_tiles, int* grid_out) {
     return WT_OK;
 }
 
-void wt_select_balance(const WtSelJob* jobs, int n_jobs, int n_tiles, int grid, int* tiles_out, int* job_out) {
-    // total cost with one segment per job, then cut greedily; a cut inside a job adds one more segment
-    long long total = (long long)n_tiles + (long long)WT_SEL_SEGMENT_COST * n_jobs;
-    int cta = 0, j = 0;
-    long long acc = 0, spent = 0;
-    tiles_out[0] = 0;
-    job_out[0] = 0;
-    for (int tile = 0; tile < n_tiles; ++tile) {
-        while (j + 1 < n_jobs && tile >= jobs[j].tile_begin + jobs[j].n_tiles) ++j;
-        const bool new_seg = (tile == tiles_out[cta]) || (tile == jobs[j].tile_begin);
-        acc += 1 + (new_seg ? WT_SEL_SEGMENT_COST : 0);
-        // target for the CTAs still to fill, from the cost still to place
-        const int left_ctas = grid - cta;
-        const long long remaining = total - spent;
-        const long long target = (remaining + left_ctas - 1) / left_ctas;
-        const int tiles_left = n_tiles - (tile + 1);
-        if (cta + 1 < grid && (acc >= target || tiles_left <= (grid - cta - 1))) {
-            if (tiles_left == 0) break;
-            spent += acc;
-            acc = 0;
-            ++cta;
-            tiles_out[cta] = tile + 1;
-            int jn = j;
-            while (jn + 1 < n_jobs && tile + 1 >= jobs[jn].tile_begin + jobs[jn].n_tiles) ++jn;
-            job_out[cta] = jn;
-            if (tile + 1 != jobs[jn].tile_begin) total += WT_SEL_SEGMENT_COST;  // the cut split a job
+// Contiguous split of the tile space that minimises the largest CTA cost, cost = tiles + seg_cost per segment (a
+// segment = the piece of one job inside one CTA: every phase pays a scan, a histogram clear and a flush for it).
+// Greedy packing under a capacity, smallest feasible capacity by bisection.
+static int pack_tiles(const WtSelJob* jobs, int n_jobs, int grid, long long cap, int seg_cost, int* tiles_out, int* job_out) {
+    int cta = 0;
+    long long room = cap;
+    if (tiles_out) { tiles_out[0] = 0; job_out[0] = 0; }
+    for (int j = 0; j < n_jobs; ++j) {
+        int left = jobs[j].n_tiles, tile = jobs[j].tile_begin;
+        while (left > 0) {
+            if (room <= seg_cost) {  // not even one tile of a new segment fits: next CTA
+                ++cta;
+                room = cap;
+                if (tiles_out && cta < grid) { tiles_out[cta] = tile; job_out[cta] = j; }
+                if (cta >= grid && !tiles_out) return cta + 1;
+            }
+            long long take = room - seg_cost;
+            if (take > left) take = left;
+            room -= seg_cost + take;
+            left -= (int)take;
+            tile += (int)take;
         }
     }
-    for (int c = cta + 1; c <= grid; ++c) tiles_out[c] = n_tiles;  // unused CTAs get empty ranges
-    for (int c = cta + 1; c < grid; ++c) job_out[c] = n_jobs > 0 ? n_jobs - 1 : 0;
+    return cta + 1;  // CTAs used
+}
+
+void wt_select_balance(const WtSelJob* jobs, int n_jobs, int n_tiles, int grid, int* tiles_out, int* job_out) {
+    static const int seg_cost = [] { const char* e = getenv("WT_SEL_SEGMENT_COST"); return e ? atoi(e) : WT_SEL_SEGMENT_COST; }();
+    long long lo = seg_cost + 1, hi = (long long)n_tiles + (long long)seg_cost * n_jobs + 1;
+    while (lo < hi) {
+        const long long mid = (lo + hi) / 2;
+        if (pack_tiles(jobs, n_jobs, grid, mid, seg_cost, nullptr, nullptr) <= grid) hi = mid; else lo = mid + 1;
+    }
+    const int used = pack_tiles(jobs, n_jobs, grid, lo, seg_cost, tiles_out, job_out);
+    for (int c = used; c <= grid; ++c) tiles_out[c] = n_tiles;  // unused CTAs get empty ranges
+    for (int c = used; c < grid; ++c) job_out[c] = n_jobs > 0 ? n_jobs - 1 : 0;
+}
+
+// Which path a launch over n_tiles tiles takes.  Measured on one B200 (tools/select_probe.py, tools/bank_probe.py): the
+// sampled path saves one of the two full passes but runs one or two more phases, each worth 6..8 us of barrier,
+// scan and flush latency whatever the size; it loses by 10 % at 31 M keys (ResNet-18 coefficients) and wins by 25 %
+// at 67 M.  WT_SELECT_PATH=radix|sampled (read at every launch) overrides.
+int wt_select_path(int n_tiles) {
+    const char* e = getenv("WT_SELECT_PATH");
+    if (e && !strcmp(e, "radix")) return 1;
+    if (e && !strcmp(e, "sampled")) return 0;
+    return n_tiles >= WT_SEL_SAMPLED_MIN_TILES ? 0 : 1;
 }
 
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
@@ -770,6 +1157,7 @@ int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
     if (rc) return rc;
     const size_t smem = sizeof(Shared);
     WtSelArgs a = args;
+    a.path = wt_select_path(a.n_tiles);
     int do_apply = a.any_apply;  // jobs without `out` skip the apply loop inside P4
     void* params[] = {&a, &do_apply};
     WT_CUDA(cudaLaunchCooperativeKernel((const void*)wt_select_kernel, dim3(grid), dim3(WT_SEL_THREADS), params, smem, stream));
