@@ -125,6 +125,23 @@ def test_generic_packed_coefficients_bitwise(mods, wavelet, mode):
 
 
 @pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
+@pytest.mark.parametrize('wavelet', ['haar', 'db4', 'bior4.4', 'coif3'])
+def test_generic_large_planes_bitwise(mods, wavelet, mode):
+    """planes large enough for the fixed-geometry analysis kernel (full 32 x 64 tiles, >= 296 CTAs): partial edge
+    tiles, row strides that allow / forbid the 16-byte staging and the float2 stores, two levels"""
+    eng, o = mods['eng'], mods['o']
+    rng = np.random.default_rng(5)
+    for (B, H, W) in [(3, 1000, 1100), (2, 1030, 1101), (1, 2048, 2048)]:
+        x = (rng.standard_normal((B, H, W)) * 0.02).astype(np.float32)
+        want = o.wavedec2_packed(x, wavelet, 2, mode)
+        got = eng.wavedec2_packed(torch.from_numpy(x).cuda(), wavelet, 2, mode)
+        assert_bit_equal(got, torch.from_numpy(want), f'dec {wavelet} {mode} {H}x{W}')
+        rec_want = o.waverec2_packed(want, x.shape, wavelet, 2, mode)[:, :H, :W]
+        rec_got = eng.waverec2_packed(got, x.shape, wavelet, 2, mode)
+        assert_bit_equal(rec_got, torch.from_numpy(np.ascontiguousarray(rec_want)), f'rec {wavelet} {mode} {H}x{W}')
+
+
+@pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
 def test_generic_path_prune_flows(mods, mode):
     dp, ne, rf = mods['dp'], mods['ne'], mods['rf']
     g = torch.Generator().manual_seed(11)

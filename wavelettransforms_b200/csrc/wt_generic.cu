@@ -9,6 +9,8 @@
 // (the index map handles wrap-around and reflection for any N, including N < F), the first axis
 // pass writes its intermediate to shared memory, the second pass writes the result.  Arithmetic and
 // accumulation order are those of oracle/dwt_oracle.c (fp32, no FMA).
+#include <cstdlib>
+
 #include "wt_generic.cuh"
 
 namespace {
@@ -143,6 +145,137 @@ wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_const
                 P.ad.p[pl * P.ad.pstride + o * P.ad.rstride + c] = sad;
                 P.da.p[pl * P.da.pstride + o * P.da.rstride + c] = sda;
                 P.dd.p[pl * P.dd.pstride + o * P.dd.rstride + c] = sdd;
+            }
+        }
+    }
+}
+
+// ---- large-plane fast path: fixed 32 x 64 output tile, one plane per CTA ----------------------------------------
+// Same arithmetic and accumulation order as wt_generic_analysis_kernel; what changes is the instruction count (ncu:
+// the runtime-geometry kernel issues ~119 thread-instructions per input element against ~32 no-FMA flops):
+// every shared-memory stride is a compile-time constant (LDS with immediate offsets instead of an IMAD + LEA per
+// tap), the axis -2 pass computes two output rows per thread from one column of F + 2 staged values (they share
+// F - 2 of them), the axis -1 pass computes two adjacent output columns per thread from 64-bit shared loads and
+// stores float2s.
+constexpr int FX_T2R = 32, FX_T2C = 64;
+constexpr int FX_HALF = 80;          // even (8-byte aligned odd half) and = 16 mod 32 (de-interleaving stores conflict-free)
+constexpr int FX_LW = 2 * FX_HALF;
+template <int F> struct FxGeom {
+    static constexpr int IR = 2 * FX_T2R + F - 2, IC = 2 * FX_T2C + F - 2, ICS = (IC + 3 + 3) & ~3;
+    static constexpr int SMEM_FLOATS_ = IR * ICS + 2 * FX_T2R * FX_LW;
+    static_assert((IC + 1) / 2 <= FX_HALF, "tile wider than the de-interleaved row");
+    static_assert(SMEM_FLOATS_ <= SMEM_FLOATS, "fixed tile does not fit");
+};
+
+template <int F, int MODE>
+__global__ void __launch_bounds__(GEN_THREADS)
+wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ AnaParams P) {
+    extern __shared__ float smem[];
+    using G = FxGeom<F>;
+    constexpr int IR = G::IR, IC = G::IC, ICS = G::ICS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile_c = blockIdx.x % P.tiles_c;
+    const int tile_r = (blockIdx.x / P.tiles_c) % P.tiles_r;
+    const long long pl = blockIdx.x / (P.tiles_c * P.tiles_r);
+    const int o0 = tile_r * FX_T2R, c0 = tile_c * FX_T2C;
+    constexpr int base = (MODE == WT_MODE_PERIODIZATION) ? F / 2 : 1;
+    const int r_start = base + 2 * o0 - (F - 1), c_start = base + 2 * c0 - (F - 1);
+    const int c_al = (c_start >> 2) << 2;
+    const int shift = c_start - c_al;
+    float* s_in = smem;                 // [IR][ICS]
+    float* s_lo = s_in + IR * ICS;      // [T2R][LW]: even columns at [0, HALF), odd columns at [HALF, LW)
+    float* s_hi = s_lo + FX_T2R * FX_LW;
+    const int rows_valid = min(FX_T2R, P.h2 - o0), cols_valid = min(FX_T2C, P.w2 - c0);
+    const bool vec = c_al >= 0 && c_al + ICS <= P.w && (P.in.rstride & 3) == 0 && (P.in.pstride & 3) == 0 &&
+                     (reinterpret_cast<uintptr_t>(P.in.p) & 15u) == 0;
+    {
+        const float* __restrict__ plane = P.in.p + pl * P.in.pstride;
+        for (int rr = warp; rr < IR; rr += NWARP) {
+            const float* __restrict__ row = plane + (long long)ext_index<MODE>(r_start + rr, P.h) * P.in.rstride;
+            float* dst = s_in + rr * ICS;
+            if (vec) {
+                for (int v = lane; v < ICS / 4; v += 32) cp_async16(dst + 4 * v, row + c_al + 4 * v);
+            } else {
+                for (int cc = lane; cc < ICS; cc += 32) cp_async4(dst + cc, row + ext_index<MODE>(c_al + cc, P.w));
+            }
+        }
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    // axis -2: output rows ol and ol + 1 of column cc from staged rows 2*ol .. 2*ol + F + 1
+    for (int ol = 2 * warp; ol < FX_T2R; ol += 2 * NWARP) {
+        const float* col = s_in + (2 * ol) * ICS + shift;
+        for (int cc = lane; cc < IC; cc += 32) {
+            float v[F + 2];
+#pragma unroll
+            for (int k = 0; k < F + 2; ++k) v[k] = col[k * ICS + cc];
+            float sl0 = 0.0f, sh0 = 0.0f, sl1 = 0.0f, sh1 = 0.0f;
+#pragma unroll
+            for (int j = 0; j < F; ++j) {  // tap j of output row ol + q reads staged row 2*(ol + q) + F-1-j
+                sl0 = __fadd_rn(sl0, __fmul_rn(bk.dec_lo[j], v[F - 1 - j]));
+                sh0 = __fadd_rn(sh0, __fmul_rn(bk.dec_hi[j], v[F - 1 - j]));
+                sl1 = __fadd_rn(sl1, __fmul_rn(bk.dec_lo[j], v[F + 1 - j]));
+                sh1 = __fadd_rn(sh1, __fmul_rn(bk.dec_hi[j], v[F + 1 - j]));
+            }
+            const int d = (cc & 1) * FX_HALF + (cc >> 1);
+            s_lo[ol * FX_LW + d] = sl0;
+            s_hi[ol * FX_LW + d] = sh0;
+            s_lo[(ol + 1) * FX_LW + d] = sl1;
+            s_hi[(ol + 1) * FX_LW + d] = sh1;
+        }
+    }
+    __syncthreads();
+    // axis -1: output columns cl = 2*lane and cl + 1.  Tile column m = 2*c + F-1-j of output column c lives at
+    // [(m & 1) * HALF + (m >> 1)] = [parity_j * HALF + c + ((F-1-j) >> 1)]: both outputs read E[0 .. F/2], O[0 .. F/2]
+    constexpr int NV2 = (F / 2 + 2) / 2;  // float2 loads per half row
+    const bool st2 = ((reinterpret_cast<uintptr_t>(P.aa.p) | reinterpret_cast<uintptr_t>(P.da.p) |
+                       reinterpret_cast<uintptr_t>(P.ad.p) | reinterpret_cast<uintptr_t>(P.dd.p)) & 7u) == 0 &&
+                     ((P.aa.rstride | P.da.rstride | P.ad.rstride | P.dd.rstride | P.aa.pstride | P.da.pstride | P.ad.pstride |
+                       P.dd.pstride) & 1) == 0;
+    const int cl = 2 * lane;
+    for (int ol = warp; ol < rows_valid; ol += NWARP) {
+        const float2* rl = reinterpret_cast<const float2*>(s_lo + ol * FX_LW) + lane;
+        const float2* rh = reinterpret_cast<const float2*>(s_hi + ol * FX_LW) + lane;
+        float le[2 * NV2], lo_[2 * NV2], he[2 * NV2], ho[2 * NV2];
+#pragma unroll
+        for (int i = 0; i < NV2; ++i) {
+            const float2 a = rl[i], b = rl[FX_HALF / 2 + i], c = rh[i], d = rh[FX_HALF / 2 + i];
+            le[2 * i] = a.x; le[2 * i + 1] = a.y;
+            lo_[2 * i] = b.x; lo_[2 * i + 1] = b.y;
+            he[2 * i] = c.x; he[2 * i + 1] = c.y;
+            ho[2 * i] = d.x; ho[2 * i + 1] = d.y;
+        }
+        float saa[2] = {0.0f, 0.0f}, sad[2] = {0.0f, 0.0f}, sda[2] = {0.0f, 0.0f}, sdd[2] = {0.0f, 0.0f};
+#pragma unroll
+        for (int j = 0; j < F; ++j) {
+            constexpr int dummy = 0;
+            (void)dummy;
+            const int par = (F - 1 - j) & 1, sft = (F - 1 - j) >> 1;
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const float vl = par ? lo_[q + sft] : le[q + sft];
+                const float vh = par ? ho[q + sft] : he[q + sft];
+                saa[q] = __fadd_rn(saa[q], __fmul_rn(bk.dec_lo[j], vl));
+                sad[q] = __fadd_rn(sad[q], __fmul_rn(bk.dec_hi[j], vl));
+                sda[q] = __fadd_rn(sda[q], __fmul_rn(bk.dec_lo[j], vh));
+                sdd[q] = __fadd_rn(sdd[q], __fmul_rn(bk.dec_hi[j], vh));
+            }
+        }
+        const long long o = o0 + ol;
+        const int c = c0 + cl;
+        float* paa = P.aa.p + pl * P.aa.pstride + o * P.aa.rstride + c;
+        float* pad = P.ad.p + pl * P.ad.pstride + o * P.ad.rstride + c;
+        float* pda = P.da.p + pl * P.da.pstride + o * P.da.rstride + c;
+        float* pdd = P.dd.p + pl * P.dd.pstride + o * P.dd.rstride + c;
+        if (cl + 1 < cols_valid && st2) {
+            *reinterpret_cast<float2*>(paa) = make_float2(saa[0], saa[1]);
+            *reinterpret_cast<float2*>(pad) = make_float2(sad[0], sad[1]);
+            *reinterpret_cast<float2*>(pda) = make_float2(sda[0], sda[1]);
+            *reinterpret_cast<float2*>(pdd) = make_float2(sdd[0], sdd[1]);
+        } else {
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                if (cl + q < cols_valid) { paa[q] = saa[q]; pad[q] = sad[q]; pda[q] = sda[q]; pdd[q] = sdd[q]; }
             }
         }
     }
@@ -422,8 +555,14 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     const long long grid = groups * P.tiles_r * P.tiles_c;
     WT_CHECK(grid < 2147483647LL, WT_E_UNSUPPORTED, "generic analysis grid too large");
     const size_t smem = (size_t)pb * per_plane * sizeof(float);
+    // large planes: the fixed-geometry kernel (full-size tiles, one plane per CTA)
+    const bool fixed = P.t2r == FX_T2R && P.t2c == FX_T2C && pb == 1 && !getenv("WT_GENERIC_NO_FIXED");
 #define WT_GEN_LAUNCH(FL, MD)                                                                                     \
-    {                                                                                                             \
+    if (fixed) {                                                                                                  \
+        auto kern = wt_generic_analysis_fixed_kernel<FL, MD>;                                                     \
+        WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
+        kern<<<(unsigned)grid, GEN_THREADS, FxGeom<FL>::SMEM_FLOATS_ * sizeof(float), stream>>>(bank, P);         \
+    } else {                                                                                                      \
         auto kern = wt_generic_analysis_kernel<FL, MD>;                                                           \
         WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
         kern<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);                                             \
@@ -448,11 +587,18 @@ int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView d
     while ((long long)((oh + P.tr - 1) / P.tr) * ((ow + P.tc - 1) / P.tc) * batch < 296 && (P.tr > 8 || P.tc > 32)) {
         if (P.tc > 32 && P.tc >= 2 * P.tr) P.tc /= 2; else if (P.tr > 8) P.tr /= 2; else P.tc /= 2;
     }
-    P.tiles_r = (oh + P.tr - 1) / P.tr;
-    P.tiles_c = (ow + P.tc - 1) / P.tc;
-    P.cr = P.tr / 2 + bank.F / 2 + 2;
-    P.cc = P.tc / 2 + bank.F / 2 + 2;
-    P.ccs = (P.cc + 3 + 3) & ~3;
+    auto geometry = [&]() {
+        P.tiles_r = (oh + P.tr - 1) / P.tr;
+        P.tiles_c = (ow + P.tc - 1) / P.tc;
+        P.cr = P.tr / 2 + bank.F / 2 + 2;
+        P.cc = P.tc / 2 + bank.F / 2 + 2;
+        P.ccs = (P.cc + 3 + 3) & ~3;
+        return 4LL * P.cr * P.ccs + 2LL * P.cr * P.tc;
+    };
+    // the longest banks (F = 18) do not fit a full 64 x 128 tile next to its four staged sub-band tiles
+    while (geometry() > SMEM_FLOATS && (P.tr > 8 || P.tc > 32)) {
+        if (P.tr > 8) P.tr /= 2; else P.tc /= 2;
+    }
     P.thr_dev = thr_dev; P.thr_host = thr_host; P.use_thr = use_thr; P.thr_a = thr_a; P.counts4 = counts4;
     const long long per_plane = 4LL * P.cr * P.ccs + 2LL * P.cr * P.tc;
     long long pb = SMEM_FLOATS / per_plane;
