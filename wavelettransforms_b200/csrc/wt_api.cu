@@ -208,7 +208,9 @@ struct WtPlan {
     std::vector<unsigned int*> d_cand;  // candidate-key lists of the select fast path
     std::vector<unsigned int> cand_cap;
     std::vector<long long> ncoef, zeros;  // per layer: explicit coefficients / implicit padding zeros
-    float *tmp0 = nullptr, *tmp1 = nullptr;
+    // generic layers are dealt round-robin to `gen_lanes` streams; a lane owns one pair of ping-pong buffers
+    std::vector<float*> tmp0, tmp1;
+    int gen_lanes = 1;
     int n_launches = 0;
 
     // optional per-phase device timing (wt_plan_set_timing): events[i] is recorded before phase i,
@@ -270,7 +272,8 @@ static int build_tables(WtPlan* P) {
             WtGenericLayer g;
             memset(&g, 0, sizeof(g));
             g.in = P->d_in[i]; g.out = P->d_out[i]; g.batch = L.batch; g.H = L.H; g.W = L.W; g.level = L.level;
-            g.layer = i; g.coef = P->d_coef[i]; g.tmp0 = P->tmp0; g.tmp1 = P->tmp1;
+            g.layer = i; g.coef = P->d_coef[i];
+            g.tmp0 = P->tmp0[P->generic.size() % P->gen_lanes]; g.tmp1 = P->tmp1[P->generic.size() % P->gen_lanes];
             g.abs_threshold = (float)P->thr_value; g.use_abs = pct ? 0 : 1;
             P->generic.push_back(g);
         } else if (!pct) {
@@ -561,8 +564,14 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
                 P->cand_cap[i] = wt_select_cand_cap(pop);
                 off_cand[i] = take((size_t)P->cand_cap[i] * sizeof(unsigned int));
             }
-    const size_t off_tmp0 = take((size_t)tmp_elems * sizeof(float));
-    const size_t off_tmp1 = take((size_t)tmp_elems * sizeof(float));
+    int n_generic = 0;
+    for (int i = 0; i < n_layers; ++i) n_generic += (P->path[i] == PATH_GENERIC);
+    P->gen_lanes = std::max(1, std::min(n_generic, 4));
+    std::vector<size_t> off_tmp0(P->gen_lanes), off_tmp1(P->gen_lanes);
+    for (int q = 0; q < P->gen_lanes; ++q) {
+        off_tmp0[q] = take((size_t)tmp_elems * sizeof(float));
+        off_tmp1[q] = take((size_t)tmp_elems * sizeof(float));
+    }
     if (host_io)
         for (int i = 0; i < n_layers; ++i)
             if (P->path[i] != PATH_EMPTY) off_io[i] = take((size_t)layer_numel(P->layers[i]) * sizeof(float));
@@ -589,8 +598,10 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
             cudaMemset(P->stamps_dev, 0, (size_t)WT_SEL_STAMP_CTAS * 16 * 8);
         P->sel_args.stamps = P->stamps_dev;
     }
-    P->tmp0 = reinterpret_cast<float*>(P->dev + off_tmp0);
-    P->tmp1 = reinterpret_cast<float*>(P->dev + off_tmp1);
+    for (int q = 0; q < P->gen_lanes; ++q) {
+        P->tmp0.push_back(reinterpret_cast<float*>(P->dev + off_tmp0[q]));
+        P->tmp1.push_back(reinterpret_cast<float*>(P->dev + off_tmp1[q]));
+    }
     for (int i = 0; i < n_layers; ++i) {
         if (P->path[i] == PATH_EMPTY) continue;
         if (P->path[i] != PATH_LEVEL0) P->d_coef[i] = reinterpret_cast<float*>(P->dev + off_coef[i]);
@@ -602,9 +613,10 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
             P->d_out[i] = P->layers[i].out;
         }
     }
-    if (P->small.size() > 1) {
+    const size_t n_streams = std::max(P->small.size(), (size_t)P->gen_lanes);
+    if (n_streams > 1) {
         bool ok = cudaEventCreateWithFlags(&P->ev_fork, cudaEventDisableTiming) == cudaSuccess;
-        for (size_t k = 1; ok && k < P->small.size(); ++k) {
+        for (size_t k = 1; ok && k < n_streams; ++k) {
             cudaStream_t q;
             cudaEvent_t ev;
             ok = cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking) == cudaSuccess;
@@ -719,10 +731,11 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         if (rc) return rc;
         if (c.n_tiles) ++launches;
     }
+    int gi = 0;
     for (auto& g : P->generic) {
         snprintf(label, sizeof(label), "generic_analysis_layer%d", g.layer);
         mark(label);
-        rc = wt_generic_analysis(P->bank, P->mode, g, P->counts_dev, stream, &launches);
+        rc = wt_generic_analysis(P->bank, P->mode, g, P->counts_dev, class_stream((size_t)(gi++ % P->gen_lanes)), &launches);
         if (rc) return rc;
     }
     if ((rc = join())) return rc;
@@ -754,10 +767,12 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         if (rc) return rc;
         if (c.n_tiles) ++launches;
     }
+    gi = 0;
     for (auto& g : P->generic) {
         snprintf(label, sizeof(label), "generic_synthesis_layer%d", g.layer);
         mark(label);
-        rc = wt_generic_synthesis(P->bank, P->mode, g, P->thresholds_dev, P->counts_dev, stream, &launches);
+        rc = wt_generic_synthesis(P->bank, P->mode, g, P->thresholds_dev, P->counts_dev, class_stream((size_t)(gi++ % P->gen_lanes)),
+                                  &launches);
         if (rc) return rc;
     }
     if ((rc = join())) return rc;

@@ -16,7 +16,7 @@
 namespace {
 
 constexpr int GEN_THREADS = 256;
-constexpr int SMEM_FLOATS = 24000;  // up to 96 KB of dynamic shared memory per CTA (2 CTAs per SM)
+constexpr int SMEM_FLOATS = 27000;  // up to 108 KB of dynamic shared memory per CTA (2 CTAs per SM)
 
 // 4-byte asynchronous global -> shared copy (SASS LDGSTS): a thread issues its whole share of a tile
 // back to back and waits once, so the staging loop is not bound by one load latency per element
@@ -460,6 +460,182 @@ wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_cons
     }
 }
 
+// ---- large-plane fast path of the synthesis: fixed TR x 128 output tile, one plane per CTA ----------------------
+// Same arithmetic and accumulation order as wt_generic_synthesis_kernel.  Output samples 2u and 2u + 1 (in the
+// shifted index q of syn_index) read the SAME hf coefficients of each band and differ only in the tap parity, so a
+// thread computes both from one set of shared-memory loads with compile-time tap indices (the runtime-geometry
+// kernel loads twice and selects every tap by parity), on both axes; the axis -1 result is stored with the two
+// parities de-interleaved so that neither pass has a shared-memory bank conflict.
+constexpr int FS_TC = 128;
+constexpr int FS_HALF = 80;  // >= TC/2 + 1 pairs, = 16 mod 32
+constexpr int FS_TW = 2 * FS_HALF;
+template <int F, int TR> struct FsGeom {
+    static constexpr int hf = F / 2;
+    static constexpr int CR = TR / 2 + hf + 2, CC = FS_TC / 2 + hf + 2, CCS = (CC + 3 + 3) & ~3;
+    static constexpr int SMEM_FLOATS_ = 4 * CR * CCS + 2 * CR * FS_TW;
+};
+// tile height of the fixed kernel for filter length F: 64 rows when the tile fits shared memory, else 32
+template <int F> constexpr int fs_tr() { return FsGeom<F, 64>::SMEM_FLOATS_ <= SMEM_FLOATS ? 64 : 32; }
+
+// the two outputs (tap parity 0, 1) fed by coefficients a[0], a[-stride], ..., a[-(hf-1)*stride] and the same of d
+template <int F, int MODE, int STRIDE>
+__device__ __forceinline__ void syn_pair(const float* a, const float* d, const WtBank& bk, float& o0, float& o1) {
+    constexpr int hf = F / 2;
+    float va[hf], vd[hf];
+#pragma unroll
+    for (int j = 0; j < hf; ++j) { va[j] = a[-j * STRIDE]; vd[j] = d[-j * STRIDE]; }
+    if (MODE == WT_MODE_PERIODIZATION) {
+        float e = 0.0f, o = 0.0f;
+#pragma unroll
+        for (int j = 0; j < hf; ++j) {
+            e = __fadd_rn(e, __fmul_rn(bk.rec_lo[2 * j], va[j]));
+            o = __fadd_rn(o, __fmul_rn(bk.rec_lo[2 * j + 1], va[j]));
+        }
+#pragma unroll
+        for (int j = 0; j < hf; ++j) {
+            e = __fadd_rn(e, __fmul_rn(bk.rec_hi[2 * j], vd[j]));
+            o = __fadd_rn(o, __fmul_rn(bk.rec_hi[2 * j + 1], vd[j]));
+        }
+        o0 = e; o1 = o;
+    } else {
+        float le = 0.0f, lo = 0.0f, he = 0.0f, ho = 0.0f;
+#pragma unroll
+        for (int j = 0; j < hf; ++j) {
+            le = __fadd_rn(le, __fmul_rn(bk.rec_lo[2 * j], va[j]));
+            lo = __fadd_rn(lo, __fmul_rn(bk.rec_lo[2 * j + 1], va[j]));
+        }
+#pragma unroll
+        for (int j = 0; j < hf; ++j) {
+            he = __fadd_rn(he, __fmul_rn(bk.rec_hi[2 * j], vd[j]));
+            ho = __fadd_rn(ho, __fmul_rn(bk.rec_hi[2 * j + 1], vd[j]));
+        }
+        o0 = __fadd_rn(__fadd_rn(0.0f, le), he);
+        o1 = __fadd_rn(__fadd_rn(0.0f, lo), ho);
+    }
+}
+
+template <int F, int MODE, int TR>
+__global__ void __launch_bounds__(GEN_THREADS)
+wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ SynParams P) {
+    extern __shared__ float smem[];
+    using G = FsGeom<F, TR>;
+    constexpr int hf = F / 2, CR = G::CR, CCS = G::CCS;
+    // q = o - SH is the index whose parity picks the taps (syn_index)
+    constexpr int SH = (MODE == WT_MODE_PERIODIZATION && (hf % 2 == 0)) ? 1 : 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile_c = blockIdx.x % P.tiles_c;
+    const int tile_r = (blockIdx.x / P.tiles_c) % P.tiles_r;
+    const long long pl = blockIdx.x / (P.tiles_c * P.tiles_r);
+    const int R0 = tile_r * TR, C0 = tile_c * FS_TC;
+    int iv0, par0;
+    syn_index<F, MODE>(R0, &iv0, &par0);
+    const int row_lo = iv0 - (hf - 1);
+    syn_index<F, MODE>(C0, &iv0, &par0);
+    const int col_lo0 = iv0 - (hf - 1);
+    const int col_lo = (col_lo0 >> 2) << 2;
+    const int d0 = col_lo0 - col_lo;
+    constexpr int band = CR * CCS;
+    float* s_aa = smem;
+    float* s_da = s_aa + band;
+    float* s_ad = s_da + band;
+    float* s_dd = s_ad + band;
+    float* s_lo = s_dd + band;  // [CR][TW]: pair t of parity p at [p * HALF + t]
+    float* s_hi = s_lo + CR * FS_TW;
+    const float t = P.use_thr ? (P.thr_dev ? __ldg(P.thr_dev) : P.thr_host) : 0.0f;
+    const bool thr = P.use_thr != 0, thr_a = thr && P.thr_a != 0;
+    const int rows_valid = min(TR, P.oh - R0), cols_valid = min(FS_TC, P.ow - C0);
+
+    auto aligned_view = [](const WtView& v) {
+        return (reinterpret_cast<uintptr_t>(v.p) & 15u) == 0 && (v.rstride & 3) == 0 && (v.pstride & 3) == 0;
+    };
+    const bool vec = col_lo >= 0 && col_lo + CCS <= P.w2 && aligned_view(P.aa) && aligned_view(P.da) && aligned_view(P.ad) &&
+                     aligned_view(P.dd);
+    for (int r2 = warp; r2 < CR; r2 += NWARP) {
+        const long long sr = syn_map<MODE>(row_lo + r2, P.h2);
+        const float* __restrict__ raa = P.aa.p + pl * P.aa.pstride + sr * P.aa.rstride;
+        const float* __restrict__ rda = P.da.p + pl * P.da.pstride + sr * P.da.rstride;
+        const float* __restrict__ rad = P.ad.p + pl * P.ad.pstride + sr * P.ad.rstride;
+        const float* __restrict__ rdd = P.dd.p + pl * P.dd.pstride + sr * P.dd.rstride;
+        const int off = r2 * CCS;
+        if (vec) {
+            for (int v = lane; v < CCS / 4; v += 32) {
+                cp_async16(s_aa + off + 4 * v, raa + col_lo + 4 * v);
+                cp_async16(s_da + off + 4 * v, rda + col_lo + 4 * v);
+                cp_async16(s_ad + off + 4 * v, rad + col_lo + 4 * v);
+                cp_async16(s_dd + off + 4 * v, rdd + col_lo + 4 * v);
+            }
+        } else {
+            for (int c2 = lane; c2 < CCS; c2 += 32) {
+                const int sc = syn_map<MODE>(col_lo + c2, P.w2);
+                cp_async4(s_aa + off + c2, raa + sc);
+                cp_async4(s_da + off + c2, rda + sc);
+                cp_async4(s_ad + off + c2, rad + sc);
+                cp_async4(s_dd + off + c2, rdd + sc);
+            }
+        }
+    }
+    cp_async_wait_all();
+    if (thr) {  // np.where(|c| < t, 0, c): every thread sweeps exactly the elements it copied
+        for (int r2 = warp; r2 < CR; r2 += NWARP) {
+            const int off = r2 * CCS;
+            for (int i = lane; i < (vec ? CCS / 4 : CCS); i += 32)
+            for (int c2 = vec ? 4 * i : i; c2 < (vec ? 4 * i + 4 : i + 1); ++c2) {
+                if (thr_a && fabsf(s_aa[off + c2]) < t) s_aa[off + c2] = 0.0f;
+                if (fabsf(s_da[off + c2]) < t) s_da[off + c2] = 0.0f;
+                if (fabsf(s_ad[off + c2]) < t) s_ad[off + c2] = 0.0f;
+                if (fabsf(s_dd[off + c2]) < t) s_dd[off + c2] = 0.0f;
+            }
+        }
+    }
+    __syncthreads();
+    // axis -1 first (idwt2).  Pair tp: q = 2*(tp - SH), q + 1, i.e. tile columns 2*tp - SH and 2*tp - SH + 1; both read
+    // the staged coefficients [tp + hf-1 + d0 - j], j < hf
+    constexpr int NPAIR_C = FS_TC / 2 + SH;
+    for (int r2 = warp; r2 < CR; r2 += NWARP) {
+        const float* aa = s_aa + r2 * CCS + (hf - 1) + d0;
+        const float* ad = s_ad + r2 * CCS + (hf - 1) + d0;
+        const float* da = s_da + r2 * CCS + (hf - 1) + d0;
+        const float* dd = s_dd + r2 * CCS + (hf - 1) + d0;
+        for (int tp = lane; tp < NPAIR_C; tp += 32) {
+            float l0, l1, h0, h1;
+            syn_pair<F, MODE, 1>(aa + tp, ad + tp, bk, l0, l1);
+            syn_pair<F, MODE, 1>(da + tp, dd + tp, bk, h0, h1);
+            s_lo[r2 * FS_TW + tp] = l0;
+            s_lo[r2 * FS_TW + FS_HALF + tp] = l1;
+            s_hi[r2 * FS_TW + tp] = h0;
+            s_hi[r2 * FS_TW + FS_HALF + tp] = h1;
+        }
+    }
+    __syncthreads();
+    // axis -2: row pair tp (tile rows 2*tp - SH, 2*tp - SH + 1) of column cl reads intermediate rows tp + hf-1 - j
+    unsigned int zc = 0, wr = 0;
+    constexpr int NPAIR_R = TR / 2 + SH;
+    float* __restrict__ plane = P.out.p + pl * P.out.pstride + C0;
+    for (int tp = warp; tp < NPAIR_R; tp += NWARP) {
+        const int rl0 = 2 * tp - SH;
+        const bool ok0 = rl0 >= 0 && rl0 < rows_valid, ok1 = rl0 + 1 < rows_valid;
+        if (!ok0 && !ok1) continue;
+        for (int cl = lane; cl < cols_valid; cl += 32) {
+            const int idx = ((cl + SH) & 1) * FS_HALF + ((cl + SH) >> 1);
+            float v0, v1;
+            syn_pair<F, MODE, FS_TW>(s_lo + (tp + hf - 1) * FS_TW + idx, s_hi + (tp + hf - 1) * FS_TW + idx, bk, v0, v1);
+            if (ok0) { plane[(long long)(R0 + rl0) * P.out.rstride + cl] = v0; zc += (v0 == 0.0f); ++wr; }
+            if (ok1) { plane[(long long)(R0 + rl0 + 1) * P.out.rstride + cl] = v1; zc += (v1 == 0.0f); ++wr; }
+        }
+    }
+    if (P.counts4) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            zc += __shfl_down_sync(0xffffffffu, zc, d);
+            wr += __shfl_down_sync(0xffffffffu, wr, d);
+        }
+        if (lane == 0 && wr) {
+            atomicAdd(reinterpret_cast<unsigned long long*>(P.counts4 + 2), (unsigned long long)zc);
+            atomicAdd(reinterpret_cast<unsigned long long*>(P.counts4 + 1), (unsigned long long)(wr - zc));
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) wt_count_nonzero_kernel(const float* __restrict__ x, long long n,
                                                                long long* counts4) {
     unsigned int nz = 0;
@@ -610,11 +786,23 @@ int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView d
     const long long grid = groups * P.tiles_r * P.tiles_c;
     WT_CHECK(grid < 2147483647LL, WT_E_UNSUPPORTED, "generic synthesis grid too large");
     const size_t smem = (size_t)pb * per_plane * sizeof(float);
+    // large planes: the fixed-geometry kernel (full-size tiles, one plane per CTA)
+    const bool no_fixed = getenv("WT_GENERIC_NO_FIXED") != nullptr;
 #define WT_GEN_LAUNCH(FL, MD)                                                                                     \
     {                                                                                                             \
-        auto kern = wt_generic_synthesis_kernel<FL, MD>;                                                          \
-        WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
-        kern<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);                                             \
+        constexpr int FTR = fs_tr<FL>();                                                                          \
+        const long long ftiles = (long long)((oh + FTR - 1) / FTR) * ((ow + FS_TC - 1) / FS_TC);                  \
+        if (!no_fixed && oh >= FTR && ow >= FS_TC && ftiles * batch >= 296) {                                     \
+            P.tr = FTR; P.tc = FS_TC; P.pb = 1;                                                                   \
+            geometry();                                                                                           \
+            auto kern = wt_generic_synthesis_fixed_kernel<FL, MD, FTR>;                                           \
+            WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));    \
+            kern<<<(unsigned)(ftiles * batch), GEN_THREADS, FsGeom<FL, FTR>::SMEM_FLOATS_ * sizeof(float), stream>>>(bank, P); \
+        } else {                                                                                                  \
+            auto kern = wt_generic_synthesis_kernel<FL, MD>;                                                      \
+            WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));    \
+            kern<<<(unsigned)grid, GEN_THREADS, smem, stream>>>(bank, P);                                         \
+        }                                                                                                         \
     }
     WT_GEN_DISPATCH(bank.F, mode)
 #undef WT_GEN_LAUNCH
