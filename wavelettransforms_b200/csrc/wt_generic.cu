@@ -157,7 +157,13 @@ wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_const
 // tap), the axis -2 pass computes two output rows per thread from one column of F + 2 staged values (they share
 // F - 2 of them), the axis -1 pass computes two adjacent output columns per thread from 64-bit shared loads and
 // stores float2s.
-constexpr int FX_T2R = 32, FX_T2C = 64;
+#ifndef WT_FX_T2R
+#define WT_FX_T2R 32
+#endif
+#ifndef WT_FS_TR_MAX
+#define WT_FS_TR_MAX 64
+#endif
+constexpr int FX_T2R = WT_FX_T2R, FX_T2C = 64;
 constexpr int FX_HALF = 80;          // even (8-byte aligned odd half) and = 16 mod 32 (de-interleaving stores conflict-free)
 constexpr int FX_LW = 2 * FX_HALF;
 template <int F> struct FxGeom {
@@ -203,9 +209,11 @@ wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid
     cp_async_wait_all();
     __syncthreads();
     // axis -2: output rows ol and ol + 1 of column cc from staged rows 2*ol .. 2*ol + F + 1
-    for (int ol = 2 * warp; ol < FX_T2R; ol += 2 * NWARP) {
+    // (row pair, column) items dealt flat over the CTA: IC is not a multiple of 32
+    for (int it = threadIdx.x; it < (FX_T2R / 2) * IC; it += GEN_THREADS) {
+        const int ol = 2 * (it / IC), cc = it % IC;
         const float* col = s_in + (2 * ol) * ICS + shift;
-        for (int cc = lane; cc < IC; cc += 32) {
+        {
             float v[F + 2];
 #pragma unroll
             for (int k = 0; k < F + 2; ++k) v[k] = col[k * ICS + cc];
@@ -475,7 +483,7 @@ template <int F, int TR> struct FsGeom {
     static constexpr int SMEM_FLOATS_ = 4 * CR * CCS + 2 * CR * FS_TW;
 };
 // tile height of the fixed kernel for filter length F: 64 rows when the tile fits shared memory, else 32
-template <int F> constexpr int fs_tr() { return FsGeom<F, 64>::SMEM_FLOATS_ <= SMEM_FLOATS ? 64 : 32; }
+template <int F> constexpr int fs_tr() { return (WT_FS_TR_MAX >= 64 && FsGeom<F, 64>::SMEM_FLOATS_ <= SMEM_FLOATS) ? 64 : 32; }
 
 // the two outputs (tap parity 0, 1) fed by coefficients a[0], a[-stride], ..., a[-(hf-1)*stride] and the same of d
 template <int F, int MODE, int STRIDE>
@@ -591,12 +599,14 @@ wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __gri
     // axis -1 first (idwt2).  Pair tp: q = 2*(tp - SH), q + 1, i.e. tile columns 2*tp - SH and 2*tp - SH + 1; both read
     // the staged coefficients [tp + hf-1 + d0 - j], j < hf
     constexpr int NPAIR_C = FS_TC / 2 + SH;
-    for (int r2 = warp; r2 < CR; r2 += NWARP) {
+    // (row, pair) items dealt flat over the CTA: neither CR nor NPAIR_C is a multiple of the warp geometry
+    for (int it = threadIdx.x; it < CR * NPAIR_C; it += GEN_THREADS) {
+        const int r2 = it / NPAIR_C, tp = it % NPAIR_C;
         const float* aa = s_aa + r2 * CCS + (hf - 1) + d0;
         const float* ad = s_ad + r2 * CCS + (hf - 1) + d0;
         const float* da = s_da + r2 * CCS + (hf - 1) + d0;
         const float* dd = s_dd + r2 * CCS + (hf - 1) + d0;
-        for (int tp = lane; tp < NPAIR_C; tp += 32) {
+        {
             float l0, l1, h0, h1;
             syn_pair<F, MODE, 1>(aa + tp, ad + tp, bk, l0, l1);
             syn_pair<F, MODE, 1>(da + tp, dd + tp, bk, h0, h1);
@@ -611,11 +621,12 @@ wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __gri
     unsigned int zc = 0, wr = 0;
     constexpr int NPAIR_R = TR / 2 + SH;
     float* __restrict__ plane = P.out.p + pl * P.out.pstride + C0;
-    for (int tp = warp; tp < NPAIR_R; tp += NWARP) {
+    for (int it = threadIdx.x; it < NPAIR_R * FS_TC; it += GEN_THREADS) {  // a warp: 32 columns of one row pair
+        const int tp = it / FS_TC, cl = it % FS_TC;
         const int rl0 = 2 * tp - SH;
         const bool ok0 = rl0 >= 0 && rl0 < rows_valid, ok1 = rl0 + 1 < rows_valid;
         if (!ok0 && !ok1) continue;
-        for (int cl = lane; cl < cols_valid; cl += 32) {
+        if (cl < cols_valid) {
             const int idx = ((cl + SH) & 1) * FS_HALF + ((cl + SH) >> 1);
             float v0, v1;
             syn_pair<F, MODE, FS_TW>(s_lo + (tp + hf - 1) * FS_TW + idx, s_hi + (tp + hf - 1) * FS_TW + idx, bk, v0, v1);
@@ -732,12 +743,18 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     WT_CHECK(grid < 2147483647LL, WT_E_UNSUPPORTED, "generic analysis grid too large");
     const size_t smem = (size_t)pb * per_plane * sizeof(float);
     // large planes: the fixed-geometry kernel (full-size tiles, one plane per CTA)
-    const bool fixed = P.t2r == FX_T2R && P.t2c == FX_T2C && pb == 1 && !getenv("WT_GENERIC_NO_FIXED");
+    const long long ftiles = (long long)((P.h2 + FX_T2R - 1) / FX_T2R) * ((P.w2 + FX_T2C - 1) / FX_T2C);
+    const bool fixed = P.h2 >= FX_T2R && P.w2 >= FX_T2C && ftiles * batch >= 296 && !getenv("WT_GENERIC_NO_FIXED");
+    if (fixed) {
+        P.t2r = FX_T2R; P.t2c = FX_T2C; P.pb = 1;
+        P.tiles_r = (P.h2 + FX_T2R - 1) / FX_T2R;
+        P.tiles_c = (P.w2 + FX_T2C - 1) / FX_T2C;
+    }
 #define WT_GEN_LAUNCH(FL, MD)                                                                                     \
     if (fixed) {                                                                                                  \
         auto kern = wt_generic_analysis_fixed_kernel<FL, MD>;                                                     \
         WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
-        kern<<<(unsigned)grid, GEN_THREADS, FxGeom<FL>::SMEM_FLOATS_ * sizeof(float), stream>>>(bank, P);         \
+        kern<<<(unsigned)(ftiles * batch), GEN_THREADS, FxGeom<FL>::SMEM_FLOATS_ * sizeof(float), stream>>>(bank, P); \
     } else {                                                                                                      \
         auto kern = wt_generic_analysis_kernel<FL, MD>;                                                           \
         WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
