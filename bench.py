@@ -480,6 +480,7 @@ def run_ours(args):
     if not args.no_variants and world == 1:
         line['siblings'] = time_siblings(args.steps, dev)
     if not args.no_variants:
+        line['bank'] = time_bank(args.steps, dev, peak_gbs)
         line['layer_sharded'] = time_layer_sharded(args.sharded_workload, min(args.steps, 100), min(args.warmup, 5), world, dev)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line['cpu_baseline'] = run_cpu_baseline(args.workload, args.cpu_sample_seconds)
@@ -575,6 +576,43 @@ def time_siblings(steps, dev):
         out[which] = {'value': elems * n / dt, 'unit': UNIT, 'ms_per_step': dt / n * 1e3, 'steps': n,
                       'sparsity': 0.5, 'workload': 'resnet18 conv layers, 50 %'}
         del copies
+    return out
+
+
+def time_bank(steps, dev, peak_gbs):
+    """BASELINE config 5 (a slice of the synthetic weight bank per GPU, seeds 1000+i): 32 tensors of 512x512x3x3 and
+    2 matrices of 4096x4096, level-5 db4 at p = 50 through dwt_pruning's clamp (3x3 planes: level 0 = select + zero;
+    4096x4096: the full five-level transform on the generic tiled path).  Device-resident, cudaEvents."""
+    from wavelettransforms_b200 import _lib, engine
+    g = torch.Generator(device=dev).manual_seed(1000)
+    stream = int(torch.cuda.current_stream().cuda_stream)
+    out = {}
+    for label, shapes in (('512x512x3x3 x32 (db4 L5 clamps to level 0)', [(512, 512, 3, 3)] * 32),
+                          ('4096x4096 x2 (db4 L5)', [(4096, 4096)] * 2)):
+        xs = [torch.randn(sh, device=dev, generator=g) * 0.02 for sh in shapes]
+        outs = [torch.empty_like(x) for x in xs]
+        levels = [min(5, _lib.dwt_max_level(min(sh[-2:]), 8)) for sh in shapes]
+        items = [(x.data_ptr(), o.data_ptr()) + engine.plane_geometry(x.shape) + (lv,) for x, o, lv in zip(xs, outs, levels)]
+        plan = _lib.Plan(items, 'db4', 'periodization', _lib.THRESHOLD_PERCENTILE, 50.0, NUMPY_SEMANTICS)
+        n = max(3, min(steps, 20))
+        for _ in range(3):
+            plan.run(stream)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            plan.run(stream)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / n
+        elems = sum(x.numel() for x in xs)
+        gbs = BYTES_PER_ELEM * elems / (ms * 1e-3) / 1e9
+        out[label] = {'value': elems / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms, 'elems': elems, 'steps': n,
+                      'launches_per_step': plan.num_launches, 'hbm_frac_whole_step': gbs / peak_gbs,
+                      'l2_policy': f'inputs + outputs {2 * elems * 4 / 1e6:.0f} MB > 126 MB L2'}
+        plan.close()
+        del xs, outs
+        torch.cuda.empty_cache()
     return out
 
 
