@@ -89,6 +89,14 @@ __device__ __forceinline__ void bin_one(unsigned int key, unsigned int* sh, unsi
     }
 }
 
+// The streaming loops are load -> wait -> process with every warp of the SM in step, so the memory system idles
+// while the SM computes and vice versa; asking L2 for the next iteration's lines before processing this one
+// overlaps the two at no register cost (a software-pipelined register prefetch spills under the 64-register cap).
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#ifndef WT_SEL_PREFETCH
+#define WT_SEL_PREFETCH 1
+#endif
+
 // Calls op(float) on x[0..len): float4 loads, UNROLL of them in flight per thread.
 template <class Op>
 __device__ __forceinline__ void span_for_each(const float* __restrict__ x, long long len, Op op) {
@@ -100,6 +108,11 @@ __device__ __forceinline__ void span_for_each(const float* __restrict__ x, long 
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u)
                 if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
+            if (WT_SEL_PREFETCH) {
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+                    if (v + (long long)(UNROLL + u) * T < nvec) prefetch_l2(&x4[v + (long long)(UNROLL + u) * T]);
+            }
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u)
                 if (v + (long long)u * T < nvec) { op(r[u].x); op(r[u].y); op(r[u].z); op(r[u].w); }
@@ -475,6 +488,11 @@ __device__ void hist2_compact_span(const float* __restrict__ x, long long len, u
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u)
                 if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
+            if (WT_SEL_PREFETCH) {
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+                    if (v + (long long)(UNROLL + u) * T < nvec) prefetch_l2(&x4[v + (long long)(UNROLL + u) * T]);
+            }
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) {
                 const bool ok = v + (long long)u * T < nvec;
@@ -618,6 +636,11 @@ __device__ void range_compact_span(const float* __restrict__ x, long long len, u
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u)
                 if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
+            if (WT_SEL_PREFETCH) {
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+                    if (v + (long long)(UNROLL + u) * T < nvec) prefetch_l2(&x4[v + (long long)(UNROLL + u) * T]);
+            }
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) {
                 const bool ok = v + (long long)u * T < nvec;
@@ -952,6 +975,11 @@ __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u)
                     if (v + (long long)u * T < nvec) r[u] = __ldcg(&x4[v + (long long)u * T]);
+                if (WT_SEL_PREFETCH) {
+#pragma unroll
+                    for (int u = 0; u < UNROLL; ++u)
+                        if (v + (long long)(UNROLL + u) * T < nvec) prefetch_l2(&x4[v + (long long)(UNROLL + u) * T]);
+                }
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u) {
                     if (v + (long long)u * T < nvec) {
