@@ -40,6 +40,16 @@ struct ZeroTaps {
 using NoZeroTaps = ZeroTaps<0, 0, 0, 0>;
 #define WT_TAP(mask, j) ((((mask) >> (j)) & 1u) == 0u)
 
+// Packed fp32x2 additions (Blackwell FADD2): two independent round-to-nearest fp32 additions in one issue slot.
+// Only the ADDS are packed: ptxas contracts mul.rn.f32x2 feeding add.rn.f32x2 into FFMA2 even under -fmad=false,
+// which would change the last bit; scalar FMULs feeding an FADD2 stay as written (checked in the SASS).  The two
+// halves are ordinary registers, so a lane of a pair can still be updated alone by a scalar FADD.
+__device__ __forceinline__ void fadd2(float& a0, float& a1, float p0, float p1) {
+    const float2 r = __fadd2_rn(make_float2(a0, a1), make_float2(p0, p1));
+    a0 = r.x;
+    a1 = r.y;
+}
+
 // single-level 2-D analysis of an H x W plane held in registers (dwt2: axis -2 first, then -1)
 template <int H, int W, int F, class Z>
 __device__ __forceinline__ void dwt2_regs(const float (&x)[H * W], const WtBank& bk, float (&aa)[half_up(H) * half_up(W)],
@@ -55,8 +65,12 @@ __device__ __forceinline__ void dwt2_regs(const float (&x)[H * W], const WtBank&
 #pragma unroll
             for (int j = 0; j < F; ++j) {
                 const float v = x[per_index(F / 2 + 2 * o - j, H) * W + c];
-                if (WT_TAP(Z::dl, j)) sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
-                if (WT_TAP(Z::dh, j)) sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+                if (WT_TAP(Z::dl, j) && WT_TAP(Z::dh, j)) {
+                    fadd2(sl, sh, __fmul_rn(bk.dec_lo[j], v), __fmul_rn(bk.dec_hi[j], v));
+                } else {
+                    if (WT_TAP(Z::dl, j)) sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
+                    if (WT_TAP(Z::dh, j)) sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+                }
             }
             lo[o * W + c] = sl;
             hi[o * W + c] = sh;
@@ -71,14 +85,8 @@ __device__ __forceinline__ void dwt2_regs(const float (&x)[H * W], const WtBank&
             for (int j = 0; j < F; ++j) {
                 const int m = per_index(F / 2 + 2 * o - j, W);
                 const float vl = lo[r * W + m], vh = hi[r * W + m];
-                if (WT_TAP(Z::dl, j)) {
-                    saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
-                    sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
-                }
-                if (WT_TAP(Z::dh, j)) {
-                    sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
-                    sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
-                }
+                if (WT_TAP(Z::dl, j)) fadd2(saa, sda, __fmul_rn(bk.dec_lo[j], vl), __fmul_rn(bk.dec_lo[j], vh));
+                if (WT_TAP(Z::dh, j)) fadd2(sad, sdd, __fmul_rn(bk.dec_hi[j], vl), __fmul_rn(bk.dec_hi[j], vh));
             }
             aa[r * W2 + o] = saa;
             ad[r * W2 + o] = sad;
