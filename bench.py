@@ -91,6 +91,26 @@ def dist_env():
     return rank, world, local
 
 
+def bind_to_gpu_numa_node(local):
+    """Pins this rank to the host cores NVML reports as local to its GPU, BEFORE any pinned allocation, so that the
+    staging buffers of the end-to-end leg are first-touched on the GPU's own NUMA node (eight ranks sharing one node's
+    memory controllers is what caps e2e at N = 8).  Best effort: any failure leaves the affinity alone."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * i + b for i, w in enumerate(mask) for b in range(64) if (w >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return 0
+
+
 def effective_levels(census, wavelet, level, clamp):
     """per-layer level as the reference computes it: each layer is its own
     multi_resolution_analysis([weight], ...) call (dwt_pruning.py:116-117), clamp at :64-65"""
@@ -403,6 +423,7 @@ def run_ours(args):
     rank, world, local = dist_env()
     if not torch.cuda.is_available():
         raise SystemExit('bench.py (impl ours) needs a CUDA device: libwtprune has no CPU fallback')
+    numa_cpus = bind_to_gpu_numa_node(local) if world > 1 else 0
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
@@ -470,7 +491,8 @@ def run_ours(args):
                    'parallelism': f'{world} independent replicas (no data-path collective)' if world > 1 else 'single GPU'},
         'clocks': clocks,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                'ms_per_step': e2e_ms / args.steps, 'matches_device_path_bitwise': consistent},
+                'ms_per_step': e2e_ms / args.steps, 'matches_device_path_bitwise': consistent,
+                'host_cores_bound_to_gpu_numa_node': numa_cpus},
         'gpu_launches': launches,
         'launches_per_step': wl.plans[0].num_launches,
         'roofline': roofline,
