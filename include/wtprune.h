@@ -36,6 +36,17 @@ extern "C" {
  * 'symmetric' is pywt's own default and the second mode carried. */
 #define WT_MODE_PERIODIZATION 0
 #define WT_MODE_SYMMETRIC 1
+/* the rest of pywt.Modes.modes -- `mode` is an open string parameter of multi_resolution_analysis
+ * (dwt_pruning.py:35, dwt_pruning_NoEntropy.py:12); they share the symmetric mode's coefficient
+ * lengths and synthesis and differ in the analysis-side signal extension only */
+#define WT_MODE_ZERO 2
+#define WT_MODE_CONSTANT 3
+#define WT_MODE_REFLECT 4
+#define WT_MODE_PERIODIC 5
+#define WT_MODE_SMOOTH 6
+#define WT_MODE_ANTISYMMETRIC 7
+#define WT_MODE_ANTIREFLECT 8
+#define WT_NUM_MODES 9
 
 /* np.percentile arithmetic: the reference pins numpy 1.22.4 (requirements.txt:2),
  * the GPU box runs numpy 2.x. */

@@ -15,7 +15,8 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
-MODES = {'periodization': 0, 'symmetric': 1}
+MODES = {'periodization': 0, 'symmetric': 1, 'zero': 2, 'constant': 3, 'reflect': 4, 'periodic': 5, 'smooth': 6,
+         'antisymmetric': 7, 'antireflect': 8}
 
 
 def build(force=False):
@@ -45,6 +46,7 @@ def lib():
         L.orc_rec_size.argtypes = [ci, ci, ci, ci]
         L.orc_dwt.argtypes = [fp, ci, ci, ci, fp, fp]
         L.orc_idwt.argtypes = [fp, fp, ci, ci, ci, fp]
+        L.orc_extend.argtypes = [fp, ci, ci, ci, ci, fp]
         L.orc_wavedec2_packed.argtypes = [fp, i64, ci, ci, ci, ci, ci, fp]
         L.orc_waverec2_packed.argtypes = [fp, i64, ci, ci, ci, ci, ci, fp]
         L.orc_percentile_plan.argtypes = [i64, ctypes.c_double, ci, ctypes.POINTER(i64),
@@ -109,6 +111,15 @@ def idwt(ca, cd, wavelet, mode='symmetric'):
     r = lib().orc_idwt(_fp(ca), _fp(cd), ca.size, wid, m, _fp(out))
     if r < 0:
         raise ValueError('idwt: bad sizes')
+    return out
+
+
+def extend(x, before, after, mode):
+    """pywt.pad(x, (before, after), mode): the boundary-extended signal of a non-periodization mode"""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    out = np.empty(x.size + before + after, np.float32)
+    if lib().orc_extend(_fp(x), x.size, mode_index(mode), int(before), int(after), _fp(out)) < 0:
+        raise ValueError('extend: bad arguments')
     return out
 
 

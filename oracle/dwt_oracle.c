@@ -23,8 +23,12 @@
  *   - analysis: one accumulator per output starting at 0.0f, taps in ascending index j;
  *   - periodization synthesis: every product is accumulated directly into out[o]
  *     (low-pass products in ascending j first, then high-pass products);
- *   - symmetric synthesis: a local sum per (output, filter) in ascending j, then out[o] += sum,
- *     low-pass before high-pass;
+ *   - symmetric synthesis (and every other non-periodization mode: pywt's idwt does not look at
+ *     the mode): a local sum per (output, filter) in ascending j, then out[o] += sum, low-pass
+ *     before high-pass;
+ *   - modes zero / constant / reflect / periodic / smooth / antisymmetric / antireflect: the
+ *     extended sample is formed first (ext_sample: an index map, a negation, or one subtract +
+ *     multiply + add for smooth, running subtract / add for antireflect), then multiplied by the tap;
  *   - dwt2: axis -2 first, then axis -1.  idwt2: axis -1 first, then axis -2.
  */
 #include <math.h>
@@ -36,6 +40,17 @@
 
 #define ORC_MODE_PERIODIZATION 0
 #define ORC_MODE_SYMMETRIC 1
+/* the rest of pywt.Modes: signal extension as tabulated in the PyWavelets
+ * documentation, "Signal extension modes"; all of them share the symmetric mode's lengths,
+ * indexing and synthesis (pywt's idwt is the same for every mode but periodization) */
+#define ORC_MODE_ZERO 2
+#define ORC_MODE_CONSTANT 3
+#define ORC_MODE_REFLECT 4
+#define ORC_MODE_PERIODIC 5
+#define ORC_MODE_SMOOTH 6
+#define ORC_MODE_ANTISYMMETRIC 7
+#define ORC_MODE_ANTIREFLECT 8
+#define ORC_NUM_MODES 9
 #define ORC_MAX_LEVEL 32
 
 int orc_wavelet_index(const char* name) {
@@ -112,6 +127,30 @@ int orc_rec_size(int n, int F, int mode, int level) {
 
 static inline int pmod(int a, int m) { int r = a % m; return r < 0 ? r + m : r; }
 
+/* whole-sample antisymmetric extension, the way pywt's convolution loops build it: a running edge
+ * value `le` that each block of n-1 samples is mirrored around (first block around the edge sample
+ * itself, the next one around the last extension value, ...).  d >= 1 = distance from the edge;
+ * `near` / `far` = index of the edge sample and of the opposite end. */
+static inline float antireflect_side(const float* x, int n, int xs, int d, int near, int far) {
+    const float xn = x[(int64_t)near * xs], xf = x[(int64_t)far * xs];
+    const int step = (far > near) ? 1 : -1;
+    float le = xn;
+    int blk = 0;
+    while (d > n - 1) {                 /* whole blocks: le becomes the block's last value */
+        float t = (blk & 1) ? (xn - xf) : (xf - xn);
+        le = (blk & 1) ? (le + t) : (le - t);
+        d -= n - 1;
+        ++blk;
+    }
+    if (blk & 1) {                      /* odd blocks walk back from the far end */
+        float t = x[(int64_t)(far - step * d) * xs] - xf;
+        return le + t;
+    } else {
+        float t = x[(int64_t)(near + step * d) * xs] - xn;
+        return le - t;
+    }
+}
+
 /* value of the boundary-extended signal at (possibly out-of-range) index idx */
 static inline float ext_sample(const float* x, int n, int xs, int idx, int mode) {
     if (mode == ORC_MODE_PERIODIZATION) {
@@ -119,11 +158,56 @@ static inline float ext_sample(const float* x, int n, int xs, int idx, int mode)
         int m = pmod(idx, np);
         if (m == n) m = n - 1;
         return x[(int64_t)m * xs];
-    } else {                               /* half-sample symmetric, period 2n */
+    }
+    if (idx >= 0 && idx < n) return x[(int64_t)idx * xs];
+    switch (mode) {
+    case ORC_MODE_ZERO:
+        return 0.0f;
+    case ORC_MODE_CONSTANT:
+        return x[(int64_t)(idx < 0 ? 0 : n - 1) * xs];
+    case ORC_MODE_REFLECT: {               /* whole-sample symmetric, period 2n-2 (n = 1: constant) */
+        if (n == 1) return x[0];
+        int per = 2 * n - 2, m = pmod(idx, per);
+        if (m >= n) m = per - m;
+        return x[(int64_t)m * xs];
+    }
+    case ORC_MODE_PERIODIC:
+        return x[(int64_t)pmod(idx, n) * xs];
+    case ORC_MODE_SMOOTH: {                /* straight line through the two edge samples (n = 1: constant) */
+        if (n < 2) return x[0];
+        if (idx < 0) {
+            float slope = x[0] - x[xs];
+            float t = slope * (float)(-idx);
+            return x[0] + t;
+        } else {
+            const float e = x[(int64_t)(n - 1) * xs];
+            float slope = e - x[(int64_t)(n - 2) * xs];
+            float t = slope * (float)(idx - (n - 1));
+            return e + t;
+        }
+    }
+    case ORC_MODE_ANTISYMMETRIC: {         /* half-sample antisymmetric, period 2n */
+        int m = pmod(idx, 2 * n);
+        return m < n ? x[(int64_t)m * xs] : -x[(int64_t)(2 * n - 1 - m) * xs];
+    }
+    case ORC_MODE_ANTIREFLECT:             /* whole-sample antisymmetric (n = 1: constant) */
+        if (n == 1) return x[0];
+        return idx < 0 ? antireflect_side(x, n, xs, -idx, 0, n - 1)
+                       : antireflect_side(x, n, xs, idx - (n - 1), n - 1, 0);
+    default: {                             /* ORC_MODE_SYMMETRIC: half-sample symmetric, period 2n */
         int m = pmod(idx, 2 * n);
         if (m >= n) m = 2 * n - 1 - m;
         return x[(int64_t)m * xs];
     }
+    }
+}
+
+/* pywt.pad(x, (before, after), mode) for the non-periodization modes: the extended signal the
+ * analysis convolves (exposed so the tests can hold it against numpy.pad) */
+int orc_extend(const float* x, int n, int mode, int before, int after, float* out) {
+    if (n < 1 || mode < ORC_MODE_SYMMETRIC || mode >= ORC_NUM_MODES || before < 0 || after < 0) return -1;
+    for (int i = -before; i < n + after; ++i) out[i + before] = ext_sample(x, n, 1, i, mode);
+    return n + before + after;
 }
 
 /* one band of a single-level 1-D analysis */
@@ -208,7 +292,7 @@ int orc_dwt(const float* x, int n, int wid, int mode, float* ca, float* cd) {
 
 int orc_idwt(const float* ca, const float* cd, int n, int wid, int mode, float* out) {
     bank32_t b; if (load_bank(wid, &b) || n < 1) return -1;
-    if (mode == ORC_MODE_SYMMETRIC && n < b.F / 2) return -1;
+    if (mode != ORC_MODE_PERIODIZATION && n < b.F / 2) return -1;
     idwt1d(ca, cd, n, 1, b.rlo, b.rhi, b.F, mode, out, 1);
     return orc_idwt_len(n, b.F, mode);
 }

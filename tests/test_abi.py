@@ -38,7 +38,7 @@ def test_max_level_and_shapes(wtlib, oracle_lib):
         F = oracle_lib.dec_len(w)
         for n in range(1, 80):
             assert wtlib.dwt_max_level(n, F) == oracle_lib.dwt_max_level(n, F)
-        for mode in ('periodization', 'symmetric'):
+        for mode in ('periodization', 'symmetric', 'zero', 'smooth', 'antireflect'):
             for (H, W) in [(1, 1), (3, 3), (7, 7), (5, 12), (64, 64)]:
                 for L in range(0, 6):
                     sh, sw, nc = wtlib.packed_shape(H, W, w, L, mode)

@@ -141,7 +141,29 @@ def test_generic_large_planes_bitwise(mods, wavelet, mode):
         assert_bit_equal(rec_got, torch.from_numpy(np.ascontiguousarray(rec_want)), f'rec {wavelet} {mode} {H}x{W}')
 
 
-@pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
+EXTRA_MODES = ['zero', 'constant', 'reflect', 'periodic', 'smooth', 'antisymmetric', 'antireflect']
+
+
+@pytest.mark.parametrize('mode', EXTRA_MODES)
+@pytest.mark.parametrize('wavelet', ['haar', 'db2', 'bior4.4', 'coif3'])
+def test_extra_modes_packed_coefficients_bitwise(mods, wavelet, mode):
+    """the other seven pywt modes: two-sweep analysis kernels + the mode-independent synthesis, planes
+    from N = 1 (multi-wrap extension, N < F) to a few tiles, odd shapes, several levels"""
+    eng, o = mods['eng'], mods['o']
+    rng = np.random.default_rng(17)
+    for (B, H, W) in [(3, 1, 1), (3, 2, 2), (5, 3, 3), (3, 7, 7), (2, 9, 12), (2, 33, 31), (1, 100, 37), (1, 260, 300)]:
+        for level in (1, 2, 4):
+            x = (rng.standard_normal((B, H, W)) * 0.02).astype(np.float32)
+            want = o.wavedec2_packed(x, wavelet, level, mode)
+            got = eng.wavedec2_packed(torch.from_numpy(x).cuda(), wavelet, level, mode)
+            assert_bit_equal(got, torch.from_numpy(want), f'dec {wavelet} {mode} {H}x{W} L{level}')
+            rec_want = o.waverec2_packed(want, x.shape, wavelet, level, mode)[:, :H, :W]
+            rec_got = eng.waverec2_packed(got, x.shape, wavelet, level, mode)
+            assert_bit_equal(rec_got, torch.from_numpy(np.ascontiguousarray(rec_want)), f'rec {wavelet} {mode} {H}x{W} L{level}')
+            np.testing.assert_allclose(rec_got.cpu().numpy(), x, atol=1e-4 if mode in ('smooth', 'antireflect') else 2e-6)
+
+
+@pytest.mark.parametrize('mode', ['periodization', 'symmetric'] + EXTRA_MODES)
 def test_generic_path_prune_flows(mods, mode):
     dp, ne, rf = mods['dp'], mods['ne'], mods['rf']
     g = torch.Generator().manual_seed(11)

@@ -43,8 +43,33 @@ def test_n1_periodization(wavelet):
     assert abs(cd[0]) < 1e-5
 
 
+ALL_MODES = ['periodization', 'symmetric', 'zero', 'constant', 'reflect', 'periodic', 'smooth', 'antisymmetric',
+             'antireflect']
+
+
+def test_extension_modes_match_numpy_pad_and_doc_table():
+    """PyWavelets documentation, "Signal extension modes": six of the modes are numpy.pad modes (pywt.pad's own
+    docstring says which), extensions longer than the signal included; antisymmetric and smooth by the table."""
+    x = np.array([1, 2, 4, 7, 11], np.float32)
+    pads = {'zero': dict(mode='constant'), 'constant': dict(mode='edge'), 'symmetric': dict(mode='symmetric'),
+            'reflect': dict(mode='reflect'), 'periodic': dict(mode='wrap'),
+            'antireflect': dict(mode='reflect', reflect_type='odd')}
+    for mode, kw in pads.items():
+        for n in (1, 2, 3, 5):
+            np.testing.assert_array_equal(o.extend(x[:n], 13, 14, mode), np.pad(x[:n], (13, 14), **kw), err_msg=f'{mode} n={n}')
+    # ... -x2 -x1 | x1 x2 ... xn | -xn -xn-1 ...
+    np.testing.assert_array_equal(o.extend(x[:3], 4, 4, 'antisymmetric'), [4, -4, -2, -1, 1, 2, 4, -4, -2, -1, 1])
+    # straight line through the two edge samples
+    np.testing.assert_array_equal(o.extend(x, 3, 3, 'smooth'), [-2, -1, 0, 1, 2, 4, 7, 11, 15, 19, 23])
+    np.testing.assert_array_equal(o.extend(x[:1], 2, 2, 'smooth'), [1, 1, 1, 1, 1])
+    # zero-padding mode, haar: pairs (0, x1), (x2, x3) ... -> the doc's dwt of an odd-length signal
+    ca, cd = o.dwt([1, 2, 3], 'haar', 'zero')
+    np.testing.assert_allclose(ca, [3 / S, 3 / S], rtol=1e-6)
+    np.testing.assert_allclose(cd, [-1 / S, 3 / S], rtol=1e-6)
+
+
 @pytest.mark.parametrize('wavelet', WAVELETS)
-@pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
+@pytest.mark.parametrize('mode', ALL_MODES)
 def test_perfect_reconstruction(wavelet, mode):
     rng = np.random.default_rng(sum(map(ord, wavelet + mode)))
     for (H, W) in [(1, 1), (2, 2), (3, 3), (4, 4), (7, 7), (8, 8), (9, 9), (33, 33), (64, 64), (5, 12), (3, 7)]:
@@ -52,7 +77,8 @@ def test_perfect_reconstruction(wavelet, mode):
             x = rng.standard_normal((3, H, W)).astype(np.float32)
             r = o.waverec2_packed(o.wavedec2_packed(x, wavelet, L, mode), x.shape, wavelet, L, mode)
             assert r.shape[-2] in (H, H + 1) and r.shape[-1] in (W, W + 1)
-            np.testing.assert_allclose(r[:, :H, :W], x, atol=2e-5)
+            # smooth / antireflect extrapolate: on N < F planes the extended values (and the rounding error) grow per level
+            np.testing.assert_allclose(r[:, :H, :W], x, atol=2e-3 if mode in ('smooth', 'antireflect') else 2e-5)
 
 
 def test_packing_rule_padding():

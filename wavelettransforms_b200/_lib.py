@@ -9,7 +9,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, 'lib', 'libwtprune.so')
 
 WT_OK, WT_E_INVALID, WT_E_CUDA, WT_E_WORKSPACE, WT_E_UNSUPPORTED = 0, -1, -2, -3, -4
-MODES = {'periodization': 0, 'symmetric': 1}
+# pywt.Modes.modes; ids are include/wtprune.h's WT_MODE_*
+MODES = {'periodization': 0, 'symmetric': 1, 'zero': 2, 'constant': 3, 'reflect': 4, 'periodic': 5, 'smooth': 6,
+         'antisymmetric': 7, 'antireflect': 8}
 NUMPY_SEMANTICS = {'legacy_1_22': 0, 'nep50_2x': 1}
 THRESHOLD_PERCENTILE, THRESHOLD_ABSOLUTE = 0, 1
 

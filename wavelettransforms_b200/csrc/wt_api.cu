@@ -110,7 +110,7 @@ void wt_level_sizes(int n, int F, int mode, int level, int* sizes) {
 extern "C" int wt_packed_shape(int H, int W, int wid, int level, int mode, int* side_h, int* side_w,
                                int64_t* coeffs_per_plane) {
     WT_CHECK(wid >= 0 && wid < WT_NUM_WAVELETS, WT_E_INVALID, "bad wavelet id %d", wid);
-    WT_CHECK(mode == WT_MODE_PERIODIZATION || mode == WT_MODE_SYMMETRIC, WT_E_INVALID, "Unknown mode name.");
+    WT_CHECK(mode >= 0 && mode < WT_NUM_MODES, WT_E_INVALID, "Unknown mode name.");
     WT_CHECK(level >= 0, WT_E_INVALID, "Level value of %d is too low . Minimum level is 0.", level);
     WT_CHECK(level <= WT_MAX_LEVEL, WT_E_UNSUPPORTED, "level %d above the supported maximum %d", level, WT_MAX_LEVEL);
     WT_CHECK(H >= 1 && W >= 1, WT_E_INVALID, "empty plane");
@@ -485,7 +485,7 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     *plan_out = nullptr;
     WT_CHECK(layers != nullptr || n_layers == 0, WT_E_INVALID, "layers is NULL");
     WT_CHECK(n_layers >= 0, WT_E_INVALID, "n_layers < 0");
-    WT_CHECK(mode == WT_MODE_PERIODIZATION || mode == WT_MODE_SYMMETRIC, WT_E_INVALID, "Unknown mode name.");
+    WT_CHECK(mode >= 0 && mode < WT_NUM_MODES, WT_E_INVALID, "Unknown mode name.");
     WT_CHECK(threshold_kind == WT_THRESHOLD_PERCENTILE || threshold_kind == WT_THRESHOLD_ABSOLUTE, WT_E_INVALID,
              "unknown threshold kind %d", threshold_kind);
     WT_CHECK(numpy_semantics == WT_NUMPY_LEGACY_1_22 || numpy_semantics == WT_NUMPY_NEP50_2X, WT_E_INVALID,

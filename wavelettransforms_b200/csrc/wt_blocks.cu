@@ -71,7 +71,7 @@ struct PackedGeom {
 int packed_geom(int H, int W, int wid, int level, int mode, PackedGeom* g, WtBank* bank) {
     int rc = wt_get_bank(wid, bank);
     if (rc) return rc;
-    WT_CHECK(mode == WT_MODE_PERIODIZATION || mode == WT_MODE_SYMMETRIC, WT_E_INVALID, "Unknown mode name.");
+    WT_CHECK(mode >= 0 && mode < WT_NUM_MODES, WT_E_INVALID, "Unknown mode name.");
     WT_CHECK(level >= 0, WT_E_INVALID, "Level value of %d is too low . Minimum level is 0.", level);
     WT_CHECK(level <= WT_MAX_LEVEL, WT_E_UNSUPPORTED, "level %d above the supported maximum %d", level, WT_MAX_LEVEL);
     WT_CHECK(H >= 1 && W >= 1, WT_E_INVALID, "empty plane");
@@ -121,7 +121,8 @@ extern "C" int wt_wavedec2_packed_f32(const float* x, int64_t batch, int H, int 
         WtView da = sub_view(packed, g.SH, g.SW, g.offh[l], 0);
         WtView ad = sub_view(packed, g.SH, g.SW, 0, g.offw[l]);
         WtView dd = sub_view(packed, g.SH, g.SW, g.offh[l], g.offw[l]);
-        rc = wt_generic_analysis_level(bank, mode, cur, batch, g.hs[l - 1], g.ws[l - 1], aa, da, ad, dd, stream);
+        float* scratch = wt_generic_scratch(tmp + (l & 1) * tmp_elems, batch, H, W, g.F, mode, level);
+        rc = wt_generic_analysis_level(bank, mode, cur, batch, g.hs[l - 1], g.ws[l - 1], aa, da, ad, dd, scratch, stream);
         cur = aa;
     }
     cudaError_t e2 = cudaStreamSynchronize(stream);

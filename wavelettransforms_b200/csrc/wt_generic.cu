@@ -673,6 +673,125 @@ __global__ void __launch_bounds__(256) wt_count_nonzero_kernel(const float* __re
     if (blockIdx.x == 0 && threadIdx.x == 0) counts4[0] = n;
 }
 
+// ---- the other seven pywt modes (zero, constant, reflect, periodic, smooth, antisymmetric, antireflect) -------------
+// pywt.dwt2 is two dwt_axis sweeps (axis -2, then axis -1 over both results) and the extension of the second sweep is
+// formed from the FIRST sweep's output, which for smooth / antireflect is not what a 2-D extended input tile would give
+// in fp32.  These modes are off the reference's default path (dwt_pruning.py:35 defaults to 'periodization'), so they
+// take a plain two-sweep form through a scratch buffer: one thread per output sample, the extended sample is formed
+// first (index map, negation, or subtract-multiply-add), then multiplied by the tap -- operation for operation what
+// oracle/dwt_oracle.c does.  Synthesis needs nothing new: pywt's idwt ignores the mode unless it is periodization.
+__device__ __forceinline__ float antireflect_side(const float* __restrict__ x, int n, long long xs, int d, int near_i, int far_i) {
+    const float xn = x[near_i * xs], xf = x[far_i * xs];
+    const int step = far_i > near_i ? 1 : -1;
+    float le = xn;
+    int blk = 0;
+    while (d > n - 1) {
+        const float t = (blk & 1) ? __fsub_rn(xn, xf) : __fsub_rn(xf, xn);
+        le = (blk & 1) ? __fadd_rn(le, t) : __fsub_rn(le, t);
+        d -= n - 1;
+        ++blk;
+    }
+    if (blk & 1) return __fadd_rn(le, __fsub_rn(x[(far_i - step * d) * xs], xf));
+    return __fsub_rn(le, __fsub_rn(x[(near_i + step * d) * xs], xn));
+}
+
+__device__ __forceinline__ float ext_value(const float* __restrict__ x, int n, long long xs, int idx, int mode) {
+    if ((unsigned)idx < (unsigned)n) return x[idx * xs];
+    switch (mode) {
+    case WT_MODE_ZERO:
+        return 0.0f;
+    case WT_MODE_CONSTANT:
+        return x[(idx < 0 ? 0 : n - 1) * xs];
+    case WT_MODE_REFLECT: {
+        if (n == 1) return x[0];
+        const int per = 2 * n - 2;
+        int m = pmodi(idx, per);
+        if (m >= n) m = per - m;
+        return x[m * xs];
+    }
+    case WT_MODE_PERIODIC:
+        return x[pmodi(idx, n) * xs];
+    case WT_MODE_SMOOTH: {
+        if (n < 2) return x[0];
+        if (idx < 0) {
+            const float slope = __fsub_rn(x[0], x[xs]);
+            return __fadd_rn(x[0], __fmul_rn(slope, (float)(-idx)));
+        }
+        const float e = x[(n - 1) * xs];
+        const float slope = __fsub_rn(e, x[(n - 2) * xs]);
+        return __fadd_rn(e, __fmul_rn(slope, (float)(idx - (n - 1))));
+    }
+    case WT_MODE_ANTISYMMETRIC: {
+        const int m = pmodi(idx, 2 * n);
+        return m < n ? x[m * xs] : -x[(2 * n - 1 - m) * xs];
+    }
+    case WT_MODE_ANTIREFLECT:
+        if (n == 1) return x[0];
+        return idx < 0 ? antireflect_side(x, n, xs, -idx, 0, n - 1) : antireflect_side(x, n, xs, idx - (n - 1), n - 1, 0);
+    default: {  // symmetric
+        int m = pmodi(idx, 2 * n);
+        if (m >= n) m = 2 * n - 1 - m;
+        return x[m * xs];
+    }
+    }
+}
+
+struct AxisParams {
+    WtView in, aa, da, ad, dd;
+    float* lo;  // [batch][h2][w] results of the axis -2 sweep
+    float* hi;
+    long long batch;
+    int h, w, h2, w2, mode, F;
+};
+
+// axis -2: in (h x w) -> lo, hi (h2 x w); consecutive threads walk a row, so the F reads of a warp are coalesced
+__global__ void __launch_bounds__(256)
+wt_generic_axis0_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ AxisParams P) {
+    const long long total = P.batch * P.h2 * P.w;
+    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += 256LL * gridDim.x) {
+        const int c = (int)(i % P.w);
+        const long long t = i / P.w;
+        const int o = (int)(t % P.h2);
+        const long long p = t / P.h2;
+        const float* __restrict__ col = P.in.p + p * P.in.pstride + c;
+        float sl = 0.0f, sh = 0.0f;
+        for (int j = 0; j < P.F; ++j) {
+            const float v = ext_value(col, P.h, P.in.rstride, 1 + 2 * o - j, P.mode);
+            sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
+            sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+        }
+        P.lo[i] = sl;
+        P.hi[i] = sh;
+    }
+}
+
+// axis -1: lo, hi (h2 x w) -> aa, ad (from lo) and da, dd (from hi), each h2 x w2
+__global__ void __launch_bounds__(256)
+wt_generic_axis1_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ AxisParams P) {
+    const long long total = P.batch * P.h2 * P.w2;
+    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += 256LL * gridDim.x) {
+        const int c = (int)(i % P.w2);
+        const long long t = i / P.w2;
+        const int o = (int)(t % P.h2);
+        const long long p = t / P.h2;
+        const float* __restrict__ rl = P.lo + t * P.w;
+        const float* __restrict__ rh = P.hi + t * P.w;
+        float saa = 0.0f, sad = 0.0f, sda = 0.0f, sdd = 0.0f;
+        for (int j = 0; j < P.F; ++j) {
+            const float vl = ext_value(rl, P.w, 1, 1 + 2 * c - j, P.mode);
+            const float vh = ext_value(rh, P.w, 1, 1 + 2 * c - j, P.mode);
+            saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
+            sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
+            sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
+            sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
+        }
+        P.aa.p[p * P.aa.pstride + (long long)o * P.aa.rstride + c] = saa;
+        P.ad.p[p * P.ad.pstride + (long long)o * P.ad.rstride + c] = sad;
+        P.da.p[p * P.da.pstride + (long long)o * P.da.rstride + c] = sda;
+        P.dd.p[p * P.dd.pstride + (long long)o * P.dd.rstride + c] = sdd;
+    }
+}
+
 }  // namespace
 
 // filter length x mode -> template instantiation; WT_GEN_LAUNCH(F, MODE) is defined at the point of use
@@ -702,7 +821,8 @@ long long wt_generic_ncoef(int H, int W, int F, int mode, int level) {
     return n;
 }
 
-long long wt_generic_tmp_elems(int H, int W, int F, int mode, int level) {
+// per-plane floats of one ping-pong buffer: [approximation / reconstruction | scratch of the two-sweep modes]
+static long long tmp_pingpong_elems(int H, int W, int F, int mode, int level) {
     int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
     wt_level_sizes(H, F, mode, level, hs);
     wt_level_sizes(W, F, mode, level, ws);
@@ -714,8 +834,42 @@ long long wt_generic_tmp_elems(int H, int W, int F, int mode, int level) {
     return m;
 }
 
+long long wt_generic_tmp_elems(int H, int W, int F, int mode, int level) {
+    long long m = tmp_pingpong_elems(H, W, F, mode, level);
+    if (mode > WT_MODE_SYMMETRIC) {  // lo + hi of the axis -2 sweep, behind the ping-pong part
+        int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
+        wt_level_sizes(H, F, mode, level, hs);
+        wt_level_sizes(W, F, mode, level, ws);
+        long long sc = 0;
+        for (int l = 1; l <= level; ++l) sc = std::max(sc, 2LL * hs[l] * ws[l - 1]);
+        m += sc;
+    }
+    return m;
+}
+
+float* wt_generic_scratch(float* tmp, long long batch, int H, int W, int F, int mode, int level) {
+    return mode > WT_MODE_SYMMETRIC ? tmp + batch * tmp_pingpong_elems(H, W, F, mode, level) : nullptr;
+}
+
 int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
-                              WtView da, WtView ad, WtView dd, cudaStream_t stream) {
+                              WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream) {
+    if (mode > WT_MODE_SYMMETRIC) {
+        WT_CHECK(scratch != nullptr, WT_E_INVALID, "generic analysis: mode %d needs the sweep scratch", mode);
+        AxisParams A;
+        A.in = in; A.aa = aa; A.da = da; A.ad = ad; A.dd = dd;
+        A.batch = batch; A.h = h; A.w = w; A.mode = mode; A.F = bank.F;
+        A.h2 = wt_dwt_coeff_len(h, bank.F, mode);
+        A.w2 = wt_dwt_coeff_len(w, bank.F, mode);
+        A.lo = scratch;
+        A.hi = scratch + batch * A.h2 * w;
+        const long long n0 = batch * A.h2 * w, n1 = batch * A.h2 * A.w2;
+        if (n0 <= 0 || n1 <= 0) return WT_OK;
+        const long long cap = 148LL * 8 * 4;
+        wt_generic_axis0_kernel<<<(unsigned)std::min((n0 + 255) / 256, cap), 256, 0, stream>>>(bank, A);
+        wt_generic_axis1_kernel<<<(unsigned)std::min((n1 + 255) / 256, cap), 256, 0, stream>>>(bank, A);
+        WT_CUDA(cudaGetLastError());
+        return WT_OK;
+    }
     AnaParams P;
     P.in = in; P.aa = aa; P.da = da; P.ad = ad; P.dd = dd;
     P.batch = batch; P.h = h; P.w = w; P.mode = mode;
@@ -869,9 +1023,11 @@ int wt_generic_analysis(const WtBank& bank, int mode, const WtGenericLayer& L, l
         WtView da = wt_view(L.coef + off[l * 3 + 0], hs[l], ws[l]);
         WtView ad = wt_view(L.coef + off[l * 3 + 1], hs[l], ws[l]);
         WtView dd = wt_view(L.coef + off[l * 3 + 2], hs[l], ws[l]);
-        rc = wt_generic_analysis_level(bank, mode, cur, L.batch, hs[l - 1], ws[l - 1], aa, da, ad, dd, stream);
+        // the scratch of the two-sweep modes sits behind the ping-pong part of the buffer `cur` is NOT in
+        float* scratch = wt_generic_scratch((l & 1) ? L.tmp0 : L.tmp1, L.batch, L.H, L.W, bank.F, mode, L.level);
+        rc = wt_generic_analysis_level(bank, mode, cur, L.batch, hs[l - 1], ws[l - 1], aa, da, ad, dd, scratch, stream);
         if (rc) return rc;
-        ++*launches;
+        *launches += (mode > WT_MODE_SYMMETRIC) ? 2 : 1;
         cur = aa;
     }
     return WT_OK;

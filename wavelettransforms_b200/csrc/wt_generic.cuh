@@ -1,4 +1,4 @@
-// wt_generic.cuh -- generic (any plane size, both modes, any level) tiled DWT path.
+// wt_generic.cuh -- generic (any plane size, every pywt mode, any level) DWT path.
 #pragma once
 #include "wt_common.cuh"
 
@@ -32,10 +32,13 @@ struct WtGenericLayer {
 // per-plane number of coefficients / tmp elements
 long long wt_generic_ncoef(int H, int W, int F, int mode, int level);
 long long wt_generic_tmp_elems(int H, int W, int F, int mode, int level);
+// modes beyond symmetric: where the scratch of the two-sweep analysis starts inside a ping-pong buffer of
+// batch * wt_generic_tmp_elems() floats (nullptr for periodization / symmetric)
+float* wt_generic_scratch(float* tmp, long long batch, int H, int W, int F, int mode, int level);
 
-// one decomposition level: in (h x w) -> aa, da, ad, dd (h2 x w2)
+// one decomposition level: in (h x w) -> aa, da, ad, dd (h2 x w2); scratch: see wt_generic_scratch
 int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
-                              WtView da, WtView ad, WtView dd, cudaStream_t stream);
+                              WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream);
 // one reconstruction level: bands (h2 x w2) -> out (oh x ow, cropped).  thr: device threshold
 // (nullable) or thr_host when use_host; thr_a: also threshold the approximation band (deepest
 // level only); counts4 != nullptr: add zero / nonzero counts of `out` (final level).
