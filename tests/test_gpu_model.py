@@ -165,3 +165,44 @@ def test_full_size_properties(mods):
     assert pruned <= 0 or pruned < 10
     err = (rec[0] - w).abs().max().item()
     assert err <= 1e-6 + 1e-5 * w.abs().max().item(), err
+
+
+@pytest.mark.parametrize('wavelet,level,p,clamp', [('bior4.4', 5, 50.0, False), ('haar', 5, 30.0, True)])
+def test_synthetic_logits_and_sparsity_parity(mods, wavelet, level, p, clamp):
+    """north star, third criterion: the model's outputs match the reference's to 1e-5 relative / 1e-6 absolute.
+    ImageNet is not in the reference tree, so: one ResNet-18 pruned by the oracle's reference flow on
+    the CPU, one by the CUDA walker, the same fixed-seed batch through both on the same device (eval mode, fp32),
+    logits compared at that tolerance; calculate_sparsity (testing_suite/eval_model.py:7-20) of both agrees."""
+    import copy
+    from wavelettransforms_b200 import eval_model
+    dp, rf = mods['dp'], mods['rf']
+    base = resnet18().eval()
+    ours, theirs = copy.deepcopy(base), copy.deepcopy(base)
+    dp.prune_model_layers(ours, wavelet, level, p, clamp_level=clamp)
+    for name, m in conv_layers(theirs):
+        want, _ = rf.multi_resolution_analysis([m.weight.detach()], wavelet, level, p, numpy_semantics='legacy_1_22',
+                                               clamp_level=clamp)
+        m.weight.data = want[0]
+    torch.manual_seed(123)
+    batch = torch.randn(4, 3, 224, 224)
+    prev = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        with torch.no_grad():
+            lo = ours.cuda()(batch.cuda()).logits.float().cpu()
+            lt = theirs.cuda()(batch.cuda()).logits.float().cpu()
+            lb = base.cuda()(batch.cuda()).logits.float().cpu()
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = prev
+    err = (lo - lt).abs().max().item()
+    assert torch.allclose(lo, lt, rtol=1e-5, atol=1e-6), f'max |dlogit| = {err:.3e}'
+    assert not torch.allclose(lo, lb, rtol=1e-3, atol=1e-4)          # the pruning did change the function
+    # reference calculate_sparsity, verbatim arithmetic, on the oracle-pruned model
+    tot = nz = 0
+    for prm in theirs.parameters():
+        if prm.dim() > 1:
+            tot += prm.numel()
+            nz += torch.sum(torch.abs(prm) < 1e-6).item()
+    assert eval_model.calculate_sparsity(ours) == nz / tot
+    assert eval_model.calculate_sparsity(ours.cpu()) == nz / tot
