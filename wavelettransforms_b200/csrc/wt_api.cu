@@ -871,6 +871,13 @@ extern "C" int wt_plan_results(WtPlan* P, void* stream_, int64_t* counts, int64_
                 g, sum[1], mx[1], sum[2], mx[2], sum[3], mx[3], sum[4], mx[4], sum[5], mx[5], sum[6], mx[6], sum[7], mx[7],
                 sum[8], mx[8], sum[9], mx[9], sum[10], mx[10], sum[11], mx[11], sum[12], mx[12], sum[13], mx[13], sum[14], mx[14],
                 sum[15], mx[15]);
+        if (getenv("WT_SELECT_STAMPS_CTAS")) {  // per-CTA arrival at the barriers (us): who is everybody waiting for
+            for (int c = 0; c < g; ++c) {
+                fprintf(stderr, "  cta %3d:", c);
+                for (int k = 0; k < 7; ++k) fprintf(stderr, " %6.1f", st[c * 16 + k] ? (double)(st[c * 16 + k] - t0) * 1e-3 : 0.0);
+                fprintf(stderr, "\n");
+            }
+        }
         std::vector<WtSelState> ss(P->sel_jobs.size());
         WT_CUDA(cudaMemcpy(ss.data(), P->sel_args.state, ss.size() * sizeof(WtSelState), cudaMemcpyDeviceToHost));
         for (size_t q = 0; q < ss.size(); ++q) {

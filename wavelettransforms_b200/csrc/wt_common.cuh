@@ -99,6 +99,8 @@ struct WtSelState {  // per job, device; written by the CTA that holds the job's
     unsigned long long crem[2];    // ranks inside those digits
     unsigned int cprefix2[2];      // wide brackets: C1 and C2 digits of both ranks (published by C3)
     unsigned long long crem2[2];
+    unsigned int tail_key[2];      // one-CTA tail: key - lo_key of both ranks
+    int tail_done;                 // 1: the tail finished this job (C1..C3 skip it, final_keys reads tail_key)
 };
 
 struct WtSelArgs {
@@ -111,6 +113,7 @@ struct WtSelArgs {
     unsigned long long* hist3;  // [n_jobs][2][CBINS]  (radix path: [2][BINS3] inside the same slot)
     int* fail_flag;             // set when any job leaves the sampled path
     int* wide_flag;             // set when any job's bracket is wider than 16 bins: the grid runs candidate pass C3
+    int* big_flag;              // set when any job's candidate list is too long for the one-CTA tail: the grid runs C1..C3
     int path;                   // 0: sampled path with radix fallback, 1: radix path only; set by wt_select_launch
     unsigned long long* hist1c; // [n_jobs][BINS1 / 32]: coarse sums of hist1 (32 fine bins each)
     const int* cta_tiles;       // nullable: [cta_grid + 1] first tile of every CTA (cost-balanced split)
@@ -142,6 +145,9 @@ size_t wt_select_scratch_bytes(int n_jobs);  // hist1+hist2+hist3+done+state, co
 void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
 #define WT_SEL_SAMPLED_MIN_TILES 10240  // 40 Mi keys
+#ifndef WT_SEL_TAIL_MAX
+#define WT_SEL_TAIL_MAX 65536  // longest candidate list one CTA finishes alone (three L2-resident passes)
+#endif
 int wt_select_path(int n_tiles);  // 0 sampled, 1 radix
 // grid wt_select_launch will use for n_tiles tiles on the current device
 int wt_select_grid(int n_tiles, int* grid_out);
@@ -162,7 +168,7 @@ int wt_apply_threshold_launch(const float* x, float* out, long long n, const flo
 struct WtSmallJob {
     const float* in;   // [batch][H][W]
     float* out;        // [batch][H][W]
-    float* coef;       // [ncoef][batch]  (coefficient-major so a warp's accesses coalesce)
+    float* coef;       // [ceil(batch / 128)][ncoef][<= 128 planes]: block-interleaved, see wt_small.cu
     long long batch;
     int level;
     int layer;

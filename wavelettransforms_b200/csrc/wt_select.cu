@@ -124,6 +124,7 @@ __device__ __forceinline__ void span_for_each(const float* __restrict__ x, long 
 }
 
 __device__ __forceinline__ unsigned long long load_bin(const unsigned long long* h, int b) { return __ldcg(&h[b]); }
+__device__ __forceinline__ unsigned long long load_bin(const unsigned int* h, int b) { return h[b]; }  // CTA-private (shared)
 
 
 __device__ __forceinline__ float lerp_threshold(float a, float b, double gamma, int mode) {
@@ -718,10 +719,69 @@ __device__ void phase_s1_compact(const WtSelArgs& a, Shared& sh, int t_begin, in
     });
 }
 
+// ---- T: one CTA finishes one job: verify the bracket, then an MSD radix select (11-bit digits, both ranks at once)
+// over the job's candidate list, which is short (5 sigma of the sampling error: ~1e4 keys) and L2-resident.  CTA-local
+// barriers only -- the grid-wide candidate passes C1..C3 cost a grid barrier, a flush and 296 redundant scans each
+// and are kept for the lists this CTA would take too long over (big_flag).
+__device__ void phase_tail(const WtSelArgs& a, Shared& sh) {
+    for (int j = blockIdx.x; j < a.n_jobs; j += gridDim.x) {
+        const WtSelJob job = a.jobs[j];
+        WtSelState* st = &a.state[j];
+        const unsigned int n_bins = __ldcg(&st->n_bins), n_c = __ldcg(&st->s_count);
+        const unsigned long long below = __ldcg(&st->below);
+        unsigned long long e0, e1;
+        explicit_ranks(job, e0, e1);
+        const bool zlo = __ldcg(&st->lo_bin) == 0u;  // then `below` counts the exact zeros
+        const bool in0 = (zlo && e0 < below) || (below <= e0 && e0 < below + (unsigned long long)n_c);
+        const bool in1 = (zlo && e1 < below) || (below <= e1 && e1 < below + (unsigned long long)n_c);
+        const bool good = n_bins != 0u && n_c <= job.cand_cap && in0 && in1;
+        if (!good) {  // hist1 / hist1c held the sample: the radix path starts from zero
+            unsigned long long* gh1 = global_hist<1>(a, j);
+            for (int b = threadIdx.x; b < WT_SEL_BINS1; b += T) gh1[b] = 0ull;
+            if (threadIdx.x < WT_SEL_COARSE) a.hist1c[(size_t)j * WT_SEL_COARSE + threadIdx.x] = 0ull;
+            if (threadIdx.x == 0) { st->failed = 1; *a.fail_flag = 1; }
+            continue;
+        }
+        if (n_c > (unsigned int)WT_SEL_TAIL_MAX) {
+            if (threadIdx.x == 0) *a.big_flag = 1;
+            continue;
+        }
+        const unsigned int lo_key = __ldcg(&st->lo_bin) << 19;
+        unsigned int pre0 = 0u, pre1 = 0u;                                   // digits resolved so far of key - lo_key
+        unsigned long long r0 = e0 < below ? 0ull : e0 - below, r1 = e1 < below ? 0ull : e1 - below;  // ranks inside them
+        int prev = 19 + (n_bins > 1u ? 32 - __clz(n_bins - 1u) : 0);          // bits of key - lo_key still open
+        unsigned int* h = sh.hist;                                           // two histograms of 2048 bins
+        while (prev > 0) {
+            const int s = prev > 11 ? prev - 11 : 0;
+            const unsigned int mask = (1u << (prev - s)) - 1u;
+            const bool two = pre0 != pre1;
+            clear_hist(sh, 4096);
+            cand_for_each(job.cand, n_c, [=](unsigned int k) {
+                const unsigned int v = k - lo_key, top = v >> prev;
+                if (top == pre0) atomicAdd(&h[(v >> s) & mask], 1u);
+                else if (two && top == pre1) atomicAdd(&h[2048u + ((v >> s) & mask)], 1u);
+            });
+            __syncthreads();
+            const Found f = scan_find_pair<2048, false>(h, two ? h + 2048 : h, 0ull, 0ull, r0, r1, sh);
+            pre0 = (pre0 << (prev - s)) | f.d0;
+            pre1 = (pre1 << (prev - s)) | f.d1;
+            r0 = f.r0;
+            r1 = f.r1;
+            prev = s;
+        }
+        if (threadIdx.x == 0) {
+            st->tail_key[0] = pre0;
+            st->tail_key[1] = pre1;
+            st->tail_done = 1;
+        }
+    }
+}
+
 // ---- C1: verify the bracket; histogram of the top 12 bits of key - lo_key over the candidate list -> hist2 ------
 __device__ void phase_c1_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
         WtSelState* st = &a.state[j];
+        if (__ldcg(&st->tail_done) || __ldcg(&st->failed)) return;  // settled by the one-CTA tail
         const unsigned int n_bins = __ldcg(&st->n_bins), n_c = __ldcg(&st->s_count);
         const unsigned long long below = __ldcg(&st->below);
         unsigned long long e0, e1;
@@ -760,7 +820,7 @@ __device__ void phase_c1_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t
 __device__ void phase_c2_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
         WtSelState* st = &a.state[j];
-        if (__ldcg(&st->failed)) return;
+        if (__ldcg(&st->failed) || __ldcg(&st->tail_done)) return;
         const unsigned int n_c = __ldcg(&st->s_count);
         const unsigned long long below = __ldcg(&st->below);
         unsigned long long e0, e1;
@@ -798,7 +858,7 @@ __device__ void phase_c3_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
         WtSelState* st = &a.state[j];
         const unsigned int n_bins = __ldcg(&st->n_bins);
-        if (__ldcg(&st->failed) || n_bins <= 16u) return;
+        if (__ldcg(&st->failed) || __ldcg(&st->tail_done) || n_bins <= 16u) return;
         const unsigned int n_c = __ldcg(&st->s_count);
         const unsigned int d0 = __ldcg(&st->cprefix[0]), d1 = __ldcg(&st->cprefix[1]);
         const unsigned long long r0 = __ldcg(&st->crem[0]), r1 = __ldcg(&st->crem[1]);
@@ -845,7 +905,10 @@ __device__ __forceinline__ void final_keys(const WtSelArgs& a, Shared& sh, int j
         const unsigned int n_bins = __ldcg(&st->n_bins);
         const int cs = cand_shift(n_bins), cs2 = cand_shift2(cs);
         unsigned int v0, v1;  // key - lo_key
-        if (n_bins > 16u) {
+        if (__ldcg(&st->tail_done)) {
+            v0 = __ldcg(&st->tail_key[0]);
+            v1 = __ldcg(&st->tail_key[1]);
+        } else if (n_bins > 16u) {
             const unsigned int q0 = __ldcg(&st->cprefix2[0]), q1 = __ldcg(&st->cprefix2[1]);
             const unsigned long long r0 = __ldcg(&st->crem2[0]), r1 = __ldcg(&st->crem2[1]);
             const unsigned long long* gh = global_hist<1>(a, j);
@@ -1022,24 +1085,31 @@ __global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs 
         phase_s1_compact(a, sh, t_begin, t_end, acc);
         acc.stamp(2);
         grid.sync();
-        phase_c1_cand(a, sh, t_begin, t_end, acc);
+        phase_tail(a, sh);
         acc.stamp(3);
         grid.sync();
-        phase_c2_cand(a, sh, t_begin, t_end, acc);
-        acc.stamp(4);
-        grid.sync();
-        if (__ldcg(a.wide_flag) != 0) {  // grid-uniform: set during S1, three barriers ago
-            phase_c3_cand(a, sh, t_begin, t_end, acc);
+        if (__ldcg(a.big_flag) != 0) {  // grid-uniform (final before the last barrier): some list is too long for one CTA
+            phase_c1_cand(a, sh, t_begin, t_end, acc);
             grid.sync();
+            phase_c2_cand(a, sh, t_begin, t_end, acc);
+            acc.stamp(4);
+            grid.sync();
+            if (__ldcg(a.wide_flag) != 0) {  // grid-uniform: set during S1
+                phase_c3_cand(a, sh, t_begin, t_end, acc);
+                grid.sync();
+            }
         }
     }
     if (a.path != 0 || __ldcg(a.fail_flag) != 0) {  // grid-uniform: the flag was final before the last barrier
         acc.begin();
         phase1_hist(a, sh, t_begin, t_end, acc);
-        grid.sync();
+        if (a.path != 0) acc.stamp(1);  // radix-only launches reuse the sampled path's boundary slots: arrival at the
+        grid.sync();                    // barrier after P1 / P2 / P3 (mean vs max over CTAs = imbalance)
         phase2_hist_compact(a, sh, t_begin, t_end, acc);
+        if (a.path != 0) acc.stamp(2);
         grid.sync();
         phase3_hist_cand(a, sh, t_begin, t_end, acc);
+        if (a.path != 0) acc.stamp(3);
         grid.sync();
         acc.end(15);
     }
@@ -1094,6 +1164,7 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
     a->state = reinterpret_cast<WtSelState*>(p); p += (size_t)n_jobs * sizeof(WtSelState);
     a->fail_flag = reinterpret_cast<int*>(p);  // inside the 256 spare bytes
     a->wide_flag = a->fail_flag + 1;
+    a->big_flag = a->fail_flag + 2;
     a->path = -1;  // resolved at launch: wt_select_path()
     a->stamps = nullptr;  // tuning aid, set by the plan when WT_SELECT_STAMPS is in the environment
     a->cta_tiles = nullptr;
