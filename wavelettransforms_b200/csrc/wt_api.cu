@@ -307,6 +307,7 @@ static int build_tables(WtPlan* P) {
     }
     P->sel_args.n_tiles = sel_tiles;
     P->sel_args.any_apply = any_apply ? 1 : 0;
+    P->sel_args.short_lists = wt_select_predict_short(P->sel_jobs.data(), (int)P->sel_jobs.size());
     return WT_OK;
 }
 
@@ -695,7 +696,13 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     };
     char label[64];
     mark("memset");
-    WT_CUDA(cudaMemsetAsync(P->zero_block, 0, P->zero_bytes, stream));
+    // counts are accumulated by the very first kernels; the select scratch (histograms + state, ~100 KB per job) is not
+    // touched before the select, so when the size classes fork its memset rides on the last auxiliary stream next to
+    // the analysis launches instead of in front of them
+    const size_t counts_off = (size_t)(reinterpret_cast<char*>(P->counts_dev) - P->zero_block);
+    const bool split_zero = !P->timing && !P->aux.empty() && counts_off > 0 && counts_off < P->zero_bytes;
+    if (split_zero) WT_CUDA(cudaMemsetAsync(P->zero_block + counts_off, 0, P->zero_bytes - counts_off, stream));
+    else WT_CUDA(cudaMemsetAsync(P->zero_block, 0, P->zero_bytes, stream));
     if (P->host_io) mark("h2d");
     if (P->host_io)
         for (int i = 0; i < n; ++i)
@@ -722,6 +729,7 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     };
     auto class_stream = [&](size_t k) { return (forked && k > 0) ? P->aux[k - 1] : stream; };
     if ((rc = fork())) return rc;
+    if (split_zero) WT_CUDA(cudaMemsetAsync(P->zero_block, 0, counts_off, P->aux.back()));
     for (size_t k = 0; k < P->small.size(); ++k) {
         auto& c = P->small[k];
         snprintf(label, sizeof(label), "small_analysis_%dx%d", c.H, c.W);

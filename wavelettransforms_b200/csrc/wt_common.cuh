@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string>
 #include <vector>
 
@@ -113,6 +114,8 @@ struct WtSelArgs {
     unsigned long long* hist3;  // [n_jobs][2][CBINS]  (radix path: [2][BINS3] inside the same slot)
     int* fail_flag;             // set when any job leaves the sampled path
     int* wide_flag;             // set when any job's bracket is wider than 16 bins: the grid runs candidate pass C3
+    unsigned int tail_max;      // longest candidate list the one-CTA tail takes (resolved at launch; 0: no tail)
+    int short_lists;            // host hint (wt_select_predict_short): every job's candidate list should fit the one-CTA tail
     int* big_flag;              // set when any job's candidate list is too long for the one-CTA tail: the grid runs C1..C3
     int path;                   // 0: sampled path with radix fallback, 1: radix path only; set by wt_select_launch
     unsigned long long* hist1c; // [n_jobs][BINS1 / 32]: coarse sums of hist1 (32 fine bins each)
@@ -135,9 +138,13 @@ static inline unsigned int wt_select_cand_cap(long long n) {
 }
 
 // S0 sample of the sampled path: at least 64 Ki keys, 1/16 of the tensor from 1 Mi keys on
+#ifndef WT_SEL_MIN_SAMPLE_LOG2
+#define WT_SEL_MIN_SAMPLE_LOG2 14  // a job is sub-sampled only while the sample keeps 16 Ki keys
+#endif
 static inline int wt_select_sample_shift(long long n) {
+    static const int min_log2 = [] { const char* e = getenv("WT_SEL_MIN_SAMPLE_LOG2"); return e ? atoi(e) : WT_SEL_MIN_SAMPLE_LOG2; }();
     int s = 0;
-    while (s < 4 && (n >> (s + 1)) >= (1LL << 16)) ++s;
+    while (s < 4 && (n >> (s + 1)) >= (1LL << min_log2)) ++s;
     return s;
 }
 size_t wt_select_scratch_bytes(int n_jobs);  // hist1+hist2+hist3+done+state, contiguous, memset to 0 before launch
@@ -146,9 +153,12 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
 #define WT_SEL_SAMPLED_MIN_TILES 10240  // 40 Mi keys
 #ifndef WT_SEL_TAIL_MAX
-#define WT_SEL_TAIL_MAX 65536  // longest candidate list one CTA finishes alone (three L2-resident passes)
+#define WT_SEL_TAIL_MAX 32768  // longest candidate list one CTA finishes alone (three L2-resident passes; measured
+                               // against the grid-wide passes: wins at 20 K keys, loses at 50 K)
 #endif
-int wt_select_path(int n_tiles);  // 0 sampled, 1 radix
+int wt_select_path(int n_tiles, int short_lists);  // 0 sampled, 1 radix
+// plan-time guess: will every job's bracket hold few enough keys for the one-CTA tail? (see wt_select.cu)
+int wt_select_predict_short(const WtSelJob* jobs, int n_jobs);
 // grid wt_select_launch will use for n_tiles tiles on the current device
 int wt_select_grid(int n_tiles, int* grid_out);
 // cost-balanced contiguous split of the tile space over `grid` CTAs: every segment (piece of one job inside one
@@ -168,7 +178,7 @@ int wt_apply_threshold_launch(const float* x, float* out, long long n, const flo
 struct WtSmallJob {
     const float* in;   // [batch][H][W]
     float* out;        // [batch][H][W]
-    float* coef;       // [ceil(batch / 128)][ncoef][<= 128 planes]: block-interleaved, see wt_small.cu
+    float* coef;       // [ncoef][batch]  (coefficient-major so a warp's accesses coalesce)
     long long batch;
     int level;
     int layer;

@@ -13,15 +13,19 @@
 // barriers separate the phases, and NO phase has a serial tail: after a barrier every CTA scans the (small,
 // L2-resident) global histogram of its own job redundantly instead of waiting for one elected CTA to do it.
 //
-// SAMPLED PATH (launches of 40 Mi keys and more, see wt_select_path): ONE full pass over the tensors, and that pass has no shared-memory atomics.
+// SAMPLED PATH (launches of 40 Mi keys and more, and smaller ones whose candidate lists are predicted short, see
+// wt_select_path / wt_select_predict_short): ONE full pass over the tensors, and that pass has no shared-memory atomics.
 //   S0  12-bit histogram (key bits 30..19) of a SAMPLE: 4096 >> sample_shift elements of every tile, at a window
-//       offset that rotates with the tile index; tensors below 128 Ki keys are read whole (the sample is exact)
+//       offset that rotates with the tile index; tensors below 32 Ki keys are read whole (the sample is exact)
 //   S1  every CTA scans the sample histogram -> a bracket of consecutive 12-bit bins that holds both ranks
 //       unless the sample lied (5 sigma of the binomial rank error on each side; exact for whole-tensor samples);
 //       then the one streaming pass: count the keys below the bracket, compact the keys inside it into the job's
 //       candidate list (warp-private staging, no CTA barrier, no histogram)
-//   C1  verify: below <= rank < below + candidates and the list did not overflow -- otherwise the job is handed to
-//       the radix path; histogram of the top 12 bits of key - lo_key inside the bracket over the candidate list
+//   T   ONE CTA per job: verify (below <= rank < below + candidates, no overflow -- otherwise the job is handed to
+//       the radix path); lists up to tail_max keys are finished right here by an MSD radix select with 11-bit
+//       digits over the L2-resident list, CTA-local barriers only.  Longer lists raise big_flag and take the
+//       grid-wide passes (a grid barrier, a flush and 296 redundant scans each):
+//   C1  histogram of the top 12 bits of key - lo_key inside the bracket over the candidate list
 //   C2  scan -> digit of both ranks; histogram of the next (7..11) bits of the matching candidates
 //   C3  only when some job's bracket is wider than 16 bins (a rank next to a cluster of ties at zero: the bins in
 //       between are many and nearly empty): the last <= 8 bits
@@ -37,6 +41,7 @@
 //       (a job whose candidates do not fit its list re-reads the tensor instead)
 #include <cooperative_groups.h>
 
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 
@@ -742,7 +747,7 @@ __device__ void phase_tail(const WtSelArgs& a, Shared& sh) {
             if (threadIdx.x == 0) { st->failed = 1; *a.fail_flag = 1; }
             continue;
         }
-        if (n_c > (unsigned int)WT_SEL_TAIL_MAX) {
+        if (n_c > a.tail_max) {
             if (threadIdx.x == 0) *a.big_flag = 1;
             continue;
         }
@@ -1166,6 +1171,7 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
     a->wide_flag = a->fail_flag + 1;
     a->big_flag = a->fail_flag + 2;
     a->path = -1;  // resolved at launch: wt_select_path()
+    a->short_lists = 0;
     a->stamps = nullptr;  // tuning aid, set by the plan when WT_SELECT_STAMPS is in the environment
     a->cta_tiles = nullptr;
     a->cta_job = nullptr;
@@ -1243,11 +1249,36 @@ void wt_select_balance(const WtSelJob* jobs, int n_jobs, int n_tiles, int grid, 
 // sampled path saves one of the two full passes but runs one or two more phases, each worth 6..8 us of barrier,
 // scan and flush latency whatever the size; it loses by 10 % at 31 M keys (ResNet-18 coefficients) and wins by 25 %
 // at 67 M.  WT_SELECT_PATH=radix|sampled (read at every launch) overrides.
-int wt_select_path(int n_tiles) {
+int wt_select_path(int n_tiles, int short_lists) {
     const char* e = getenv("WT_SELECT_PATH");
     if (e && !strcmp(e, "radix")) return 1;
     if (e && !strcmp(e, "sampled")) return 0;
-    return n_tiles >= WT_SEL_SAMPLED_MIN_TILES ? 0 : 1;
+    return (n_tiles >= WT_SEL_SAMPLED_MIN_TILES || short_lists) ? 0 : 1;
+}
+
+// Below 40 Mi keys the sampled path only pays when the one-CTA tail can finish every job (measured, ResNet-18: 81 us
+// against 104 us radix when it can, 83 us against 64 us when the lists are long and the grid-wide passes C1..C3 run).
+// A candidate list is the bracket of 12-bit bins around the rank: one bin (2^-4 of an octave) holds about q / 16 of
+// the explicit keys at explicit quantile q of a bell-shaped magnitude distribution (density of |x| per log-bin grows
+// linearly with x near zero), and the bracket adds 5 sigma of the sample's rank error on both sides.  Deep
+// decompositions of small planes put the rank a few percent into the explicit keys (padding zeros and vanishing
+// deep-level details sort first): short lists.  A mid-quantile over raw weights: long lists, radix.  A wrong guess only
+// costs time: the kernel checks the real list length (big_flag) and the real bracket (fail_flag).
+int wt_select_predict_short(const WtSelJob* jobs, int n_jobs) {
+    static const double limit = [] { const char* e = getenv("WT_SEL_SHORT_LIMIT"); return e ? atof(e) : 32768.0; }();
+    for (int j = 0; j < n_jobs; ++j) {
+        const WtSelJob& jb = jobs[j];
+        if (jb.n <= 0) continue;
+        if (jb.cand == nullptr) return 0;
+        double r = (double)(jb.k0 - jb.zeros);
+        if (r < 0) r = 0;
+        double q = r / (double)jb.n;
+        if (q > 1.0) q = 1.0;
+        const double m = (double)(jb.n >> jb.sample_shift);
+        const double est = (double)jb.n * (2.0 * q / 16.0 + (m < (double)jb.n ? 10.0 * sqrt(q * (1.0 - q) / m) : 0.0));
+        if (est > limit) return 0;
+    }
+    return 1;
 }
 
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
@@ -1256,7 +1287,11 @@ int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
     if (rc) return rc;
     const size_t smem = sizeof(Shared);
     WtSelArgs a = args;
-    a.path = wt_select_path(a.n_tiles);
+    a.path = wt_select_path(a.n_tiles, a.short_lists);
+    {
+        const char* e = getenv("WT_SEL_TAIL_MAX");  // tuning aid, read at every launch
+        a.tail_max = e ? (unsigned int)atoi(e) : (unsigned int)WT_SEL_TAIL_MAX;
+    }
     int do_apply = a.any_apply;  // jobs without `out` skip the apply loop inside P4
     void* params[] = {&a, &do_apply};
     WT_CUDA(cudaLaunchCooperativeKernel((const void*)wt_select_kernel, dim3(grid), dim3(WT_SEL_THREADS), params, smem, stream));

@@ -10,10 +10,9 @@
 // constant-bank operand taken from the __grid_constant__ kernel parameter).  A CTA's planes are one
 // contiguous span of global memory: it is staged through shared memory with a 1-D TMA bulk copy
 // (cp.async.bulk + mbarrier) and read back at an odd word stride (9, 25, 49 floats: conflict free).
-// Coefficients are stored block-interleaved: the 128 planes of a CTA own one contiguous [ncoef][128] block
-// (warps still read and write 32 consecutive floats), so any 16 KB tile of the select's stream holds every kind of
-// coefficient -- with a plain [ncoef][batch] layout the CTAs that drew the near-zero deep-level rows did all of the
-// select's candidate compaction while the rest waited at the grid barrier.
+// Coefficients are stored coefficient-major ([ncoef][batch]) so warps read and write them coalesced.  (A per-CTA
+// block-interleaved layout [batch / 128][ncoef][128] evens out the select's work per tile but costs more in these
+// kernels' DRAM locality than it saves there: ResNet-152 1.19 -> 1.42 ms.  Measured and dropped.)
 //
 // Arithmetic follows oracle/dwt_oracle.c exactly (fp32, multiply then add, no FMA, same order).
 #include "wt_common.cuh"
@@ -267,18 +266,6 @@ __device__ __forceinline__ void stage_in(float* s, const float* __restrict__ g, 
     }
 }
 
-// real coefficients per plane of an H x W periodization decomposition (same as wt_small_ncoef)
-template <int H, int W>
-__device__ __forceinline__ int small_ncoef(int level) {
-    int n = 0, h = H, w = W;
-    for (int l = 0; l < level; ++l) {
-        h = (h + 1) / 2;
-        w = (w + 1) / 2;
-        n += 3 * h * w;
-    }
-    return n + h * w;
-}
-
 template <int HW>
 __device__ __forceinline__ void stage_out(float* g, const float* s, int cnt) {
     const unsigned int bytes = (unsigned int)cnt * HW * 4u;
@@ -317,10 +304,9 @@ wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __
             x[i] = s_in[threadIdx.x * HW + i];
             nz += (x[i] != 0.0f);
         }
-        // block-interleaved: this CTA's cnt planes own one contiguous [ncoef][cnt] block
-        float* __restrict__ cbase = job.coef + p0 * small_ncoef<H, W>(job.level) + threadIdx.x;
-        const int stride = cnt;
-        auto put = [&](int idx, float v) { cbase[idx * stride] = v; };
+        float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
+        const long long stride = job.batch;
+        auto put = [&](int idx, float v) { cbase[(long long)idx * stride] = v; };
         SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::analyze(x, job.level, bk, put);
     }
     // nonzeros of the input (dwt_pruning_NoEntropy.py:58) and numel
@@ -353,10 +339,10 @@ wt_small_synthesis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* _
     unsigned int zc = 0;
     if ((int)threadIdx.x < cnt) {
         float x[HW];
-        const float* __restrict__ cbase = job.coef + p0 * small_ncoef<H, W>(job.level) + threadIdx.x;
-        const int stride = cnt;
+        const float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
+        const long long stride = job.batch;
         auto get = [&](int idx) {
-            const float c = __ldg(&cbase[idx * stride]);
+            const float c = __ldg(&cbase[(long long)idx * stride]);
             return (fabsf(c) < t) ? 0.0f : c;  // np.where(|c| < t, 0, c), strict (dwt_pruning.py:31)
         };
         SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::synthesize(x, job.level, bk, get);
