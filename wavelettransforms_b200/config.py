@@ -6,9 +6,15 @@ numpy_semantics: which NumPy's np.percentile arithmetic the threshol
   'nep50_2x'    -- NumPy >= 2 (the NumPy installed on the GPU box); float32 index/lerp.
 Override with the environment variable WT_NUMPY_SEMANTICS or by assigning to this attribute.
 
+async_save: save_model snapshots the state dict and writes it from a background thread, so the next
+pruning method starts while safetensors serialises (once the kernels take microseconds, `save_pretrained` IS the
+critical path of main_pruning.py:175-209).  Off by default: the reference returns with the files on disk.
+utils.wait_for_saves() joins; it also runs at interpreter exit.
+
 verbose: re-enables the reference's per-layer debug prints (dwt_pruning.py:29-30,121-122).
 """
 import os
 
 numpy_semantics = os.environ.get('WT_NUMPY_SEMANTICS', 'legacy_1_22')
 verbose = os.environ.get('WT_VERBOSE', '0') not in ('0', '', 'false', 'False')
+async_save = os.environ.get('WT_ASYNC_SAVE', '0') not in ('0', '', 'false', 'False')

@@ -21,14 +21,57 @@ def load_model(model_path, config_path=None):
     return AutoModelForImageClassification.from_pretrained(model_path)
 
 
-def save_model(model, output_dir):
-    """utils.py:28-38"""
+_save_pool = None
+_pending_saves = []
+
+
+def _write_model(model, output_dir, state_dict=None):
     os.makedirs(output_dir, exist_ok=True)
     if hasattr(model, 'save_pretrained'):
-        model.save_pretrained(output_dir)
+        if state_dict is None:
+            model.save_pretrained(output_dir)
+        else:
+            model.save_pretrained(output_dir, state_dict=state_dict)
     else:
         import torch
-        torch.save(model.state_dict(), os.path.join(output_dir, 'pytorch_model.bin'))
+        torch.save(model.state_dict() if state_dict is None else state_dict, os.path.join(output_dir, 'pytorch_model.bin'))
+
+
+def save_model(model, output_dir):
+    """utils.py:28-38.  With config.async_save the tensors are snapshotted here (device tensors through pinned
+    host memory, non-blocking) and the serialisation runs on a background thread; wait_for_saves() joins."""
+    from . import config
+    if not config.async_save:
+        _write_model(model, output_dir)
+        return None
+    import atexit
+    from concurrent.futures import ThreadPoolExecutor
+
+    import torch
+    global _save_pool
+    if _save_pool is None:
+        _save_pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix='wt-save')
+        atexit.register(wait_for_saves)
+    snap, on_device = {}, False
+    for k, v in model.state_dict().items():
+        v = v.detach()
+        if v.is_cuda:
+            h = torch.empty(v.shape, dtype=v.dtype, pin_memory=True)
+            h.copy_(v, non_blocking=True)
+            snap[k], on_device = h, True
+        else:
+            snap[k] = v.clone()
+    if on_device:
+        torch.cuda.current_stream().synchronize()
+    fut = _save_pool.submit(_write_model, model, output_dir, snap)
+    _pending_saves.append(fut)
+    return fut
+
+
+def wait_for_saves():
+    """joins every background save started by save_model; re-raises the first failure"""
+    while _pending_saves:
+        _pending_saves.pop(0).result()
 
 
 def setup_csv_writer(file_path, mode='w'):
