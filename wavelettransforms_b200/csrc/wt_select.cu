@@ -774,6 +774,17 @@ __device__ void phase_tail(const WtSelArgs& a, Shared& sh) {
             r1 = f.r1;
             prev = s;
         }
+        // both order statistics and the threshold, the way final_keys / P4 form them
+        const unsigned long long ez = lo_key == 0u ? below : 0ull;  // exact zeros among the explicit keys
+        const unsigned int key0 = (job.k0 < job.zeros || e0 < ez) ? 0u : lo_key + pre0;
+        const unsigned int key1 = (job.k1 < job.zeros || e1 < ez) ? 0u : lo_key + pre1;
+        const float t = lerp_threshold(__uint_as_float(key0), __uint_as_float(key1), job.gamma, job.lerp_mode);
+        if (threadIdx.x == 0) {
+            st->a = __uint_as_float(key0);
+            st->b = __uint_as_float(key1);
+            st->t = t;
+            a.thresholds[job.layer] = t;
+        }
         if (threadIdx.x == 0) {
             st->tail_key[0] = pre0;
             st->tail_key[1] = pre1;
@@ -1016,6 +1027,7 @@ __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
         if (!job.out && base != 0) return;  // select-only job: its first-tile CTA publishes, nobody applies
         WtSelState* st = &a.state[j];
+        if (!job.out && __ldcg(&st->tail_done)) return;  // the one-CTA tail already published a, b and the threshold
         acc.begin();
         unsigned int key0, key1;
         final_keys(a, sh, j, job, key0, key1);
