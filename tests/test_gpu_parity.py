@@ -269,10 +269,14 @@ def _sample_windows(n, shift):
     return ((idx & 4095) >> (12 - shift)) == win
 
 
-@pytest.fixture
-def sampled_path(monkeypatch):
-    """launches below 40 Mi keys take the radix path by default: force the sampled one (read at every launch)"""
+@pytest.fixture(params=['default', '0', '3000', '4194304'])
+def sampled_path(monkeypatch, request):
+    """launches below 40 Mi keys take the radix path unless their candidate lists are predicted short: force the
+    sampled one (read at every launch), with the one-CTA tail at its default size, switched off (every list takes the
+    grid-wide passes C1..C3), tiny (tail and grid-wide jobs side by side in one launch) and unbounded"""
     monkeypatch.setenv('WT_SELECT_PATH', 'sampled')
+    if request.param != 'default':
+        monkeypatch.setenv('WT_SEL_TAIL_MAX', request.param)
 
 
 def test_select_sampled_path_adversarial(mods, sampled_path):
@@ -341,6 +345,27 @@ print('forced path ok')
     env = dict(os.environ, WT_SELECT_PATH=path)
     r = subprocess.run([sys.executable, '-c', code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and 'forced path ok' in r.stdout, r.stdout + r.stderr
+
+
+def test_select_path_prediction_and_tail_on_deep_small_planes(mods, monkeypatch):
+    """the headline shape in small: unclamped level 5 on 3x3 planes puts the percentile rank a few percent into the
+    explicit keys (padding zeros and vanishing details sort first), the plan predicts short candidate lists and takes
+    sampled + tail without being told; same bits as the oracle, and as the radix path forced on the same input"""
+    dp, rf = mods['dp'], mods['rf']
+    monkeypatch.delenv('WT_SELECT_PATH', raising=False)
+    g = torch.Generator().manual_seed(31)
+    ws = [torch.randn(256, 256, 3, 3, generator=g) * 0.02, torch.randn(64, 3, 7, 7, generator=g) * 0.1,
+          torch.randn(512, 128, 1, 1, generator=g) * 0.05]
+    for p in (50.0, 20.0, 75.0):
+        got, gz = dp.multi_resolution_analysis(ws, 'bior4.4', 5, p, clamp_level=False)
+        want, wz = rf.multi_resolution_analysis(ws, 'bior4.4', 5, p, numpy_semantics='legacy_1_22', clamp_level=False)
+        monkeypatch.setenv('WT_SELECT_PATH', 'radix')
+        rad, rz = dp.multi_resolution_analysis(ws, 'bior4.4', 5, p, clamp_level=False)
+        monkeypatch.delenv('WT_SELECT_PATH')
+        assert gz == wz == rz
+        for a, b, c in zip(got, want, rad):
+            assert_bit_equal(a, b, f'auto path p={p}')
+            assert_bit_equal(c, b, f'radix path p={p}')
 
 
 def test_select_default_path_at_scale(mods):
