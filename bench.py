@@ -544,8 +544,38 @@ def time_layer_sharded(name, steps, warmup, world, dev):
         if gather and world > 1:
             torch.distributed.all_gather_into_tensor(flats[r], flats[r][rank * layout.shard_elems:(rank + 1) * layout.shard_elems])
 
+    # third mode: the kernels store every pruned weight into all ranks' buffers themselves (symmetric memory over NVLink,
+    # Plan.set_peers); the collective shrinks to one device-side barrier
+    peer = None
+    if world > 1 and not os.environ.get('WT_BENCH_NO_PEER_STORE'):
+        try:
+            peer = []
+            for r in range(R):
+                pb = sharded.PeerBuffer(layout, dev)
+                items = [(x.data_ptr(), layout.view(pb.flat, i).data_ptr()) + engine.plane_geometry(x.shape) + (levels[i],)
+                         for x, i in zip(plans[r][1], mine)]
+                pl = _lib.Plan(items, wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, pct, NUMPY_SEMANTICS)
+                pl.set_peers(pb.deltas)
+                peer.append((pl, pb))
+        except Exception as e:      # symmetric memory unavailable on this box, or a layer off the mirrored paths
+            print(f'[bench] peer-store mode unavailable: {e}', file=sys.stderr)
+            peer = None
+        ok = torch.tensor([1 if peer else 0], device=dev)
+        torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN)      # all ranks or none
+        if not int(ok.item()):
+            peer = None
+
+    def peer_step(i, _):
+        pl, pb = peer[i % R]
+        if mine:
+            pl.run(stream)
+        pb.barrier()
+
     out = {}
-    for label, gather in (('prune_only', False), ('prune_allgather', True)):
+    modes = [('prune_only', False, step), ('prune_allgather', True, step)]
+    if peer:
+        modes.append(('prune_peer_store', True, peer_step))
+    for label, gather, step in modes:
         for i in range(warmup):
             step(i, gather)
         torch.cuda.synchronize()
@@ -560,6 +590,16 @@ def time_layer_sharded(name, steps, warmup, world, dev):
         barrier(world)
         ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
         out[label] = {'value': elems * steps / (ms * 1e-3), 'ms_per_step': ms / steps}
+    if peer:
+        # the peer-stored buffer of every rank must equal the all-gathered one, bit for bit
+        step0 = modes[0][2]
+        step0(0, True)
+        peer_step(0, True)
+        torch.cuda.synchronize()
+        barrier(world)
+        out['prune_peer_store']['matches_allgather_bitwise'] = bool(torch.equal(flats[0], peer[0][1].flat))
+        for pl, _ in peer:
+            pl.close()
     for p, _ in plans:
         p.close()
     out.update(workload=name, scaling='strong', layers=len(census), elems=elems, lpt_balance=layout.balance,

@@ -139,6 +139,14 @@ int wt_plan_results(WtPlan* plan, void* stream, int64_t* counts, int64_t* nonzer
  * per-kernel durations; leave it off on the production path (each event costs ~1 us of stream time).
  */
 int wt_plan_set_timing(WtPlan* plan, int enable);
+/* Layer-sharded runs (north star: layers dealt to the GPUs of a box, the pruned state reassembled on every rank).
+ * Every rank's output tensors live in a flat buffer of ONE layout that is mapped into all peers (CUDA VMM /
+ * symmetric memory); byte_deltas[q] = (peer q's mapping of ITS buffer) - (this rank's buffer).  The kernels that
+ * store pruned weights then store each value a second time at out + byte_deltas[q] for every q -- plain global
+ * stores over NVLink, issued next to the arithmetic -- which replaces the all-gather after the last kernel.  The
+ * caller still needs one cross-rank barrier before reading.  n_peers = 0 switches it off.  WT_E_UNSUPPORTED for plans
+ * with layers on the generic tiled path or absolute thresholds (their kernels do not mirror stores). */
+int wt_plan_set_peers(WtPlan* plan, int n_peers, const int64_t* byte_deltas);
 int wt_plan_phase_times(WtPlan* plan, int max_phases, float* ms, int* launches, char* names,
                         int name_stride);
 /* device address of the int64 [n_layers][4] result block {numel, nonzero, zeros, nonzero_before} */

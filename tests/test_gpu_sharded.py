@@ -49,3 +49,27 @@ def test_sharded_gpu_matches_reference_flow(wtlib, oracle_lib, pg, wavelet, leve
     # inputs untouched (multi_resolution_analysis never modifies its input, dwt_pruning.py:84-85)
     for w, x in zip(host, ws):
         assert torch.equal(w, x.cpu())
+
+
+def test_sharded_gpu_peer_store_equals_allgather(wtlib, oracle_lib, pg):
+    """gather='peer_store': the synthesis kernels and the select's apply phase store every pruned weight into all
+    ranks' symmetric-memory buffers themselves; the result must be the all-gathered buffer bit for bit, on every rank.
+    Needs world_size > 1: `torchrun --nproc-per-node 2 -m pytest tests/test_gpu_sharded.py -m gpu`."""
+    if dist.get_world_size(pg) < 2:
+        pytest.skip('one rank: there is no peer to store into')
+    from oracle import reference_flow as rf
+    from wavelettransforms_b200 import sharded, workloads
+    census = workloads.conv_census('resnet18')[:12]
+    host = workloads.random_init_weights(census, seed=5)
+    dev = torch.device('cuda', torch.cuda.current_device())
+    ws = [w.to(dev) for w in host]
+    for wavelet, level, clamp in (('bior4.4', 5, False), ('bior4.4', 5, True), ('haar', 5, True)):
+        a, ca, flat_a, _ = sharded.prune_model_sharded(ws, wavelet, level, 50.0, clamp_level=clamp,
+                                                       numpy_semantics='legacy_1_22', group=pg)
+        b, cb, flat_b, _ = sharded.prune_model_sharded(ws, wavelet, level, 50.0, clamp_level=clamp,
+                                                       numpy_semantics='legacy_1_22', group=pg, gather='peer_store')
+        torch.cuda.synchronize()
+        assert torch.equal(flat_a, flat_b) and np.array_equal(ca, cb)
+        for i, w in enumerate(host):
+            want, _ = rf.multi_resolution_analysis([w], wavelet, level, 50.0, numpy_semantics='legacy_1_22', clamp_level=clamp)
+            assert np.array_equal(b[i].cpu().numpy().view(np.uint32), want[0].numpy().view(np.uint32)), census[i][0]

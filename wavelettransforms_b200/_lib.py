@@ -26,7 +26,7 @@ EXPORTS = [
     'wt_version', 'wt_last_error', 'wt_wavelet_lookup', 'wt_wavelet_filters', 'wt_dwt_max_level', 'wt_dwt_coeff_len',
     'wt_packed_shape', 'wt_percentile_plan', 'wt_plan_create', 'wt_plan_destroy', 'wt_plan_device_bytes',
     'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device',
-    'wt_plan_set_timing', 'wt_plan_phase_times',
+    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers',
     'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
     'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32',
 ]
@@ -63,6 +63,7 @@ def lib():
     L.wt_plan_results.argtypes = [vp, vp, P(i64), P(i64), P(fl)]
     L.wt_plan_counts_device.argtypes = [vp, P(vp)]
     L.wt_plan_set_timing.argtypes = [vp, ci]
+    L.wt_plan_set_peers.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_int64)]
     L.wt_plan_phase_times.argtypes = [vp, ci, P(fl), P(ci), ctypes.c_char_p, ci]
     L.wt_dwt_prune_f32.argtypes = [P(WtLayerDesc), ci, ci, ci, ci, dbl, ci, vp, P(i64), P(i64), P(fl)]
     L.wt_select_abs_f32.argtypes = [vp, i64, i64, i64, i64, vp, vp]
@@ -173,6 +174,12 @@ class Plan:
         check(lib().wt_plan_results(self._h, ctypes.c_void_p(stream), counts, nzb, thr))
         c = np.array(counts[:3 * self.n], dtype=np.int64).reshape(self.n, 3)
         return c, np.array(nzb[:self.n], dtype=np.int64), np.array(thr[:self.n], dtype=np.float32)
+
+    def set_peers(self, byte_deltas):
+        """mirror every output store at out + delta for each delta (peer mappings of the same flat buffer layout)"""
+        d = [int(x) for x in byte_deltas]
+        arr = (ctypes.c_int64 * max(len(d), 1))(*d)
+        check(lib().wt_plan_set_peers(self._h, len(d), arr))
 
     def set_timing(self, enable=True):
         check(lib().wt_plan_set_timing(self._h, 1 if enable else 0))

@@ -194,6 +194,7 @@ struct WtPlan {
     WtSelJob* sel_jobs_dev = nullptr;
     WtSelArgs sel_args;
     // zeroed every run: [select scratch | counts]
+    WtPeers peers = {};  // layer-sharded runs: byte distance to every peer's mapping of the output buffer
     char* zero_block = nullptr;
     size_t zero_bytes = 0;
     float* thresholds_dev = nullptr;
@@ -266,6 +267,7 @@ static int build_tables(WtPlan* P) {
             j.n_tiles = (int)((L.batch + WT_SMALL_THREADS - 1) / WT_SMALL_THREADS);
             j.abs_threshold = (float)P->thr_value;
             j.use_abs = pct ? 0 : 1;
+            j.peers = P->peers;
             cls->n_tiles += j.n_tiles;
             cls->jobs.push_back(j);
         } else if (P->path[i] == PATH_GENERIC) {
@@ -307,6 +309,7 @@ static int build_tables(WtPlan* P) {
     }
     P->sel_args.n_tiles = sel_tiles;
     P->sel_args.any_apply = any_apply ? 1 : 0;
+    P->sel_args.peers = P->peers;
     P->sel_args.short_lists = wt_select_predict_short(P->sel_jobs.data(), (int)P->sel_jobs.size());
     return WT_OK;
 }
@@ -665,6 +668,27 @@ extern "C" int wt_plan_set_io(WtPlan* P, const WtLayerDesc* layers, int n_layers
         }
     }
     if (P->host_io) return WT_OK;
+    int rc = build_tables(P);
+    if (rc) return rc;
+    return upload_tables(P);
+}
+
+extern "C" int wt_plan_set_peers(WtPlan* P, int n_peers, const int64_t* byte_deltas) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    WT_CHECK(n_peers >= 0 && n_peers <= WT_MAX_PEERS, WT_E_INVALID, "wt_plan_set_peers: 0..%d peers", WT_MAX_PEERS);
+    WT_CHECK(n_peers == 0 || byte_deltas != nullptr, WT_E_INVALID, "wt_plan_set_peers: NULL deltas");
+    WT_CHECK(!P->host_io, WT_E_UNSUPPORTED, "wt_plan_set_peers: host-I/O plans have no device output buffer to mirror");
+    if (n_peers > 0) {
+        // the kernels that mirror their stores: small-plane synthesis and the select's level-0 apply
+        WT_CHECK(P->thr_kind == WT_THRESHOLD_PERCENTILE, WT_E_UNSUPPORTED, "wt_plan_set_peers: percentile plans only");
+        for (size_t i = 0; i < P->layers.size(); ++i)
+            WT_CHECK(P->path[i] != PATH_GENERIC, WT_E_UNSUPPORTED,
+                     "wt_plan_set_peers: layer %d runs on the generic tiled path, which does not mirror its stores", (int)i);
+        for (int q = 0; q < n_peers; ++q)
+            WT_CHECK((byte_deltas[q] & 15) == 0, WT_E_INVALID, "wt_plan_set_peers: peer mappings must keep 16-byte alignment");
+    }
+    P->peers.n = n_peers;
+    for (int q = 0; q < n_peers; ++q) P->peers.delta[q] = (long long)byte_deltas[q];
     int rc = build_tables(P);
     if (rc) return rc;
     return upload_tables(P);

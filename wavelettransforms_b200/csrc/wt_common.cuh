@@ -50,6 +50,15 @@ int wt_idwt_len(int n, int F, int mode);
 // sizes[0] = n, sizes[l] = coefficient length at level l
 void wt_level_sizes(int n, int F, int mode, int level, int* sizes);
 
+// Layer-sharded runs (sharded.py): every rank owns a flat buffer of the same layout, mapped into every peer (CUDA VMM /
+// symmetric memory); a kernel that stores a pruned weight also stores it at the same offset of each peer's buffer --
+// plain st.global over NVLink -- so the all-gather happens under the arithmetic instead of after it.
+#define WT_MAX_PEERS 7
+struct WtPeers {
+    int n;
+    long long delta[WT_MAX_PEERS];  // byte distance from this rank's buffer to the peer's mapping of its own
+};
+
 // ---- select (wt_select.cu) ----------------------------------------------------------------------
 // One job = one population whose order statistics are wanted: the explicit values x[0..n) plus
 // `zeros` implicit zeros (coeffs_to_array padding).  Jobs with out != nullptr also get the
@@ -114,6 +123,7 @@ struct WtSelArgs {
     unsigned long long* hist3;  // [n_jobs][2][CBINS]  (radix path: [2][BINS3] inside the same slot)
     int* fail_flag;             // set when any job leaves the sampled path
     int* wide_flag;             // set when any job's bracket is wider than 16 bins: the grid runs candidate pass C3
+    WtPeers peers;              // level-0 apply: out is also stored at out + delta of every peer
     unsigned int tail_max;      // longest candidate list the one-CTA tail takes (resolved at launch; 0: no tail)
     int short_lists;            // host hint (wt_select_predict_short): every job's candidate list should fit the one-CTA tail
     int* big_flag;              // set when any job's candidate list is too long for the one-CTA tail: the grid runs C1..C3
@@ -186,6 +196,7 @@ struct WtSmallJob {
     int n_tiles;
     float abs_threshold;
     int use_abs;       // 1: compare against abs_threshold, 0: against thresholds[layer]
+    WtPeers peers;     // synthesis: the output tile is also stored at out + delta of every peer
 };
 
 // true when (H, W, F, level, mode) has a register-resident instantiation

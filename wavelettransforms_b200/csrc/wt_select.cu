@@ -1066,12 +1066,18 @@ __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_
                         r[u].x = apply_one(r[u].x, t, zc, nzb); r[u].y = apply_one(r[u].y, t, zc, nzb);
                         r[u].z = apply_one(r[u].z, t, zc, nzb); r[u].w = apply_one(r[u].w, t, zc, nzb);
                         __stcs(&o4[v + (long long)u * T], r[u]);
+                        for (int q = 0; q < a.peers.n; ++q)  // layer-sharded run: the same slot of every peer's buffer
+                            __stcs(reinterpret_cast<float4*>(reinterpret_cast<char*>(&o4[v + (long long)u * T]) + a.peers.delta[q]), r[u]);
                     }
                 }
             }
             done = nvec << 2;
         }
-        for (long long i = done + threadIdx.x; i < len; i += T) o[i] = apply_one(x[i], t, zc, nzb);
+        for (long long i = done + threadIdx.x; i < len; i += T) {
+            const float w = apply_one(x[i], t, zc, nzb);
+            o[i] = w;
+            for (int q = 0; q < a.peers.n; ++q) *reinterpret_cast<float*>(reinterpret_cast<char*>(&o[i]) + a.peers.delta[q]) = w;
+        }
         // every element of the span is visited exactly once: thread 0 contributes the span length
         block_add3(a.counts + (size_t)job.layer * 4, zc, nzb, threadIdx.x == 0 ? (unsigned int)len : 0u, sh.hist);
         acc.end(14);
@@ -1184,6 +1190,7 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
     a->big_flag = a->fail_flag + 2;
     a->path = -1;  // resolved at launch: wt_select_path()
     a->short_lists = 0;
+    a->peers.n = 0;
     a->stamps = nullptr;  // tuning aid, set by the plan when WT_SELECT_STAMPS is in the environment
     a->cta_tiles = nullptr;
     a->cta_job = nullptr;

@@ -353,6 +353,18 @@ wt_small_synthesis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* _
         }
     }
     stage_out<HW>(job.out + p0 * HW, s_out, cnt);
+    if (job.peers.n) {  // layer-sharded run: the staged tile also goes to the same slot of every peer's buffer
+        const int nel = cnt * HW;
+        for (int q = 0; q < job.peers.n; ++q) {
+            float* g = reinterpret_cast<float*>(reinterpret_cast<char*>(job.out + p0 * HW) + job.peers.delta[q]);
+            if (((reinterpret_cast<uintptr_t>(g) & 15u) == 0) && (nel & 3) == 0) {
+                for (int i = threadIdx.x; i < (nel >> 2); i += WT_SMALL_THREADS)
+                    reinterpret_cast<float4*>(g)[i] = reinterpret_cast<const float4*>(s_out)[i];
+            } else {
+                for (int i = threadIdx.x; i < nel; i += WT_SMALL_THREADS) g[i] = s_out[i];
+            }
+        }
+    }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) zc += __shfl_down_sync(0xffffffffu, zc, d);
     if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = zc;

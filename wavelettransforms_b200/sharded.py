@@ -19,15 +19,15 @@ import torch.distributed as dist
 
 from . import workloads
 
-PruneFn = Callable[[List[torch.Tensor], List[torch.Tensor], List[int]], np.ndarray]
+PruneFn = Callable[..., np.ndarray]     # (xs, outs, levels[, peer_deltas]) -> counts [n, 4]
 
 
 def _gpu_prune_fn(wavelet, mode, threshold_kind, threshold_value, numpy_semantics) -> PruneFn:
     from . import engine
 
-    def fn(xs, outs, levels):
+    def fn(xs, outs, levels, peer_deltas=None):
         res = engine.prune_device_tensors(xs, levels, wavelet, mode, threshold_kind, threshold_value, numpy_semantics,
-                                          outs=outs)
+                                          outs=outs, peer_deltas=peer_deltas)
         c = np.zeros((len(xs), 4), dtype=np.int64)
         c[:, :3] = res.counts
         c[:, 3] = res.nonzero_before
@@ -64,28 +64,67 @@ class ShardLayout:
         return flat[base:base + self.numels[i]].view(self.shapes[i])
 
 
+class PeerBuffer:
+    """The flat [world][shard_elems] fp32 buffer of a ShardLayout, allocated in symmetric memory (CUDA VMM, every
+    rank's copy mapped into every peer over NVLink) so the pruning kernels can store each pruned weight into all
+    ranks' buffers themselves (`Plan.set_peers`): the all-gather happens under the arithmetic, tile by tile, and
+    what is left of the collective is one barrier."""
+
+    def __init__(self, layout: ShardLayout, device, group: Optional[dist.ProcessGroup] = None):
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group or dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.flat = symm_mem.empty(self.world * layout.shard_elems, dtype=torch.float32, device=device)
+        self.handle = symm_mem.rendezvous(self.flat, group.group_name)
+        mine = int(self.handle.buffer_ptrs[self.rank])
+        if mine != self.flat.data_ptr():
+            raise RuntimeError('symmetric memory: the local mapping is not the tensor itself')
+        # byte distance from this rank's buffer to each peer's mapping of its own
+        self.deltas = [int(p) - mine for r, p in enumerate(self.handle.buffer_ptrs) if r != self.rank]
+        self.flat.zero_()               # slot padding reads as zero, like the torch.zeros buffer of the NCCL mode
+        torch.cuda.current_stream().synchronize()
+        self.handle.barrier()           # nobody stores into a peer that is still clearing
+
+    def barrier(self):
+        """device-side barrier on the current stream (signal pads): every rank's stores have landed after it"""
+        self.handle.barrier()
+
+
 def prune_sharded(weights: List[torch.Tensor], levels: Sequence[int], prune_fn: PruneFn,
                   group: Optional[dist.ProcessGroup] = None, layout: Optional[ShardLayout] = None,
-                  gather: bool = True):
+                  gather=True, peer_buffer: Optional[PeerBuffer] = None):
     """weights: the full (replicated) list on this rank's device.  Returns (pruned tensors -- views into
     the gathered flat buffer, every layer present on every rank --, counts int64 [n_layers, 4]:
     numel, nonzero after, zeros after, nonzero before; flat buffer; layout).  gather=False skips both
-    collectives (prune-only timing): then only the owned layers' views are meaningful."""
+    collectives (prune-only timing): then only the owned layers' views are meaningful.  gather='peer_store'
+    (CUDA, world > 1): the flat buffer lives in symmetric memory and the kernels store into every rank's copy
+    themselves; one device-side barrier replaces the all-gather (pass `peer_buffer` to reuse an allocation)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     layout = layout or ShardLayout([w.shape for w in weights], world)
     dev = weights[0].device if weights else torch.device('cpu')
-    flat = torch.zeros(world * layout.shard_elems, dtype=torch.float32, device=dev)
+    peer = gather == 'peer_store' and world > 1
+    if peer:
+        peer_buffer = peer_buffer or PeerBuffer(layout, dev, group)
+        flat = peer_buffer.flat
+    else:
+        flat = torch.zeros(world * layout.shard_elems, dtype=torch.float32, device=dev)
     mine = layout.owned(rank)
     my_shard = flat[rank * layout.shard_elems:(rank + 1) * layout.shard_elems]
     xs = [weights[i].contiguous() for i in mine]
     outs = [layout.view(flat, i) for i in mine]          # kernels store straight into the send slot
     counts_local = torch.zeros((len(weights), 4), dtype=torch.int64)
     if mine:
-        c = prune_fn(xs, outs, [int(levels[i]) for i in mine])
+        if peer:
+            c = prune_fn(xs, outs, [int(levels[i]) for i in mine], peer_deltas=peer_buffer.deltas)
+        else:
+            c = prune_fn(xs, outs, [int(levels[i]) for i in mine])
         counts_local[mine] = torch.from_numpy(np.asarray(c, dtype=np.int64))
     counts = counts_local.to(dev)
-    if gather and world > 1:
+    if peer:
+        peer_buffer.barrier()
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
+    elif gather and world > 1:
         dist.all_gather_into_tensor(flat, my_shard.clone() if dev.type == 'cpu' else my_shard, group=group)
         # every layer has exactly one owner and the others contribute zeros: a sum is the gather of the counts
         dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
@@ -95,7 +134,7 @@ def prune_sharded(weights: List[torch.Tensor], levels: Sequence[int], prune_fn: 
 
 def prune_model_sharded(weights: List[torch.Tensor], wavelet: str, level: int, percentile: float, *,
                         mode: str = 'periodization', clamp_level: bool = True, numpy_semantics: Optional[str] = None,
-                        group: Optional[dist.ProcessGroup] = None, gather: bool = True):
+                        group: Optional[dist.ProcessGroup] = None, gather=True):
     """dwt_pruning.wavelet_pruning's per-layer loop (dwt_pruning.py:155-164), layer-sharded.  Each layer is
     its own multi_resolution_analysis call in the reference, so the clamp (:64-65) is per layer."""
     from . import _lib, config
