@@ -278,6 +278,20 @@ __device__ __forceinline__ void stage_out(float* g, const float* s, int cnt) {
     }
 }
 
+// stores the CTA's staged output tile at the same slot of every peer's buffer (plain global stores over NVLink)
+__device__ __noinline__ void mirror_tile(const float* s, float* out, const WtPeers* __restrict__ peers, int nel) {
+    const int n = __ldg(&peers->n);
+    for (int q = 0; q < n; ++q) {
+        float* g = reinterpret_cast<float*>(reinterpret_cast<char*>(out) + __ldg(&peers->delta[q]));
+        if (((reinterpret_cast<uintptr_t>(g) & 15u) == 0) && (nel & 3) == 0) {
+            for (int i = threadIdx.x; i < (nel >> 2); i += WT_SMALL_THREADS)
+                reinterpret_cast<float4*>(g)[i] = reinterpret_cast<const float4*>(s)[i];
+        } else {
+            for (int i = threadIdx.x; i < nel; i += WT_SMALL_THREADS) g[i] = s[i];
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------------
@@ -353,18 +367,9 @@ wt_small_synthesis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* _
         }
     }
     stage_out<HW>(job.out + p0 * HW, s_out, cnt);
-    if (job.peers.n) {  // layer-sharded run: the staged tile also goes to the same slot of every peer's buffer
-        const int nel = cnt * HW;
-        for (int q = 0; q < job.peers.n; ++q) {
-            float* g = reinterpret_cast<float*>(reinterpret_cast<char*>(job.out + p0 * HW) + job.peers.delta[q]);
-            if (((reinterpret_cast<uintptr_t>(g) & 15u) == 0) && (nel & 3) == 0) {
-                for (int i = threadIdx.x; i < (nel >> 2); i += WT_SMALL_THREADS)
-                    reinterpret_cast<float4*>(g)[i] = reinterpret_cast<const float4*>(s_out)[i];
-            } else {
-                for (int i = threadIdx.x; i < nel; i += WT_SMALL_THREADS) g[i] = s_out[i];
-            }
-        }
-    }
+    // layer-sharded run: the staged tile also goes to the same slot of every peer's buffer (out of line and through the
+    // job table in global memory, so the single-GPU kernel keeps its registers and instruction stream)
+    if (__ldg(&jobs[j].peers.n)) mirror_tile(s_out, job.out + p0 * HW, &jobs[j].peers, cnt * HW);
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) zc += __shfl_down_sync(0xffffffffu, zc, d);
     if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = zc;
