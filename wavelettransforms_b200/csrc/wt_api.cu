@@ -297,6 +297,7 @@ static int build_tables(WtPlan* P) {
             j.cand = P->d_cand[i];
             j.cand_cap = P->cand_cap[i];
             j.sample_shift = wt_select_sample_shift(j.n);
+            if (l0) j.peers = P->peers;
             j.tile_begin = sel_tiles;
             const long long nt = (j.n + WT_SEL_TILE - 1) / WT_SEL_TILE;
             WT_CHECK(sel_tiles + nt < 2147483647LL, WT_E_UNSUPPORTED, "too many select tiles");
@@ -309,7 +310,6 @@ static int build_tables(WtPlan* P) {
     }
     P->sel_args.n_tiles = sel_tiles;
     P->sel_args.any_apply = any_apply ? 1 : 0;
-    P->sel_args.peers = P->peers;
     P->sel_args.short_lists = wt_select_predict_short(P->sel_jobs.data(), (int)P->sel_jobs.size());
     return WT_OK;
 }

@@ -90,6 +90,7 @@ struct WtSelJob {
     int layer;       // index into the counts / thresholds arrays
     unsigned int cand_cap;  // capacity of cand[] in keys
     int sample_shift;       // sampled path: S0 reads 4096 >> sample_shift elements of every 4096-element tile
+    WtPeers peers;          // level-0 apply: out is also stored at out + delta of every peer (read from the job table)
 };
 
 struct WtSelState {  // per job, device; written by the CTA that holds the job's first tile
@@ -123,7 +124,6 @@ struct WtSelArgs {
     unsigned long long* hist3;  // [n_jobs][2][CBINS]  (radix path: [2][BINS3] inside the same slot)
     int* fail_flag;             // set when any job leaves the sampled path
     int* wide_flag;             // set when any job's bracket is wider than 16 bins: the grid runs candidate pass C3
-    WtPeers peers;              // level-0 apply: out is also stored at out + delta of every peer
     unsigned int tail_max;      // longest candidate list the one-CTA tail takes (resolved at launch; 0: no tail)
     int short_lists;            // host hint (wt_select_predict_short): every job's candidate list should fit the one-CTA tail
     int* big_flag;              // set when any job's candidate list is too long for the one-CTA tail: the grid runs C1..C3

@@ -1022,6 +1022,26 @@ __device__ void phase3_hist_cand(const WtSelArgs& a, Shared& sh, int t_begin, in
     });
 }
 
+// stores o[0..len) at the same offset of every peer's buffer; the thread -> element mapping is the apply loop's
+__device__ __noinline__ void mirror_span(const float* o, long long len, const WtPeers* __restrict__ peers) {
+    const int np = __ldg(&peers->n);
+    long long done = 0;
+    if ((reinterpret_cast<uintptr_t>(o) & 15u) == 0) {
+        const long long nvec = len >> 2;
+        const float4* o4 = reinterpret_cast<const float4*>(o);
+        for (long long v = threadIdx.x; v < nvec; v += T) {
+            const float4 r = o4[v];
+            for (int q = 0; q < np; ++q)
+                __stcs(reinterpret_cast<float4*>(reinterpret_cast<char*>(const_cast<float4*>(&o4[v])) + __ldg(&peers->delta[q])), r);
+        }
+        done = nvec << 2;
+    }
+    for (long long i = done + threadIdx.x; i < len; i += T) {
+        const float w = o[i];
+        for (int q = 0; q < np; ++q) *reinterpret_cast<float*>(reinterpret_cast<char*>(const_cast<float*>(&o[i])) + __ldg(&peers->delta[q])) = w;
+    }
+}
+
 // ---- P4: threshold from hist3; apply: out = |x| < t ? 0 : x, counts ----------------------------------------
 __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
@@ -1066,18 +1086,15 @@ __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_
                         r[u].x = apply_one(r[u].x, t, zc, nzb); r[u].y = apply_one(r[u].y, t, zc, nzb);
                         r[u].z = apply_one(r[u].z, t, zc, nzb); r[u].w = apply_one(r[u].w, t, zc, nzb);
                         __stcs(&o4[v + (long long)u * T], r[u]);
-                        for (int q = 0; q < a.peers.n; ++q)  // layer-sharded run: the same slot of every peer's buffer
-                            __stcs(reinterpret_cast<float4*>(reinterpret_cast<char*>(&o4[v + (long long)u * T]) + a.peers.delta[q]), r[u]);
                     }
                 }
             }
             done = nvec << 2;
         }
-        for (long long i = done + threadIdx.x; i < len; i += T) {
-            const float w = apply_one(x[i], t, zc, nzb);
-            o[i] = w;
-            for (int q = 0; q < a.peers.n; ++q) *reinterpret_cast<float*>(reinterpret_cast<char*>(&o[i]) + a.peers.delta[q]) = w;
-        }
+        for (long long i = done + threadIdx.x; i < len; i += T) o[i] = apply_one(x[i], t, zc, nzb);
+        // layer-sharded run: the span just written (every thread re-reads exactly what it stored, still in L2) also goes
+        // to the same slot of every peer's buffer; out of line so the single-GPU loop keeps its registers
+        if (__ldg(&a.jobs[j].peers.n)) mirror_span(o, len, &a.jobs[j].peers);
         // every element of the span is visited exactly once: thread 0 contributes the span length
         block_add3(a.counts + (size_t)job.layer * 4, zc, nzb, threadIdx.x == 0 ? (unsigned int)len : 0u, sh.hist);
         acc.end(14);
@@ -1190,7 +1207,6 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
     a->big_flag = a->fail_flag + 2;
     a->path = -1;  // resolved at launch: wt_select_path()
     a->short_lists = 0;
-    a->peers.n = 0;
     a->stamps = nullptr;  // tuning aid, set by the plan when WT_SELECT_STAMPS is in the environment
     a->cta_tiles = nullptr;
     a->cta_job = nullptr;
