@@ -16,7 +16,9 @@ LIBDIR = os.path.join(HERE, 'lib')
 OBJDIR = os.path.join(HERE, 'build')
 LIB = os.path.join(LIBDIR, 'libwtprune.so')
 
-SOURCES = ['wt_api.cu', 'wt_select.cu', 'wt_small.cu', 'wt_generic.cu', 'wt_maskers.cu', 'wt_blocks.cu']
+SOURCES = ['wt_fused_s7.cu', 'wt_fused_s5.cu', 'wt_fused_s3.cu', 'wt_fused_s1.cu', 'wt_fused_s7f.cu', 'wt_fused_s5f.cu', 'wt_fused_s3f.cu',
+           'wt_fused_s1f.cu', 'wt_small.cu', 'wt_fused_flat.cu', 'wt_api.cu', 'wt_select.cu', 'wt_generic.cu', 'wt_maskers.cu',
+           'wt_blocks.cu']  # heaviest first
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17', '-fmad=false',
               '-diag-suppress', '177', '-Xcompiler', '-fPIC']
 
@@ -32,7 +34,7 @@ def _deps_mtime():
     m = 0.0
     for d in (CSRC, os.path.join(os.path.dirname(HERE), 'include')):
         for f in os.listdir(d):
-            if f.endswith(('.cu', '.cuh', '.h')):
+            if f.endswith(('.cu', '.cuh', '.h', '.inc')):
                 m = max(m, os.path.getmtime(os.path.join(d, f)))
     return m
 
@@ -45,7 +47,7 @@ def build_library(force=False, verbose=False):
     nvcc = _nvcc()
     hdr_m = max(os.path.getmtime(os.path.join(d, f))
                 for d in (CSRC, os.path.join(os.path.dirname(HERE), 'include'))
-                for f in os.listdir(d) if f.endswith(('.cuh', '.h')))
+                for f in os.listdir(d) if f.endswith(('.cuh', '.h', '.inc')))
 
     def compile_one(src):
         s = os.path.join(CSRC, src)
@@ -60,7 +62,7 @@ def build_library(force=False, verbose=False):
             raise RuntimeError(f'nvcc failed for {src}:\n{r.stdout}\n{r.stderr}')
         return o
 
-    with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
+    with ThreadPoolExecutor(max_workers=min(os.cpu_count() or 4, len(SOURCES))) as ex:
         objs = list(ex.map(compile_one, SOURCES))
     cmd = [nvcc, '-shared', '-o', LIB] + objs + ['-gencode', 'arch=compute_100a,code=sm_100a', '-lcudart']
     r = subprocess.run(cmd, capture_output=True, text=True)

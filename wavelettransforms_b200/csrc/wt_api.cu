@@ -169,7 +169,21 @@ extern "C" int wt_percentile_plan(int64_t n, double p, int sem, int64_t* k0, int
 }
 
 // ---- plans ------------------------------------------------------------------------------------------------
-enum { PATH_EMPTY = 0, PATH_LEVEL0 = 1, PATH_SMALL = 2, PATH_GENERIC = 3 };
+enum { PATH_EMPTY = 0, PATH_LEVEL0 = 1, PATH_SMALL = 2, PATH_GENERIC = 3, PATH_FUSED = 4 };
+
+// one persistent fused launch (wt_fused.cuh): the flat class (H = W = 0: every level-0 tensor) or one small-plane size
+struct FusedClass {
+    int H = 0, W = 0;
+    std::vector<int> layers;       // plan layer of every job, in job order (ascending population)
+    std::vector<WtFJob> jobs;
+    std::vector<WtFSeg> segs;
+    WtFJob* jobs_dev = nullptr;
+    WtFSeg* segs_dev = nullptr;
+    char* scratch[2] = {nullptr, nullptr};
+    size_t scratch_bytes = 0;
+    int parity = 0;                // scratch block the next run uses (the run zeroes the other one for the run after)
+    int n_tickets = 0, n_select = 0;
+};
 
 struct SmallClass {
     int H, W;
@@ -201,6 +215,9 @@ struct WtPlan {
     long long* counts_dev = nullptr;
 
     std::vector<SmallClass> small;
+    std::vector<FusedClass> fused;
+    int arithmetic = 0;  // 0: faithful (no FMA, the oracle's arithmetic), 1: fma_taporder (wt_plan_set_arithmetic)
+    bool legacy_zero = false;  // some launch still accumulates into the zeroed block (generic path, legacy kernels)
     std::vector<WtGenericLayer> generic;
     std::vector<int> level0_abs;  // layers pruned by the plain threshold kernel (absolute, level 0)
 
@@ -242,6 +259,69 @@ static size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
 static long long layer_numel(const WtLayerDesc& L) { return L.batch * (long long)L.H * L.W; }
 
+// job tables and ticket queues of the fused classes (wt_fused.cuh)
+static int build_fused_tables(WtPlan* P) {
+    const bool pct = (P->thr_kind == WT_THRESHOLD_PERCENTILE);
+    for (auto& c : P->fused) {
+        c.jobs.clear();
+        c.segs.clear();
+        c.n_select = 0;
+        for (int i : c.layers) {
+            const WtLayerDesc& L = P->layers[i];
+            WtFJob j;
+            memset(&j, 0, sizeof(j));
+            j.in = P->d_in[i]; j.out = P->d_out[i];
+            j.level = L.level; j.layer = i;
+            j.abs_threshold = (float)P->thr_value;
+            long long keys_per_unit = 1;
+            if (c.H == 0) {
+                j.units = layer_numel(L);
+            } else {
+                j.units = L.batch;
+                keys_per_unit = P->ncoef[i] / L.batch;
+                j.zeros = P->zeros[i];
+            }
+            wt_fused_geometry(c.H, c.W, &j, keys_per_unit);
+            WT_CHECK(j.n < (1LL << 31), WT_E_UNSUPPORTED, "layer %d: population too large for the fused path", i);
+            if (pct) {
+                int64_t k0, k1; double gamma;
+                int rc = wt_percentile_plan(j.n + j.zeros, P->thr_value, P->sem, &k0, &k1, &gamma);
+                if (rc) return rc;
+                j.k0 = k0; j.k1 = k1; j.gamma = gamma;
+                j.lerp_mode = (P->sem == WT_NUMPY_LEGACY_1_22) ? WT_LERP_LEGACY : WT_LERP_NEP50;
+                j.cand = P->d_cand[i];
+                j.cand_cap = P->cand_cap[i];
+                ++c.n_select;
+            } else {
+                j.lerp_mode = WT_LERP_ABSOLUTE;
+            }
+            j.peers = P->peers;
+            c.jobs.push_back(j);
+        }
+        // the ticket queue: every S first, then a software pipeline over the jobs, smallest first --
+        // position p holds C(p), F2(p-1), F3(p-2), A(p-3) -- so the stage hand-overs of a job hide under its neighbours'
+        // streaming passes and the exposed end of the queue is the apply of the largest jobs
+        const int nj = (int)c.jobs.size();
+        int ticket = 0;
+        auto seg = [&](int stage, int job, int count) {
+            if (count <= 0) return;
+            WtFSeg g = {ticket, count, stage, job};
+            c.segs.push_back(g);
+            ticket += count;
+        };
+        if (pct)
+            for (int j = 0; j < nj; ++j) seg(WT_ST_S, j, c.jobs[j].s_chunks);
+        for (int p = 0; p < nj + 3; ++p) {
+            if (pct && p < nj) seg(WT_ST_C, p, c.jobs[p].chunks);
+            if (pct && p - 1 >= 0 && p - 1 < nj) seg(WT_ST_F2, p - 1, c.jobs[p - 1].f_chunks);
+            if (pct && p - 2 >= 0 && p - 2 < nj) seg(WT_ST_F3, p - 2, c.jobs[p - 2].f_chunks);
+            if (p - 3 >= 0 && p - 3 < nj) seg(WT_ST_A, p - 3, c.jobs[p - 3].chunks);
+        }
+        c.n_tickets = ticket;
+    }
+    return WT_OK;
+}
+
 // fills the host-side job tables from plan->layers and the current device pointers
 static int build_tables(WtPlan* P) {
     const int n = (int)P->layers.size();
@@ -251,10 +331,14 @@ static int build_tables(WtPlan* P) {
     P->level0_abs.clear();
     int sel_tiles = 0;
     bool any_apply = false;
+    {
+        int rc = build_fused_tables(P);
+        if (rc) return rc;
+    }
     for (int i = 0; i < n; ++i) {
         const WtLayerDesc& L = P->layers[i];
         const long long numel = layer_numel(L);
-        if (P->path[i] == PATH_EMPTY) continue;
+        if (P->path[i] == PATH_EMPTY || P->path[i] == PATH_FUSED) continue;
         const bool pct = (P->thr_kind == WT_THRESHOLD_PERCENTILE);
         if (P->path[i] == PATH_SMALL) {
             SmallClass* cls = nullptr;
@@ -343,6 +427,11 @@ static int upload_tables(WtPlan* P) {
     for (auto& c : P->small)
         if (!c.jobs.empty())
             WT_CUDA(cudaMemcpy(c.jobs_dev, c.jobs.data(), c.jobs.size() * sizeof(WtSmallJob), cudaMemcpyHostToDevice));
+    for (auto& c : P->fused) {
+        if (c.jobs.empty()) continue;
+        WT_CUDA(cudaMemcpy(c.jobs_dev, c.jobs.data(), c.jobs.size() * sizeof(WtFJob), cudaMemcpyHostToDevice));
+        WT_CUDA(cudaMemcpy(c.segs_dev, c.segs.data(), c.segs.size() * sizeof(WtFSeg), cudaMemcpyHostToDevice));
+    }
     return WT_OK;
 }
 
@@ -516,6 +605,7 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     P->ncoef.assign(n_layers, 0); P->zeros.assign(n_layers, 0);
     P->d_cand.assign(n_layers, nullptr); P->cand_cap.assign(n_layers, 0);
     const int F = P->bank.F;
+    const bool legacy = getenv("WT_LEGACY_PATH") != nullptr;  // A/B aid: the round-1 kernels (coefficients through HBM)
 
     // ---- classify + size ----
     size_t bytes = 0;
@@ -530,7 +620,14 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
         const long long numel = layer_numel(L);
         if (numel == 0) continue;
         if ((L.in == nullptr || L.out == nullptr)) { delete P; wt_set_error("layer %d: NULL tensor pointer", i); return WT_E_INVALID; }
-        if (L.level == 0) {
+        if (!legacy && wt_fused_supported(L.H, L.W, F, L.level, mode) && numel * 4 < (1LL << 31)) {
+            P->path[i] = PATH_FUSED;
+            const int ch = L.level == 0 ? 0 : L.H, cw = L.level == 0 ? 0 : L.W;
+            FusedClass* cls = nullptr;
+            for (auto& c : P->fused) if (c.H == ch && c.W == cw) cls = &c;
+            if (!cls) { FusedClass c; c.H = ch; c.W = cw; P->fused.push_back(c); cls = &P->fused.back(); }
+            cls->layers.push_back(i);
+        } else if (L.level == 0) {
             P->path[i] = PATH_LEVEL0;
         } else if (wt_small_supported(L.H, L.W, F, L.level, mode)) {
             P->path[i] = PATH_SMALL;
@@ -541,20 +638,40 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
             P->path[i] = PATH_GENERIC;
             tmp_elems = std::max(tmp_elems, L.batch * wt_generic_tmp_elems(L.H, L.W, F, mode, L.level));
         }
-        if (P->path[i] != PATH_LEVEL0) {
+        if (L.level != 0) {
             int sh, sw; int64_t nc;
             rc = wt_packed_shape(L.H, L.W, wavelet_id, L.level, mode, &sh, &sw, &nc);
             if (rc) { delete P; return rc; }
             P->ncoef[i] = L.batch * nc;
             P->zeros[i] = L.batch * ((long long)sh * sw - nc);
         }
-        if (threshold_kind == WT_THRESHOLD_PERCENTILE) ++n_sel;
+        if (threshold_kind == WT_THRESHOLD_PERCENTILE && P->path[i] != PATH_FUSED) ++n_sel;
+        if (P->path[i] != PATH_FUSED) P->legacy_zero = true;
+    }
+    // jobs of a fused class in ascending order of population (the ticket queue pipelines over them in this order)
+    for (auto& c : P->fused)
+        std::stable_sort(c.layers.begin(), c.layers.end(), [&](int a, int b) {
+            const long long na = P->layers[a].level == 0 ? layer_numel(P->layers[a]) : P->ncoef[a];
+            const long long nb = P->layers[b].level == 0 ? layer_numel(P->layers[b]) : P->ncoef[b];
+            return na < nb;
+        });
+    {   // smallest class first: launch order of wt_plan_run
+        auto work = [&](const FusedClass& c) { long long w = 0; for (int i : c.layers) w += layer_numel(P->layers[i]); return w; };
+        std::stable_sort(P->fused.begin(), P->fused.end(), [&](const FusedClass& a, const FusedClass& b) { return work(a) < work(b); });
     }
     // ---- layout of the single device block ----
     auto take = [&](size_t sz) { size_t o = bytes; bytes = align_up(bytes + sz); return o; };
     const size_t off_sel_jobs = take((size_t)std::max(n_sel, 1) * sizeof(WtSelJob));
     std::vector<size_t> off_small(P->small.size());
     for (size_t c = 0; c < P->small.size(); ++c) off_small[c] = take((size_t)n_layers * sizeof(WtSmallJob));
+    std::vector<size_t> off_fjobs(P->fused.size()), off_fsegs(P->fused.size()), off_fscr(P->fused.size());
+    for (size_t c = 0; c < P->fused.size(); ++c) {
+        const size_t nj = P->fused[c].layers.size();
+        off_fjobs[c] = take(nj * sizeof(WtFJob));
+        off_fsegs[c] = take((5 * nj + 8) * sizeof(WtFSeg));
+        P->fused[c].scratch_bytes = wt_fused_scratch_bytes((int)nj);
+        off_fscr[c] = take(2 * P->fused[c].scratch_bytes);
+    }
     const size_t off_thr = take((size_t)std::max(n_layers, 1) * sizeof(float));
     const size_t sel_scratch = wt_select_scratch_bytes(std::max(n_sel, 1));
     const size_t off_zero = take(sel_scratch + (size_t)std::max(n_layers, 1) * 4 * sizeof(long long));
@@ -564,7 +681,7 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     if (threshold_kind == WT_THRESHOLD_PERCENTILE)
         for (int i = 0; i < n_layers; ++i)
             if (P->path[i] != PATH_EMPTY) {
-                const long long pop = (P->path[i] == PATH_LEVEL0) ? layer_numel(P->layers[i]) : P->ncoef[i];
+                const long long pop = (P->layers[i].level == 0) ? layer_numel(P->layers[i]) : P->ncoef[i];
                 P->cand_cap[i] = wt_select_cand_cap(pop);
                 off_cand[i] = take((size_t)P->cand_cap[i] * sizeof(unsigned int));
             }
@@ -588,6 +705,15 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     }
     P->sel_jobs_dev = reinterpret_cast<WtSelJob*>(P->dev + off_sel_jobs);
     for (size_t c = 0; c < P->small.size(); ++c) P->small[c].jobs_dev = reinterpret_cast<WtSmallJob*>(P->dev + off_small[c]);
+    for (size_t c = 0; c < P->fused.size(); ++c) {
+        FusedClass& fc = P->fused[c];
+        fc.jobs_dev = reinterpret_cast<WtFJob*>(P->dev + off_fjobs[c]);
+        fc.segs_dev = reinterpret_cast<WtFSeg*>(P->dev + off_fsegs[c]);
+        fc.scratch[0] = P->dev + off_fscr[c];
+        fc.scratch[1] = fc.scratch[0] + fc.scratch_bytes;
+        e = cudaMemset(fc.scratch[0], 0, 2 * fc.scratch_bytes);
+        if (e != cudaSuccess) { wt_set_error("cudaMemset failed: %s", cudaGetErrorString(e)); wt_plan_destroy(P); return WT_E_CUDA; }
+    }
     P->thresholds_dev = reinterpret_cast<float*>(P->dev + off_thr);
     P->zero_block = P->dev + off_zero;
     P->zero_bytes = zero_bytes;
@@ -608,7 +734,7 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     }
     for (int i = 0; i < n_layers; ++i) {
         if (P->path[i] == PATH_EMPTY) continue;
-        if (P->path[i] != PATH_LEVEL0) P->d_coef[i] = reinterpret_cast<float*>(P->dev + off_coef[i]);
+        if (P->path[i] == PATH_SMALL || P->path[i] == PATH_GENERIC) P->d_coef[i] = reinterpret_cast<float*>(P->dev + off_coef[i]);
         if (P->cand_cap[i]) P->d_cand[i] = reinterpret_cast<unsigned int*>(P->dev + off_cand[i]);
         if (host_io) {
             P->d_in[i] = P->d_out[i] = reinterpret_cast<float*>(P->dev + off_io[i]);
@@ -617,7 +743,7 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
             P->d_out[i] = P->layers[i].out;
         }
     }
-    const size_t n_streams = std::max(P->small.size(), (size_t)P->gen_lanes);
+    const size_t n_streams = std::max(P->small.size() + P->fused.size(), (size_t)P->gen_lanes);
     if (n_streams > 1) {
         bool ok = cudaEventCreateWithFlags(&P->ev_fork, cudaEventDisableTiming) == cudaSuccess;
         for (size_t k = 1; ok && k < n_streams; ++k) {
@@ -680,10 +806,12 @@ extern "C" int wt_plan_set_peers(WtPlan* P, int n_peers, const int64_t* byte_del
     WT_CHECK(!P->host_io, WT_E_UNSUPPORTED, "wt_plan_set_peers: host-I/O plans have no device output buffer to mirror");
     if (n_peers > 0) {
         // the kernels that mirror their stores: small-plane synthesis and the select's level-0 apply
-        WT_CHECK(P->thr_kind == WT_THRESHOLD_PERCENTILE, WT_E_UNSUPPORTED, "wt_plan_set_peers: percentile plans only");
-        for (size_t i = 0; i < P->layers.size(); ++i)
+        for (size_t i = 0; i < P->layers.size(); ++i) {
             WT_CHECK(P->path[i] != PATH_GENERIC, WT_E_UNSUPPORTED,
                      "wt_plan_set_peers: layer %d runs on the generic tiled path, which does not mirror its stores", (int)i);
+            WT_CHECK(P->path[i] == PATH_FUSED || P->path[i] == PATH_EMPTY || P->thr_kind == WT_THRESHOLD_PERCENTILE, WT_E_UNSUPPORTED,
+                     "wt_plan_set_peers: absolute-threshold plans mirror their stores on the fused path only");
+        }
         for (int q = 0; q < n_peers; ++q)
             WT_CHECK((byte_deltas[q] & 15) == 0, WT_E_INVALID, "wt_plan_set_peers: peer mappings must keep 16-byte alignment");
     }
@@ -719,20 +847,15 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         if (name) { P->phase_names[slot] = name; ++P->n_phases; }
     };
     char label[64];
-    mark("memset");
-    // counts are accumulated by the very first kernels; the select scratch (histograms + state, ~100 KB per job) is not
-    // touched before the select, so when the size classes fork its memset rides on the last auxiliary stream next to
-    // the analysis launches instead of in front of them
+    // counts / select scratch of the launches that accumulate with atomics (generic path, legacy kernels); the fused
+    // classes zero their own scratch for the next run and store their counts, so a fused-only plan enqueues no memset
     const size_t counts_off = (size_t)(reinterpret_cast<char*>(P->counts_dev) - P->zero_block);
-    const bool split_zero = !P->timing && !P->aux.empty() && counts_off > 0 && counts_off < P->zero_bytes;
-    if (split_zero) WT_CUDA(cudaMemsetAsync(P->zero_block + counts_off, 0, P->zero_bytes - counts_off, stream));
-    else WT_CUDA(cudaMemsetAsync(P->zero_block, 0, P->zero_bytes, stream));
-    if (P->host_io) mark("h2d");
-    if (P->host_io)
-        for (int i = 0; i < n; ++i)
-            if (P->path[i] != PATH_EMPTY)
-                WT_CUDA(cudaMemcpyAsync(P->d_in[i], P->layers[i].in, (size_t)layer_numel(P->layers[i]) * sizeof(float),
-                                        cudaMemcpyHostToDevice, stream));
+    const bool split_zero = P->legacy_zero && !P->timing && !P->aux.empty() && counts_off > 0 && counts_off < P->zero_bytes;
+    if (P->legacy_zero) {
+        mark("memset");
+        if (split_zero) WT_CUDA(cudaMemsetAsync(P->zero_block + counts_off, 0, P->zero_bytes - counts_off, stream));
+        else WT_CUDA(cudaMemsetAsync(P->zero_block, 0, P->zero_bytes, stream));
+    }
     int rc;
     // 1. analysis
     // size classes fork onto the auxiliary streams (kept serial on the caller's stream while phases are timed)
@@ -754,6 +877,24 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     auto class_stream = [&](size_t k) { return (forked && k > 0) ? P->aux[k - 1] : stream; };
     if ((rc = fork())) return rc;
     if (split_zero) WT_CUDA(cudaMemsetAsync(P->zero_block, 0, counts_off, P->aux.back()));
+    // 0. the fused classes: one persistent launch each, independent of everything below (smallest class first, so the
+    // short kernels hold their SM slots before the long one fills the rest)
+    for (size_t k = 0; k < P->fused.size(); ++k) {
+        FusedClass& c = P->fused[k];
+        if (c.n_tickets <= 0) continue;
+        if (c.H) snprintf(label, sizeof(label), "fused_%dx%d", c.H, c.W); else snprintf(label, sizeof(label), "fused_flat");
+        mark(label);
+        WtFArgs fa;
+        memset(&fa, 0, sizeof(fa));
+        fa.jobs = c.jobs_dev; fa.segs = c.segs_dev;
+        fa.n_jobs = (int)c.jobs.size(); fa.n_segs = (int)c.segs.size(); fa.n_tickets = c.n_tickets; fa.n_select = c.n_select;
+        fa.scratch = c.scratch[c.parity]; fa.scratch_next = c.scratch[c.parity ^ 1]; fa.scratch_bytes = c.scratch_bytes;
+        fa.thresholds = P->thresholds_dev; fa.counts = P->counts_dev;
+        rc = wt_fused_launch(c.H, c.W, P->bank, P->arithmetic, fa, class_stream(P->small.size() + k));
+        if (rc) return rc;
+        c.parity ^= 1;
+        ++launches;
+    }
     for (size_t k = 0; k < P->small.size(); ++k) {
         auto& c = P->small[k];
         snprintf(label, sizeof(label), "small_analysis_%dx%d", c.H, c.W);
