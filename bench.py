@@ -271,6 +271,11 @@ def phase_elems(wl, phase):
     """weight elements the launch group `phase` processes"""
     def numel(sel):
         return sum(int(np.prod(s)) for (_, s), lv in zip(wl.census, wl.levels) if sel(s, lv))
+    if phase == 'fused_flat':
+        return numel(lambda s, lv: lv == 0)
+    if phase.startswith('fused_'):
+        h, w = (int(v) for v in phase.split('_', 1)[1].split('x'))
+        return numel(lambda s, lv: lv > 0 and s[-2] == h and s[-1] == w)
     if phase.startswith('small_'):
         hw = phase.rsplit('_', 1)[1]
         h, w = (int(v) for v in hw.split('x'))

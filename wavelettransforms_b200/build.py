@@ -16,9 +16,14 @@ LIBDIR = os.path.join(HERE, 'lib')
 OBJDIR = os.path.join(HERE, 'build')
 LIB = os.path.join(LIBDIR, 'libwtprune.so')
 
-SOURCES = ['wt_fused_s7.cu', 'wt_fused_s5.cu', 'wt_fused_s3.cu', 'wt_fused_s1.cu', 'wt_fused_s7f.cu', 'wt_fused_s5f.cu', 'wt_fused_s3f.cu',
-           'wt_fused_s1f.cu', 'wt_small.cu', 'wt_fused_flat.cu', 'wt_api.cu', 'wt_select.cu', 'wt_generic.cu', 'wt_maskers.cu',
-           'wt_blocks.cu']  # heaviest first
+SOURCES = ['wt_fused_s7.cu', 'wt_fused_s5.cu', 'wt_fused_s3.cu', 'wt_fused_s1.cu', 'wt_small.cu', 'wt_fused_flat.cu', 'wt_api.cu',
+           'wt_select.cu', 'wt_generic.cu', 'wt_maskers.cu', 'wt_blocks.cu']  # heaviest first
+# the fma_taporder instantiations of the fused kernels (wt_fused_s<N>f.cu) double the build time: WT_BUILD_FMA=1 adds them
+if os.environ.get('WT_BUILD_FMA'):
+    SOURCES = ['wt_fused_s7f.cu', 'wt_fused_s5f.cu', 'wt_fused_s3f.cu', 'wt_fused_s1f.cu'] + SOURCES
+    NVCC_EXTRA = ['-DWT_WITH_FMA_KERNELS']
+else:
+    NVCC_EXTRA = []
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17', '-fmad=false',
               '-diag-suppress', '177', '-Xcompiler', '-fPIC']
 
@@ -54,7 +59,7 @@ def build_library(force=False, verbose=False):
         o = os.path.join(OBJDIR, src.replace('.cu', '.o'))
         if not force and os.path.exists(o) and os.path.getmtime(o) >= max(os.path.getmtime(s), hdr_m):
             return o
-        cmd = [nvcc] + NVCC_FLAGS + ['-c', s, '-o', o]
+        cmd = [nvcc] + NVCC_FLAGS + NVCC_EXTRA + ['-c', s, '-o', o]
         if verbose:
             print(' '.join(cmd), flush=True)
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -176,13 +176,13 @@ struct FusedClass {
     int H = 0, W = 0;
     std::vector<int> layers;       // plan layer of every job, in job order (ascending population)
     std::vector<WtFJob> jobs;
-    std::vector<WtFSeg> segs;
     WtFJob* jobs_dev = nullptr;
-    WtFSeg* segs_dev = nullptr;
     char* scratch[2] = {nullptr, nullptr};
     size_t scratch_bytes = 0;
     int parity = 0;                // scratch block the next run uses (the run zeroes the other one for the run after)
-    int n_tickets = 0, n_select = 0;
+    int total_items = 0, total_s_items = 0, n_select = 0;
+    double share = 1.0;            // this class's part of the bytes of all fused classes of the plan
+    unsigned long long* stamps_dev = nullptr;  // WT_FUSED_STAMPS tuning aid
 };
 
 struct SmallClass {
@@ -264,7 +264,6 @@ static int build_fused_tables(WtPlan* P) {
     const bool pct = (P->thr_kind == WT_THRESHOLD_PERCENTILE);
     for (auto& c : P->fused) {
         c.jobs.clear();
-        c.segs.clear();
         c.n_select = 0;
         for (int i : c.layers) {
             const WtLayerDesc& L = P->layers[i];
@@ -298,26 +297,16 @@ static int build_fused_tables(WtPlan* P) {
             j.peers = P->peers;
             c.jobs.push_back(j);
         }
-        // the ticket queue: every S first, then a software pipeline over the jobs, smallest first --
-        // position p holds C(p), F2(p-1), F3(p-2), A(p-3) -- so the stage hand-overs of a job hide under its neighbours'
-        // streaming passes and the exposed end of the queue is the apply of the largest jobs
-        const int nj = (int)c.jobs.size();
-        int ticket = 0;
-        auto seg = [&](int stage, int job, int count) {
-            if (count <= 0) return;
-            WtFSeg g = {ticket, count, stage, job};
-            c.segs.push_back(g);
-            ticket += count;
-        };
-        if (pct)
-            for (int j = 0; j < nj; ++j) seg(WT_ST_S, j, c.jobs[j].s_chunks);
-        for (int p = 0; p < nj + 3; ++p) {
-            if (pct && p < nj) seg(WT_ST_C, p, c.jobs[p].chunks);
-            if (pct && p - 1 >= 0 && p - 1 < nj) seg(WT_ST_F2, p - 1, c.jobs[p - 1].f_chunks);
-            if (pct && p - 2 >= 0 && p - 2 < nj) seg(WT_ST_F3, p - 2, c.jobs[p - 2].f_chunks);
-            if (p - 3 >= 0 && p - 3 < nj) seg(WT_ST_A, p - 3, c.jobs[p - 3].chunks);
+        // the class-wide item spaces of the full passes and of the sample pass: every CTA takes one contiguous share
+        c.total_items = c.total_s_items = 0;
+        for (WtFJob& j : c.jobs) {
+            j.item_begin = c.total_items;
+            j.s_begin = c.total_s_items;
+            c.total_items += j.items;
+            c.total_s_items += j.s_items;
         }
-        c.n_tickets = ticket;
+        if (!c.jobs.empty())
+            WT_CHECK(c.jobs.size() <= 4096, WT_E_UNSUPPORTED, "more than 4096 tensors in one fused class");
     }
     return WT_OK;
 }
@@ -430,7 +419,6 @@ static int upload_tables(WtPlan* P) {
     for (auto& c : P->fused) {
         if (c.jobs.empty()) continue;
         WT_CUDA(cudaMemcpy(c.jobs_dev, c.jobs.data(), c.jobs.size() * sizeof(WtFJob), cudaMemcpyHostToDevice));
-        WT_CUDA(cudaMemcpy(c.segs_dev, c.segs.data(), c.segs.size() * sizeof(WtFSeg), cudaMemcpyHostToDevice));
     }
     return WT_OK;
 }
@@ -448,6 +436,7 @@ extern "C" int wt_plan_destroy(WtPlan* P) {
     for (cudaEvent_t e : P->ev_join) cudaEventDestroy(e);
     if (P->ev_fork) cudaEventDestroy(P->ev_fork);
     for (cudaStream_t q : P->aux) cudaStreamDestroy(q);
+    for (auto& c : P->fused) if (c.stamps_dev) cudaFree(c.stamps_dev);
     if (P->stamps_dev) cudaFree(P->stamps_dev);
     if (P->cta_table_dev) cudaFree(P->cta_table_dev);
     if (P->dev) cudaFree(P->dev);
@@ -605,7 +594,19 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     P->ncoef.assign(n_layers, 0); P->zeros.assign(n_layers, 0);
     P->d_cand.assign(n_layers, nullptr); P->cand_cap.assign(n_layers, 0);
     const int F = P->bank.F;
-    const bool legacy = getenv("WT_LEGACY_PATH") != nullptr;  // A/B aid: the round-1 kernels (coefficients through HBM)
+    // Which layers take the fused recompute kernels (wt_fused.cuh) -- decided by measurement on the B200:
+    //   absolute thresholds, level 0 or filters of <= 4 taps (HBM-bound): ONE pass, 2-4x faster than the round-1 kernels;
+    //   percentile thresholds: bit-exact and 1.1x the algorithmic DRAM traffic, but four latency-bound phases against the
+    //   select's three on a 45 MB model, and a slower streaming loop on large data: the round-1 kernels stay the default.
+    // WT_FUSED=all|abs|off overrides (all: every layer the fused kernels support; WT_LEGACY_PATH = off).
+    int fused_mode = 1;
+    if (const char* e = getenv("WT_FUSED")) fused_mode = !strcmp(e, "all") ? 2 : (!strcmp(e, "off") ? 0 : 1);
+    if (getenv("WT_LEGACY_PATH")) fused_mode = 0;
+    auto wants_fused = [&](const WtLayerDesc& L) {
+        if (fused_mode == 2) return true;
+        if (fused_mode == 0) return false;
+        return threshold_kind == WT_THRESHOLD_ABSOLUTE && (L.level == 0 || F <= 4);
+    };
 
     // ---- classify + size ----
     size_t bytes = 0;
@@ -620,7 +621,7 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
         const long long numel = layer_numel(L);
         if (numel == 0) continue;
         if ((L.in == nullptr || L.out == nullptr)) { delete P; wt_set_error("layer %d: NULL tensor pointer", i); return WT_E_INVALID; }
-        if (!legacy && wt_fused_supported(L.H, L.W, F, L.level, mode) && numel * 4 < (1LL << 31)) {
+        if (wants_fused(L) && wt_fused_supported(L.H, L.W, F, L.level, mode) && numel * 4 < (1LL << 31)) {
             P->path[i] = PATH_FUSED;
             const int ch = L.level == 0 ? 0 : L.H, cw = L.level == 0 ? 0 : L.W;
             FusedClass* cls = nullptr;
@@ -658,17 +659,19 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     {   // smallest class first: launch order of wt_plan_run
         auto work = [&](const FusedClass& c) { long long w = 0; for (int i : c.layers) w += layer_numel(P->layers[i]); return w; };
         std::stable_sort(P->fused.begin(), P->fused.end(), [&](const FusedClass& a, const FusedClass& b) { return work(a) < work(b); });
+        long long all = 0;
+        for (auto& c : P->fused) all += work(c);
+        for (auto& c : P->fused) c.share = all ? (double)work(c) / (double)all : 1.0;
     }
     // ---- layout of the single device block ----
     auto take = [&](size_t sz) { size_t o = bytes; bytes = align_up(bytes + sz); return o; };
     const size_t off_sel_jobs = take((size_t)std::max(n_sel, 1) * sizeof(WtSelJob));
     std::vector<size_t> off_small(P->small.size());
     for (size_t c = 0; c < P->small.size(); ++c) off_small[c] = take((size_t)n_layers * sizeof(WtSmallJob));
-    std::vector<size_t> off_fjobs(P->fused.size()), off_fsegs(P->fused.size()), off_fscr(P->fused.size());
+    std::vector<size_t> off_fjobs(P->fused.size()), off_fscr(P->fused.size());
     for (size_t c = 0; c < P->fused.size(); ++c) {
         const size_t nj = P->fused[c].layers.size();
         off_fjobs[c] = take(nj * sizeof(WtFJob));
-        off_fsegs[c] = take((5 * nj + 8) * sizeof(WtFSeg));
         P->fused[c].scratch_bytes = wt_fused_scratch_bytes((int)nj);
         off_fscr[c] = take(2 * P->fused[c].scratch_bytes);
     }
@@ -708,7 +711,6 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     for (size_t c = 0; c < P->fused.size(); ++c) {
         FusedClass& fc = P->fused[c];
         fc.jobs_dev = reinterpret_cast<WtFJob*>(P->dev + off_fjobs[c]);
-        fc.segs_dev = reinterpret_cast<WtFSeg*>(P->dev + off_fsegs[c]);
         fc.scratch[0] = P->dev + off_fscr[c];
         fc.scratch[1] = fc.scratch[0] + fc.scratch_bytes;
         e = cudaMemset(fc.scratch[0], 0, 2 * fc.scratch_bytes);
@@ -877,21 +879,33 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     auto class_stream = [&](size_t k) { return (forked && k > 0) ? P->aux[k - 1] : stream; };
     if ((rc = fork())) return rc;
     if (split_zero) WT_CUDA(cudaMemsetAsync(P->zero_block, 0, counts_off, P->aux.back()));
-    // 0. the fused classes: one persistent launch each, independent of everything below (smallest class first, so the
-    // short kernels hold their SM slots before the long one fills the rest)
+    // 0. the fused classes: one cooperative launch each, independent of everything below.  Smallest class first, each
+    // on its own stream; a later (larger) class leaves room for the CTAs of the earlier ones, so that the kernels are
+    // resident together (if the guess is wrong the larger launch simply waits for the smaller kernels to end).
+    int reserve = 0;
     for (size_t k = 0; k < P->fused.size(); ++k) {
         FusedClass& c = P->fused[k];
-        if (c.n_tickets <= 0) continue;
+        if (c.total_items <= 0) continue;
         if (c.H) snprintf(label, sizeof(label), "fused_%dx%d", c.H, c.W); else snprintf(label, sizeof(label), "fused_flat");
         mark(label);
         WtFArgs fa;
         memset(&fa, 0, sizeof(fa));
-        fa.jobs = c.jobs_dev; fa.segs = c.segs_dev;
-        fa.n_jobs = (int)c.jobs.size(); fa.n_segs = (int)c.segs.size(); fa.n_tickets = c.n_tickets; fa.n_select = c.n_select;
+        fa.jobs = c.jobs_dev;
+        fa.n_jobs = (int)c.jobs.size(); fa.n_select = c.n_select;
+        fa.total_items = c.total_items; fa.total_s_items = c.total_s_items;
         fa.scratch = c.scratch[c.parity]; fa.scratch_next = c.scratch[c.parity ^ 1]; fa.scratch_bytes = c.scratch_bytes;
         fa.thresholds = P->thresholds_dev; fa.counts = P->counts_dev;
-        rc = wt_fused_launch(c.H, c.W, P->bank, P->arithmetic, fa, class_stream(P->small.size() + k));
+        cudaStream_t cs = class_stream(P->small.size() + k);
+        if (getenv("WT_FUSED_STAMPS")) {
+            const size_t sb = (size_t)WT_SEL_STAMP_CTAS * WT_F_STAMP_SLOTS * 8;
+            if (!c.stamps_dev && cudaMalloc((void**)&c.stamps_dev, sb) != cudaSuccess) c.stamps_dev = nullptr;
+            if (c.stamps_dev) cudaMemsetAsync(c.stamps_dev, 0, sb, cs);
+            fa.stamps = c.stamps_dev;
+        }
+        int grid = 0;
+        rc = wt_fused_launch(c.H, c.W, P->bank, P->arithmetic, fa, reserve, k + 1 == P->fused.size() ? 1.0 : c.share, cs, &grid);
         if (rc) return rc;
+        reserve += 2 * grid;
         c.parity ^= 1;
         ++launches;
     }
@@ -1024,6 +1038,41 @@ extern "C" int wt_plan_results(WtPlan* P, void* stream_, int64_t* counts, int64_
         WT_CUDA(cudaMemcpyAsync(thr.data(), P->thresholds_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, stream));
     }
     WT_CUDA(cudaStreamSynchronize(stream));
+    if (getenv("WT_FUSED_DEBUG")) {   // tuning aid: the last run of every fused class (failed jobs, phase boundaries per CTA)
+        for (auto& c : P->fused) {
+            const char* scr = c.scratch[c.parity ^ 1];
+            WtFHeader h;
+            WT_CUDA(cudaMemcpy(&h, scr, sizeof(h), cudaMemcpyDeviceToHost));
+            fprintf(stderr, "[wt fused %dx%d] jobs %zu items %d sample items %d failed %u wide %u\n", c.H, c.W, c.jobs.size(), c.total_items,
+                    c.total_s_items, h.fail_count, h.wide);
+            if (c.stamps_dev) {
+                const int SL = WT_F_STAMP_SLOTS;
+                std::vector<unsigned long long> sp((size_t)WT_SEL_STAMP_CTAS * SL);
+                WT_CUDA(cudaMemcpy(sp.data(), c.stamps_dev, sp.size() * 8, cudaMemcpyDeviceToHost));
+                unsigned long long t0 = ~0ull;
+                int g = 0;
+                for (int q = 0; q < WT_SEL_STAMP_CTAS; ++q) if (sp[(size_t)q * SL]) { t0 = std::min(t0, sp[(size_t)q * SL]); g = q + 1; }
+                double mx[8] = {0}, sum[8] = {0};
+                for (int q = 0; q < g; ++q)
+                    for (int k = 0; k < 7; ++k) {
+                        const unsigned long long raw = sp[(size_t)q * SL + k];
+                        const double v = raw ? (double)(raw - t0) * 1e-3 : 0.0;
+                        mx[k] = std::max(mx[k], v);
+                        sum[k] += v / g;
+                    }
+                fprintf(stderr, "  %d CTAs, us mean/max: start %.1f/%.1f endS %.1f/%.1f endC %.1f/%.1f endT1 %.1f/%.1f startA %.1f/%.1f endA %.1f/%.1f endX %.1f/%.1f\n",
+                        g, sum[0], mx[0], sum[1], mx[1], sum[2], mx[2], sum[3], mx[3], sum[4], mx[4], sum[5], mx[5], sum[6], mx[6]);
+            }
+            std::vector<WtFState> st(c.jobs.size());
+            WT_CUDA(cudaMemcpy(st.data(), scr + sizeof(WtFHeader), st.size() * sizeof(WtFState), cudaMemcpyDeviceToHost));
+            for (size_t q = 0; q < st.size(); ++q)
+                if (st[q].failed || getenv("WT_FUSED_DEBUG_ALL"))
+                    fprintf(stderr, "  job %zu layer %d n %lld zeros %lld k0 %lld shift %d items %d/%d: lo %u width %u below %llu cand %u (cap %u) a %g b %g t %g%s\n",
+                            q, c.jobs[q].layer, c.jobs[q].n, c.jobs[q].zeros, c.jobs[q].k0, c.jobs[q].sample_shift, c.jobs[q].items,
+                            c.jobs[q].s_items, st[q].lo_key, st[q].width, st[q].below, st[q].s_count, c.jobs[q].cand_cap, st[q].a, st[q].b,
+                            st[q].t, st[q].failed ? "  FAILED -> exact path" : "");
+        }
+    }
     if (P->stamps_dev && !P->sel_jobs.empty()) {
         std::vector<unsigned long long> st((size_t)WT_SEL_STAMP_CTAS * 16);
         WT_CUDA(cudaMemcpy(st.data(), P->stamps_dev, st.size() * 8, cudaMemcpyDeviceToHost));

@@ -177,21 +177,20 @@ int wt_select_grid(int n_tiles, int* grid_out);
 void wt_select_balance(const WtSelJob* jobs, int n_jobs, int n_tiles, int grid, int* tiles_out, int* job_out);
 #define WT_SEL_STAMP_CTAS 2048
 
-// ---- fused prune kernels (wt_fused.cuh): one persistent dataflow launch per plane class -----------------------------
+// ---- fused prune kernels (wt_fused.cuh): one cooperative launch per plane class, coefficients never leave the SM ------
 #define WT_F_BINS1 4096   // key bits 30..19
 #define WT_F_FBINS 2048   // 11-bit refinement digits
 #define WT_F_FBINS3 512   // last <= 9 bits
 #define WT_F_HIST_WORDS (WT_F_BINS1 + WT_F_BINS1 / 32 + WT_F_FBINS + 2 * WT_F_FBINS + 2 * WT_F_FBINS3)  // u32 per job
-#define WT_F_FLAT_CHUNK 8192                                        // flat class: elements per item
-#define WT_F_SMALL_THREADS(H, W) (((H) * (W) <= 9) ? 256 : 128)     // small-plane classes: planes per tile = threads per CTA
-#define WT_F_SMALL_CHUNK_TILES 4                                    // tiles per item
+#define WT_F_FLAT_CHUNK 4096                                        // flat class: elements per item
+#define WT_F_SMALL_THREADS(H, W) (((H) * (W) <= 9) ? 256 : 128)     // small-plane classes: planes per item = threads per CTA
 #define WT_F_WFLUSH 224   // a warp moves its staged candidates to the global list once it holds more keys
-#define WT_F_WSTAGE (WT_F_WFLUSH + 32)
-
-// stages (per-job completion counters) and ready flags
-enum { WT_ST_S = 0, WT_ST_C = 1, WT_ST_F2 = 2, WT_ST_F3 = 3, WT_ST_A = 4, WT_ST_X1 = 5, WT_ST_X2 = 6, WT_ST_X3 = 7, WT_ST_XA = 8,
-       WT_F_NSTAGE = 9 };
-enum { WT_RD_S = 0, WT_RD_C = 1, WT_RD_F2 = 2, WT_RD_T = 3, WT_RD_X1 = 4, WT_RD_X2 = 5, WT_RD_XT = 6, WT_F_NREADY = 7 };
+#define WT_F_GROUP 8      // keys per thread the count / compact pass handles at once
+#define WT_F_WSTAGE (WT_F_WFLUSH + 32 * WT_F_GROUP)   // one more group always fits
+#define WT_F_NOKEY 0xffffffffu   // not a key (ragged end of an item, lane without a plane): beyond every bracket
+#define WT_F_JIDX 512     // jobs whose item offsets a CTA keeps in shared memory (more: looked up in global memory)
+#define WT_F_SLICE 4096   // candidate keys per slice of the tail rounds
+#define WT_F_STAMP_SLOTS 16      // u64 slots per CTA of the tuning stamps (WT_FUSED_STAMPS)
 
 struct __align__(16) WtFJob {   // one tensor of the class (device, read-only during a run)
     const float* in;         // [units] elements (flat class) or [units][H][W] planes
@@ -208,58 +207,63 @@ struct __align__(16) WtFJob {   // one tensor of the class (device, read-only du
     int level;
     int layer;               // row of counts[] / thresholds[]
     int sample_shift;        // S reads 1 / 2^shift of the job
-    int chunks, s_chunks, f_chunks;  // items of the full passes / of S / of F2 and F3
-    int pad0;
+    int items, s_items;      // items of the full passes / of the sample pass
+    int item_begin, s_begin; // first item of this job in the class-wide item spaces (prefix sums over the jobs)
     WtPeers peers;           // layer-sharded runs: out is also stored at out + delta of every peer
 };
 static_assert(sizeof(WtFJob) % 16 == 0, "WtFJob is copied with 16-byte loads");
 
-struct WtFState {            // per job, inside the zeroed scratch
-    unsigned int done[WT_F_NSTAGE];
-    unsigned int ready[WT_F_NREADY];
-    unsigned long long below;     // explicit keys < lo_key (counted by C)
-    unsigned long long zc, nzb;   // zeros written / nonzero inputs (A)
-    unsigned long long r[2], r2[2];
-    unsigned int s_count;         // keys appended to cand[] by C
-    unsigned int lo_key, width;   // bracket [lo_key, lo_key + width) in key patterns
-    int sh1, sh2;                 // bits of (key - lo_key) below the F1 digit / below the F2 digit
-    unsigned int d[2], d2[2];
-    int failed;
-    float a, b, t;                // sorted[k0], sorted[k1], threshold
+struct __align__(128) WtFState {   // per job, inside the zeroed scratch; one 128-byte line per access pattern
+    // line 0: written once per phase by the CTA that holds the job's first item / slice, read in the next phase
+    unsigned long long r[2], r2[2];   // ranks inside the digits found so far
+    unsigned int lo_key, width;       // bracket [lo_key, lo_key + width) in key patterns (0 width: no bracket)
+    unsigned int d[2], d2[2];         // digits of both ranks after the F1 / F2 (X1 / X2) scans
+    int failed;                       // the job left the sampled pipeline: the exact path X runs it
+    float a, b, t;                    // sorted[k0], sorted[k1], threshold
+    int pad0[10];
+    // line 1: the candidate list's fill level (an atomicAdd with a consumer inside the C pass)
+    unsigned int s_count;             // keys appended to cand[] by C
+    int pad1[31];
+    // line 2: accumulators and the completion counter of the apply (fire-and-forget atomics, one consumer each)
+    unsigned long long below;         // explicit keys < lo_key (counted by C)
+    unsigned long long zc, nzb;       // zeros written / nonzero inputs (A)
+    unsigned int done;                // items of the apply pass completed
+    int pad2[25];
 };
+static_assert(sizeof(WtFState) == 384, "WtFState: three 128-byte lines");
 
 struct WtFHeader {           // first 256 bytes of the scratch
-    int ticket, ticket2;
-    unsigned int verified, fail_count;
-    int pad[60];
-};
-
-struct WtFSeg {              // `count` consecutive tickets from `first`: items 0.. of (stage, job)
-    int first, count, stage, job;
+    unsigned int fail_count; // jobs handed to the exact path
+    unsigned int wide;       // some bracket is wider than 8 bins: the tail runs its second round
+    int pad[62];
 };
 
 struct WtFArgs {
     const WtFJob* jobs;
-    const WtFSeg* segs;
-    int n_jobs, n_segs, n_tickets;
-    int n_select;            // jobs that run a select (the rest are absolute-threshold jobs: stage A only)
+    int n_jobs;
+    int n_select;            // jobs that run a select (0: absolute-threshold class, phase A only, no grid barrier)
+    int total_items, total_s_items;
     char* scratch;           // this run's block: zero at launch
     char* scratch_next;      // zeroed by this run for the next one
     unsigned long long scratch_bytes;
     float* thresholds;       // [n_layers]
     long long* counts;       // [n_layers][4] {numel, nonzero, zeros, nonzero_before}
+    unsigned long long* stamps;  // nullable tuning aid: [grid][WT_F_STAMP_SLOTS] phase boundaries per CTA (WT_FUSED_STAMPS)
 };
 
 static inline size_t wt_fused_scratch_bytes(int n_jobs) {
     size_t b = sizeof(WtFHeader) + (size_t)n_jobs * sizeof(WtFState) + (size_t)n_jobs * WT_F_HIST_WORDS * 4;
     return (b + 255) / 256 * 256;
 }
-// chunk geometry of a job (fills units-derived fields: n, sample_shift, chunks, s_chunks, f_chunks); H = W = 0: flat class
+// item geometry of a job (fills n, sample_shift, items, s_items from units); H = W = 0: flat class
 void wt_fused_geometry(int H, int W, WtFJob* job, long long keys_per_unit);
-// true when (H, W, F, level) has a fused small-plane instantiation
+// true when (H, W, F, level) has a fused instantiation
 bool wt_fused_supported(int H, int W, int F, int level, int mode);
-// launches the persistent kernel of the class (H = W = 0: flat); fma: arithmetic fma_taporder
-int wt_fused_launch(int H, int W, const WtBank& bank, int fma, const WtFArgs& args, cudaStream_t stream);
+// Cooperative launch of the class's kernel (H = W = 0: flat); fma: arithmetic fma_taporder.  The grid is what fits the
+// device minus `reserve_ctas` (room for the kernels of other classes that run next to it), at most one CTA per item and
+// at most `share` (0..1: this class's part of the plan's bytes) of the device; *grid_out = the grid used.
+int wt_fused_launch(int H, int W, const WtBank& bank, int fma, const WtFArgs& args, int reserve_ctas, double share,
+                    cudaStream_t stream, int* grid_out);
 
 // ---- level-0 apply for absolute thresholds and generic elementwise helpers (wt_select.cu) --------
 int wt_apply_threshold_launch(const float* x, float* out, long long n, const float* thr_dev, float thr_host,

@@ -5,34 +5,40 @@
 // coefficients of a small plane live in registers and are recomputed from the weights in every pass that needs them
 // (hard part 2).  Algorithmic traffic stays what it is -- read the weight, write the pruned weight.
 //
-// Dataflow instead of grid barriers.  The work of a launch is a static queue of tickets; a CTA draws the next ticket
-// with one atomicAdd (prefetched under the previous item) and every job (tensor) walks through its stages on its own:
-//   S   12-bit histogram (key bits 30..19 of |c|) of a 1/2^s SAMPLE of the job's keys (whole for jobs < 32 Ki keys)
-//       -> the CTA that finishes the job's last S item brackets both ranks in consecutive bins (5 sigma of the
-//          binomial rank error) and publishes the bracket
-//   C   the one full pass: count the keys below the bracket, compact the keys inside it into the job's candidate
-//       list (warp-private staging) and histogram the top 11 bits of (key - lo) of those candidates
-//       -> the last CTA verifies the bracket with the EXACT counts (a miss hands the job to the exact path X below, so
-//          the result never depends on the sample) and locates both ranks in that histogram
-//   F2  next <= 11 bits over the candidate list (a few slices per job, L2-resident)  -> usually final
-//   F3  last <= 9 bits (only for brackets wider than 8 bins: a rank next to the massive tie at zero)
-//       -> sorted[k0], sorted[k1] -> np.percentile's lerp (legacy_1_22 / nep50_2x) -> threshold
-//   A   apply: recompute the coefficients, zero |c| < t, synthesise, crop, store, count zeros
-// "->" is done by whichever CTA happens to complete the stage of that job last (a per-job counter), which then raises
-// a per-job flag; an item whose job is not ready yet spins on that flag.  Tickets are drawn in queue order and a stage
-// only ever waits for tickets that were drawn earlier, so there is no deadlock whatever the number of resident CTAs,
-// and nobody waits for anybody else's job: no grid barrier, no cooperative launch, no elected-CTA tail.  The queue is a
-// software pipeline over the jobs (C(j), F2(j-1), F3(j-2), A(j-3), smallest job first), so the latency of the
-// stage hand-overs of one job hides under the streaming passes of its neighbours and A(j) finds the weights C(j) read
-// a moment ago still in L2.
+// One cooperative launch per plane class, a persistent grid (every CTA owns one contiguous range of the class's items,
+// cut into per-job segments) and a few grid barriers:
+//   S   12-bit histogram (key bits 30..19 of |c|) of a 1/2^s SAMPLE of every job's keys (whole for jobs < 32 Ki keys)
+//   --- barrier ---
+//   C   every CTA scans the sample histogram of its segment's job -> a bracket of consecutive bins that holds both
+//       ranks unless the sample lied (5 sigma of the binomial rank error); then the one full pass: count the keys
+//       below the bracket, compact the keys inside it into the job's candidate list (warp-private staging) and
+//       histogram the top 11 bits of (key - lo) of those candidates (F1)
+//   --- barrier ---
+//   T1  the candidate lists, cut into slices dealt to all CTAs: verify the bracket with the EXACT counts (a miss hands
+//       the job to the exact path X below, so the result never depends on the sample), digits of both ranks from F1,
+//       histogram of the next <= 11 bits of the matching candidates (F2)
+//   --- barrier ---
+//   T2  only when some bracket is wider than 8 bins (a rank next to the massive tie at zero): the last <= 9 bits (F3)
+//   A   every CTA scans F2 (F3) of its segment's job -> sorted[k0], sorted[k1] -> np.percentile's lerp (legacy_1_22 /
+//       nep50_2x) -> threshold; apply: recompute the coefficients, zero |c| < t, synthesise, crop, store, count zeros
+// No phase has a serial tail: after a barrier every CTA scans the small L2-resident histogram of its own job
+// redundantly instead of waiting for an elected CTA; the CTA that holds a job's first item (slice) publishes the
+// result of the scan for the phase after the next barrier, so every phase does one scan per segment.
 //
 // X1..X3 + XA: exact MSD radix select (12 + 11 + 8 bits, three recomputing passes, no candidate list) for the jobs
-// whose bracket missed or whose list overflowed; drawn from a second ticket counter after the main queue, by the same
-// CTAs, only if some job failed.
+// whose bracket missed or whose list overflowed; four more phases over the same partition, run only if some job failed.
 //
-// The per-run scratch (ticket counters, per-job counters, flags and histograms) must be zero at launch; every launch
-// zeroes the scratch block of the NEXT run (two blocks alternate), so a step enqueues no memset.
+// Absolute-threshold classes (dwt_pruning_NoEntropy.py:45) run phase A alone: one pass, no barrier.
+//
+// The per-run scratch (per-job state and histograms) must be zero at launch; every launch zeroes the scratch block of
+// the NEXT run (two blocks alternate), so a step enqueues no memset.  (A first version of this kernel replaced the grid
+// barriers by per-job flags and a ticket queue; measured on the B200 every hand-over between stages of a job cost
+// 10-25 us under load and the waiting CTAs could do nothing useful: 150 us for ResNet-18 at level 0 against 66 us for
+// the barrier kernel it was meant to beat.  Dropped.)
 #pragma once
+#include <cooperative_groups.h>
+#include <math.h>
+
 #include "wt_common.cuh"
 
 namespace wtf {
@@ -134,9 +140,8 @@ struct Shared {
     unsigned long long res_cnt[2];
     unsigned int res_digit[2];
     unsigned int red[3][T / 32];
-    int ticket;       // next ticket of this CTA (prefetched)
-    int flag;         // broadcast slot (last finisher, fallback decision)
-    WtFJob job;       // the job of the current context
+    int jidx[2][WT_F_JIDX];   // first item of every job in the full / sample item space
+    WtFJob job;       // the job of the current segment
 };
 
 // ---- block scans over global (L2) histograms -------------------------------------------------------------------------
@@ -325,36 +330,115 @@ __device__ __forceinline__ void cand_for_each(const unsigned int* cand, unsigned
     for (unsigned int i = (nvec << 2) + threadIdx.x; i < n; i += T) op(__ldcg(&cand[i]));
 }
 
-// the histogram passes: S / X1 bin key bits 30..19, X2 bits 18..8 and X3 bits 7..0 of the keys that match the prefix
+// tuning aid (WT_FUSED_STAMPS): one globaltimer stamp per phase boundary and CTA
+__device__ __forceinline__ unsigned long long now_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// the histogram passes over N keys per thread: S / X1 bin key bits 30..19, X2 bits 18..8 and X3 bits 7..0 of the keys
+// that match the prefix found so far
+enum { HIST_TOP = 0, HIST_X2 = 1, HIST_X3 = 2 };
 struct HistOp {
     unsigned int* h;
-    int stage;
+    int kind;
     unsigned int p0, p1;
     bool two;
-    __device__ __forceinline__ void operator()(unsigned int key, bool valid) const {
-        if (!valid) return;
-        if (stage == WT_ST_S || stage == WT_ST_X1) {
-            atomicAdd(&h[key >> 19], 1u);
-        } else if (stage == WT_ST_X2) {
-            const unsigned int top = key >> 19;
-            if (top == p0) atomicAdd(&h[(key >> 8) & 2047u], 1u);
-            else if (two && top == p1) atomicAdd(&h[NBF + ((key >> 8) & 2047u)], 1u);
+    template <int N>
+    __device__ __forceinline__ void operator()(const unsigned int (&key)[N]) const {
+        if (kind == HIST_TOP) {
+#pragma unroll
+            for (int i = 0; i < N; ++i)
+                if (key[i] != WT_F_NOKEY) atomicAdd(&h[key[i] >> 19], 1u);
+        } else if (kind == HIST_X2) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+                const unsigned int top = key[i] >> 19;   // WT_F_NOKEY >> 19 = 8191 is no 12-bit prefix
+                if (top == p0) atomicAdd(&h[(key[i] >> 8) & 2047u], 1u);
+                else if (two && top == p1) atomicAdd(&h[NBF + ((key[i] >> 8) & 2047u)], 1u);
+            }
         } else {
-            const unsigned int top = key >> 8;
-            if (top == p0) atomicAdd(&h[key & 255u], 1u);
-            else if (two && top == p1) atomicAdd(&h[NBF3 + (key & 255u)], 1u);
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+                const unsigned int top = key[i] >> 8;
+                if (top == p0) atomicAdd(&h[key[i] & 255u], 1u);
+                else if (two && top == p1) atomicAdd(&h[NBF3 + (key[i] & 255u)], 1u);
+            }
+        }
+    }
+};
+
+// moves a warp's staged candidate keys to the job's global list (one global atomic per flush)
+__device__ __forceinline__ void warp_flush(const unsigned int* wbuf, unsigned int& wc, unsigned int* g_count, unsigned int* cand,
+                                           unsigned int cap) {
+    const int lane = threadIdx.x & 31;
+    unsigned int gbase = 0;
+    if (lane == 0) gbase = atomicAdd(g_count, wc);
+    gbase = __shfl_sync(0xffffffffu, gbase, 0);
+    __syncwarp();
+    for (unsigned int i = lane; i < wc; i += 32)
+        if (gbase + i < cap) cand[gbase + i] = wbuf[i];
+    __syncwarp();
+    wc = 0;
+}
+
+// the count / compact pass (phase C) over N keys per thread: keys below the bracket are counted, keys inside it go to
+// the warp's staging slice (positions from one warp prefix sum per group of <= WT_F_GROUP keys) and into the F1 histogram
+struct CompactOp {
+    unsigned int* h;
+    unsigned int* wbuf;
+    unsigned int* g_count;
+    unsigned int* cand;
+    unsigned int cap;
+    unsigned int lo, w;
+    int s1;
+    unsigned int nb, wc;   // hot accumulators, read back by the caller
+    template <int N>
+    __device__ __forceinline__ void operator()(const unsigned int (&key)[N]) {
+#pragma unroll
+        for (int g0 = 0; g0 < N; g0 += WT_F_GROUP) {
+            constexpr int G = WT_F_GROUP;
+            unsigned int hitmask = 0;
+#pragma unroll
+            for (int i = 0; i < G; ++i) {
+                if (g0 + i < N) {
+                    nb += key[g0 + i] < lo;
+                    if (key[g0 + i] - lo < w) hitmask |= 1u << i;
+                }
+            }
+            if (__any_sync(0xffffffffu, hitmask != 0u)) {
+                const int lane = threadIdx.x & 31;
+                const unsigned int nh = __popc(hitmask);
+                unsigned int inc = nh;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
+                    if (lane >= d) inc += o;
+                }
+                const unsigned int total = __shfl_sync(0xffffffffu, inc, 31);
+                unsigned int pos = wc + inc - nh;
+#pragma unroll
+                for (int i = 0; i < G; ++i) {
+                    if (g0 + i < N && (hitmask & (1u << i))) {
+                        wbuf[pos++] = key[g0 + i];
+                        atomicAdd(&h[(key[g0 + i] - lo) >> s1], 1u);
+                    }
+                }
+                wc += total;
+                if (wc > WT_F_WFLUSH) warp_flush(wbuf, wc, g_count, cand, cap);
+            }
         }
     }
 };
 
 // ======================================================================================================================
-// The CTA-side state machine.  K (the plane class) provides:
-//   THREADS, MIN_CTAS, SMEM_BYTES (class-private shared memory after Shared<THREADS>)
-//   init(smem)                                       once per CTA
-//   visit(bk, job, item, sampled, smem, op)          op(key, valid) for every explicit key of work item `item` (sampled:
-//                                                    of sample item `item`), called by all 32 lanes of a warp together
-//   apply(bk, job, item, t, smem, zc, nzb)           out = prune(in) for the item; zc += zeros written, nzb += nonzero inputs
-//   numel(job)                                       weight elements of the job
+// The CTA-side phases.  K (the plane class) provides:
+//   THREADS, MIN_CTAS, SMEM_BYTES (class-private shared memory after Shared<THREADS>), init(smem), numel(job)
+//   visit(bk, job, first, count, sampled, smem, op)   op(keys[N]) over every explicit key of items [first, first + count)
+//                                                     (sampled: of the sample items), N keys per thread at a time
+//                                                     (WT_F_NOKEY = none), called by all 32 lanes of a warp together
+//   apply(bk, job, first, count, t, smem, zc, nzb)    out = prune(in) for the items; zc += zeros written, nzb += nonzero inputs
 // ======================================================================================================================
 template <class K>
 struct Cta {
@@ -365,17 +449,6 @@ struct Cta {
     const WtFArgs& a;
     Sh& sh;
     unsigned char* ksm;  // class-private shared memory
-    // current context: every item of (stage, job) since the last flush
-    int stage = -1, job_i = -1, pending = 0;
-    bool skip = false;   // the job needs nothing from this stage (failed, already final, absolute threshold ...)
-    // stage-private accumulators
-    unsigned int nbelow = 0, wcount = 0;  // C (wcount is warp-uniform)
-    unsigned int zc = 0, nzb = 0;         // A
-    // stage parameters read from the job state when the context opens
-    unsigned int lo_key = 0, width = 0, pa = 0, pb = 0;
-    int sh_hi = 0, sh_lo = 0;
-    bool two = false;
-    float thr = 0.0f;
 
     __device__ Cta(const WtBank& bk_, const WtFArgs& a_, Sh& sh_, unsigned char* ksm_) : bk(bk_), a(a_), sh(sh_), ksm(ksm_) {}
 
@@ -418,432 +491,342 @@ struct Cta {
             if ((threadIdx.x & 31) == 0 && s) atomicAdd(&gc[b >> 5], s);
         }
     }
-    __device__ __forceinline__ void wait_flag(const unsigned int* f) {
-        if (threadIdx.x == 0)
-            while (ld_acquire(f) == 0u) __nanosleep(40);
+    // the job descriptor into shared memory (int4 copies)
+    __device__ __forceinline__ void load_job(int j) {
+        __syncthreads();
+        const int4* src = reinterpret_cast<const int4*>(a.jobs + j);
+        int4* dst = reinterpret_cast<int4*>(&sh.job);
+        for (int i = threadIdx.x; i < (int)(sizeof(WtFJob) / 16); i += T) dst[i] = __ldg(&src[i]);
         __syncthreads();
     }
-    __device__ __forceinline__ void warp_flush(unsigned int& wcount) {
-        const int lane = threadIdx.x & 31;
-        const unsigned int* wbuf = sh.stage + (threadIdx.x >> 5) * WT_F_WSTAGE;
-        unsigned int gbase = 0;
-        if (lane == 0) gbase = atomicAdd(&state(job_i)->s_count, wcount);
-        gbase = __shfl_sync(0xffffffffu, gbase, 0);
-        __syncwarp();
-        unsigned int* cand = sh.job.cand;
-        const unsigned int cap = sh.job.cand_cap;
-        for (unsigned int i = lane; i < wcount; i += 32)
-            if (gbase + i < cap) cand[gbase + i] = wbuf[i];
-        __syncwarp();
-        wcount = 0;
+    __device__ __forceinline__ int find_job(int item, bool sample) const {
+        int lo = 0, hi = a.n_jobs - 1;
+        const bool cached = a.n_jobs <= WT_F_JIDX;   // offsets in shared memory: no chain of dependent global loads
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            const int b = cached ? sh.jidx[sample ? 1 : 0][mid] : (sample ? __ldg(&a.jobs[mid].s_begin) : __ldg(&a.jobs[mid].item_begin));
+            if (b <= item) lo = mid; else hi = mid - 1;
+        }
+        return lo;
     }
-
-    // ---- failure: the job leaves the sampled pipeline; every later stage skips it and X1..XA run it after the queue ----
-    __device__ void fail_job(int j) {  // whole CTA
-        unsigned int* gh = hist1(j);
-        for (int b = threadIdx.x; b < NB1 + NCOARSE; b += T) gh[b] = 0u;  // held the sample: X1 starts from zero
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            WtFState* st = state(j);
-            st->failed = 1;
-            __threadfence();
-            atomicAdd(&header()->fail_count, 1u);
-            st_release(&st->ready[WT_RD_S], 1u);
-            st_release(&st->ready[WT_RD_C], 1u);
-            st_release(&st->ready[WT_RD_F2], 1u);
-            st_release(&st->ready[WT_RD_T], 1u);
-            __threadfence();
-            atomicAdd(&header()->verified, 1u);
+    // f(j, first, count) for every job overlapped by this CTA's contiguous share of the class's (sample) items; the
+    // job's descriptor is in sh.job when f runs
+    template <class F>
+    __device__ __forceinline__ void for_each_segment(bool sample, F f) {
+        const long long total = sample ? a.total_s_items : a.total_items;
+        const int lo = (int)(total * blockIdx.x / gridDim.x), hi = (int)(total * (blockIdx.x + 1) / gridDim.x);
+        if (lo >= hi) return;
+        int j = find_job(lo, sample), item = lo;
+        while (item < hi && j < a.n_jobs) {
+            load_job(j);
+            const int jb = sample ? sh.job.s_begin : sh.job.item_begin, jn = sample ? sh.job.s_items : sh.job.items;
+            if (item < jb + jn) {
+                const int end = hi < jb + jn ? hi : jb + jn;
+                f(j, item - jb, end - item);
+                item = end;
+            }
+            ++j;
         }
     }
 
-    // both order statistics as key patterns -> threshold -> published (thread 0 stores); v0, v1 = key - lo_key
-    __device__ void publish_threshold(int j, const WtFJob& job, unsigned int key0, unsigned int key1, unsigned int ready_slot) {
-        const float t = lerp_threshold(__uint_as_float(key0), __uint_as_float(key1), job.gamma, job.lerp_mode);
-        if (threadIdx.x == 0) {
-            WtFState* st = state(j);
-            st->a = __uint_as_float(key0);
-            st->b = __uint_as_float(key1);
-            st->t = t;
-            a.thresholds[job.layer] = t;
-            st_release(&st->ready[ready_slot], 1u);
-        }
-    }
-    __device__ void finish_sampled(int j, const WtFJob& job, unsigned int v0, unsigned int v1) {
-        WtFState* st = state(j);
-        const unsigned int lo = __ldcg(&st->lo_key);
-        unsigned long long e0, e1;
-        explicit_ranks(job, e0, e1);
-        const unsigned long long ez = (lo == 1u) ? __ldcg(&st->below) : 0ull;  // exact zeros among the explicit keys
-        const unsigned int key0 = (job.k0 < job.zeros || e0 < ez) ? 0u : lo + v0;  // a rank inside the zeros is 0
-        const unsigned int key1 = (job.k1 < job.zeros || e1 < ez) ? 0u : lo + v1;
-        publish_threshold(j, job, key0, key1, WT_RD_T);
+    // bits of (key - lo) below the F1 digit, taken by the F2 digit, left for F3
+    __device__ __forceinline__ static void tail_shifts(unsigned int w, int& s1, int& take2, int& s2) {
+        const int bits = 32 - __clz(w - 1u);
+        s1 = bits - 11;
+        take2 = s1 < 11 ? s1 : 11;
+        s2 = s1 - take2;
     }
 
-    // ---- what the CTA that completes stage `s` of job j does ("->" in the header comment) ------------------------------
-    __device__ void finisher(int s, int j) {
-        const WtFJob& job = sh.job;
-        WtFState* st = state(j);
-        if (s == WT_ST_S) {
+    // ---- S / X1: 12-bit histogram of the sample (S) or of every key of the failed jobs (X1) ------------------------------
+    __device__ __noinline__ void phase_hist_top(bool sample) {
+        for_each_segment(sample, [&](int j, int first, int count) {
+            if (!sample && !__ldcg(&state(j)->failed)) return;
+            if (sample && sh.job.lerp_mode == WT_LERP_ABSOLUTE) return;
+            clear_hist(NB1);
+            HistOp op{sh.hist, HIST_TOP, 0u, 0u, false};
+            K::visit(bk, sh.job, first, count, sample, ksm, op);
+            flush_hist1(j);
+        });
+    }
+
+    __device__ void mark_failed(WtFState* st) {   // one thread
+        st->failed = 1;
+        atomicAdd(&header()->fail_count, 1u);
+    }
+
+    // ---- C: bracket from the sample histogram; count below, compact the bracket, F1 histogram -----------------------------
+    __device__ __noinline__ void phase_compact() {
+        for_each_segment(false, [&](int j, int first, int count) {
+            const WtFJob& job = sh.job;
+            if (job.lerp_mode == WT_LERP_ABSOLUTE) return;
+            WtFState* st = state(j);
             unsigned long long e0, e1;
             explicit_ranks(job, e0, e1);
             const Found f = scan_find_two_level<T>(coarse(j), hist1(j), 0ull, e0, e1, sh, job.n);
-            if (f.d1 < f.d0 || job.cand == nullptr) { fail_job(j); return; }
+            const bool ok = !(f.d1 < f.d0 || job.cand == nullptr);
             // a bracket that starts at bin 0 leaves the exact zeros out of the list: they are counted as "below" and a
             // rank inside them is 0 without looking (the massive tie of this domain: pruned weights, vanishing details)
             const unsigned int lo = (f.d0 << 19) | (f.d0 == 0u ? 1u : 0u);
             const unsigned int w = ((f.d1 + 1u) << 19) - lo;
-            const int bits = 32 - __clz(w - 1u);
-            const int s1 = bits - 11, take2 = s1 < 11 ? s1 : 11;
-            if (threadIdx.x == 0) {
-                st->lo_key = lo; st->width = w; st->sh1 = s1; st->sh2 = s1 - take2;
-                st_release(&st->ready[WT_RD_S], 1u);
+            if (first == 0 && threadIdx.x == 0) {   // every CTA of the job takes the same decision from the same histogram
+                st->lo_key = lo;
+                st->width = ok ? w : 0u;
+                if (!ok) mark_failed(st);
+                else if (w > (1u << 22)) header()->wide = 1u;
             }
-        } else if (s == WT_ST_C) {
-            if (__ldcg(&st->failed)) return;
-            const unsigned int n_c = __ldcg(&st->s_count);
+            if (!ok) return;
+            int s1, take2, s2;
+            tail_shifts(w, s1, take2, s2);
+            clear_hist(NBF);
+            CompactOp op{sh.hist, sh.stage + (threadIdx.x >> 5) * WT_F_WSTAGE, &st->s_count, job.cand, job.cand_cap, lo, w, s1, 0u, 0u};
+            K::visit(bk, job, first, count, false, ksm, op);
+            if (op.wc) warp_flush(op.wbuf, op.wc, op.g_count, op.cand, op.cap);
+            unsigned int nb = op.nb;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) nb += __shfl_down_sync(0xffffffffu, nb, d);
+            if ((threadIdx.x & 31) == 0 && nb) atomicAdd(&st->below, (unsigned long long)nb);
+            flush_bins(histf1(j), NBF);
+        });
+    }
+
+    // exact-count check of the bracket C used: both ranks fall inside the candidate list (or inside the exact zeros below it)
+    __device__ __forceinline__ bool bracket_holds(const WtFJob& job, unsigned int lo, unsigned int n_c, unsigned long long below,
+                                                  unsigned long long& e0, unsigned long long& e1) const {
+        explicit_ranks(job, e0, e1);
+        const bool zlo = lo == 1u;  // the bracket starts at bin 0: `below` counts the exact zeros
+        const bool in0 = (zlo && e0 < below) || (below <= e0 && e0 < below + (unsigned long long)n_c);
+        const bool in1 = (zlo && e1 < below) || (below <= e1 && e1 < below + (unsigned long long)n_c);
+        return n_c <= job.cand_cap && in0 && in1;
+    }
+
+    // ---- T1 / T2: the candidate lists in slices of WT_F_SLICE keys; slice sl of job j belongs to CTA (37 j + sl) mod grid ----
+    __device__ __noinline__ void phase_tail(int round) {
+        unsigned int* cnt = sh.stage;   // free outside phase C: every job's list length, read once
+        __syncthreads();
+        for (int i = threadIdx.x; i < a.n_jobs; i += T) cnt[i] = __ldcg(&state(i)->s_count);
+        __syncthreads();
+        const unsigned int G = gridDim.x;
+        for (int j = 0; j < a.n_jobs; ++j) {
+            unsigned int n_c = cnt[j];
+            const unsigned int slices = n_c ? (n_c + WT_F_SLICE - 1) / WT_F_SLICE : 1u;
+            const unsigned int sl0 = (blockIdx.x + G - (unsigned int)((37ull * j) % G)) % G;
+            if (sl0 >= slices) continue;   // CTA-uniform
+            load_job(j);
+            const WtFJob& job = sh.job;
+            WtFState* st = state(j);
+            unsigned int* gh1 = hist1(j);
+            const bool owner = sl0 == 0u;
+            const unsigned int lo = __ldcg(&st->lo_key), w = __ldcg(&st->width);
+            if (__ldcg(&st->failed) || w == 0u) {   // failed in C (or, round 2, in T1): the sample histogram must not reach X1
+                if (owner && round == 1) for (int b = threadIdx.x; b < NB1 + NCOARSE; b += T) gh1[b] = 0u;
+                continue;
+            }
             const unsigned long long below = __ldcg(&st->below);
             unsigned long long e0, e1;
-            explicit_ranks(job, e0, e1);
-            const bool zlo = __ldcg(&st->lo_key) == 1u;  // then `below` counts the exact zeros
-            const bool in0 = (zlo && e0 < below) || (below <= e0 && e0 < below + (unsigned long long)n_c);
-            const bool in1 = (zlo && e1 < below) || (below <= e1 && e1 < below + (unsigned long long)n_c);
-            if (!(n_c <= job.cand_cap && in0 && in1)) { fail_job(j); return; }
-            const unsigned int* h = histf1(j);
-            const Found f = scan_find_pair<T, NBF>(h, h, 0ull, 0ull, e0 < below ? 0ull : e0 - below, e1 < below ? 0ull : e1 - below, sh);
-            if (threadIdx.x == 0) {
-                st->d[0] = f.d0; st->d[1] = f.d1; st->r[0] = f.r0; st->r[1] = f.r1;
-                st_release(&st->ready[WT_RD_C], 1u);
-                __threadfence();
-                atomicAdd(&header()->verified, 1u);
-            }
-        } else if (s == WT_ST_F2) {
-            if (__ldcg(&st->failed)) return;
-            const unsigned int d0 = __ldcg(&st->d[0]), d1 = __ldcg(&st->d[1]);
-            const int s1 = __ldcg(&st->sh1), s2 = __ldcg(&st->sh2);
-            const unsigned int* h = histf2(j);
-            const Found f = scan_find_pair<T, NBF>(h, d0 != d1 ? h + NBF : h, 0ull, 0ull, __ldcg(&st->r[0]), __ldcg(&st->r[1]), sh);
-            const unsigned int q0 = (d0 << (s1 - s2)) | f.d0, q1 = (d1 << (s1 - s2)) | f.d1;
-            if (s2 == 0) {
-                finish_sampled(j, job, q0, q1);
-            } else if (threadIdx.x == 0) {
-                st->d2[0] = q0; st->d2[1] = q1; st->r2[0] = f.r0; st->r2[1] = f.r1;
-                st_release(&st->ready[WT_RD_F2], 1u);
-            }
-        } else if (s == WT_ST_F3) {
-            if (__ldcg(&st->failed) || __ldcg(&st->sh2) == 0) return;
-            const unsigned int q0 = __ldcg(&st->d2[0]), q1 = __ldcg(&st->d2[1]);
-            const int s2 = __ldcg(&st->sh2);
-            const unsigned int* h = histf3(j);
-            const Found f = scan_find_pair<T, NBF3>(h, q0 != q1 ? h + NBF3 : h, 0ull, 0ull, __ldcg(&st->r2[0]), __ldcg(&st->r2[1]), sh);
-            finish_sampled(j, job, (q0 << s2) | f.d0, (q1 << s2) | f.d1);
-        } else if (s == WT_ST_X1) {
-            const Found f = scan_find_two_level<T>(coarse(j), hist1(j), (unsigned long long)job.zeros, (unsigned long long)job.k0,
-                                                   (unsigned long long)job.k1, sh, 0);
-            if (threadIdx.x == 0) {
-                st->d[0] = f.d0; st->d[1] = f.d1; st->r[0] = f.r0; st->r[1] = f.r1;
-                st_release(&st->ready[WT_RD_X1], 1u);
-            }
-        } else if (s == WT_ST_X2) {
-            const unsigned int p0 = __ldcg(&st->d[0]), p1 = __ldcg(&st->d[1]);
-            const unsigned long long z = (unsigned long long)job.zeros;
-            const unsigned int* h = histf2(j);
-            const Found f = scan_find_pair<T, NBF>(h, p0 != p1 ? h + NBF : h, p0 == 0u ? z : 0ull, p1 == 0u ? z : 0ull,
-                                                   __ldcg(&st->r[0]), __ldcg(&st->r[1]), sh);
-            if (threadIdx.x == 0) {
-                st->d2[0] = (p0 << 11) | f.d0; st->d2[1] = (p1 << 11) | f.d1; st->r2[0] = f.r0; st->r2[1] = f.r1;
-                st_release(&st->ready[WT_RD_X2], 1u);
-            }
-        } else if (s == WT_ST_X3) {
-            const unsigned int n0 = __ldcg(&st->d2[0]), n1 = __ldcg(&st->d2[1]);
-            const unsigned long long z = (unsigned long long)job.zeros;
-            const unsigned int* h = histf3(j);
-            const Found f = scan_find_pair<T, NBF3>(h, n0 != n1 ? h + NBF3 : h, n0 == 0u ? z : 0ull, n1 == 0u ? z : 0ull,
-                                                    __ldcg(&st->r2[0]), __ldcg(&st->r2[1]), sh);
-            publish_threshold(j, job, (n0 << 8) | f.d0, (n1 << 8) | f.d1, WT_RD_XT);
-        } else {  // A / XA: the job's counts are complete
-            if (s == WT_ST_A && job.lerp_mode != WT_LERP_ABSOLUTE && __ldcg(&st->failed)) return;
-            if (threadIdx.x == 0) {
-                const long long numel = K::numel(job);
-                const long long z = (long long)__ldcg(&st->zc);
-                long long* c = a.counts + (size_t)job.layer * 4;
-                c[0] = numel; c[1] = numel - z; c[2] = z; c[3] = (long long)__ldcg(&st->nzb);
-            }
-        }
-    }
-
-    // number of items stage s has for the job
-    __device__ __forceinline__ int stage_items(int s, const WtFJob& job) const {
-        if (s == WT_ST_S) return job.s_chunks;
-        if (s == WT_ST_F2 || s == WT_ST_F3) return job.f_chunks;
-        return job.chunks;
-    }
-
-    // ---- closes the current context: partial results to the job's global state, then the completion count ------------
-    __device__ __noinline__ void flush() {
-        if (stage < 0) return;
-        const int s = stage, j = job_i;
-        WtFState* st = state(j);
-        if (!skip) {
-            if (s == WT_ST_S || s == WT_ST_X1) {
-                flush_hist1(j);
-            } else if (s == WT_ST_C) {
-                if (wcount) warp_flush(wcount);
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) nbelow += __shfl_down_sync(0xffffffffu, nbelow, d);
-                if ((threadIdx.x & 31) == 0 && nbelow) atomicAdd(&st->below, (unsigned long long)nbelow);
-                nbelow = 0;
-                flush_bins(histf1(j), NBF);
-            } else if (s == WT_ST_F2 || s == WT_ST_X2) {
-                flush_bins(histf2(j), 2 * NBF);
-            } else if (s == WT_ST_F3 || s == WT_ST_X3) {
-                flush_bins(histf3(j), 2 * NBF3);
-            } else {  // A / XA
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) {
-                    zc += __shfl_down_sync(0xffffffffu, zc, d);
-                    nzb += __shfl_down_sync(0xffffffffu, nzb, d);
+            if (!bracket_holds(job, lo, n_c, below, e0, e1)) {   // every CTA of the job sees the same counts
+                if (owner && round == 1) {
+                    for (int b = threadIdx.x; b < NB1 + NCOARSE; b += T) gh1[b] = 0u;
+                    if (threadIdx.x == 0) mark_failed(st);
                 }
-                if ((threadIdx.x & 31) == 0) {
-                    if (zc) atomicAdd(&st->zc, (unsigned long long)zc);
-                    if (nzb) atomicAdd(&st->nzb, (unsigned long long)nzb);
-                }
-                zc = nzb = 0;
+                continue;
             }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            __threadfence();
-            const unsigned int prev = atomicAdd(&st->done[s], (unsigned int)pending);
-            const int last = (prev + (unsigned int)pending == (unsigned int)stage_items(s, sh.job));
-            if (last) __threadfence();
-            sh.flag = last;
-        }
-        __syncthreads();
-        const int last = sh.flag;
-        __syncthreads();
-        if (last) finisher(s, j);
-        stage = -1;
-        pending = 0;
-    }
-
-    // ---- opens the context (stage s, job j): dependencies, stage parameters, shared histogram ----------------------------
-    __device__ void open(int s, int j) {
-        stage = s; job_i = j; pending = 0; skip = false;
-        __syncthreads();
-        {   // the job descriptor into shared memory (int4 copies)
-            const int4* src = reinterpret_cast<const int4*>(a.jobs + j);
-            int4* dst = reinterpret_cast<int4*>(&sh.job);
-            for (int i = threadIdx.x; i < (int)(sizeof(WtFJob) / 16); i += T) dst[i] = __ldg(&src[i]);
-        }
-        __syncthreads();
-        const WtFJob& job = sh.job;
-        WtFState* st = state(j);
-        const bool absolute = job.lerp_mode == WT_LERP_ABSOLUTE;
-        switch (s) {
-            case WT_ST_S:
-                clear_hist(NB1);
-                break;
-            case WT_ST_C:
-                wait_flag(&st->ready[WT_RD_S]);
-                if (__ldcg(&st->failed)) { skip = true; break; }
-                lo_key = __ldcg(&st->lo_key); width = __ldcg(&st->width); sh_hi = __ldcg(&st->sh1);
-                nbelow = 0; wcount = 0;
-                clear_hist(NBF);
-                break;
-            case WT_ST_F2:
-                wait_flag(&st->ready[WT_RD_C]);
-                if (__ldcg(&st->failed)) { skip = true; break; }
-                lo_key = __ldcg(&st->lo_key); sh_hi = __ldcg(&st->sh1); sh_lo = __ldcg(&st->sh2);
-                pa = __ldcg(&st->d[0]); pb = __ldcg(&st->d[1]); two = pa != pb;
+            int s1, take2, s2;
+            tail_shifts(w, s1, take2, s2);
+            unsigned int p0, p1;
+            unsigned int* h = sh.hist;
+            if (round == 1) {
+                const unsigned int* g1 = histf1(j);
+                const Found f = scan_find_pair<T, NBF>(g1, g1, 0ull, 0ull, e0 < below ? 0ull : e0 - below, e1 < below ? 0ull : e1 - below, sh);
+                p0 = f.d0; p1 = f.d1;
+                if (owner && threadIdx.x == 0) { st->d[0] = p0; st->d[1] = p1; st->r[0] = f.r0; st->r[1] = f.r1; }
+                if (n_c == 0u) continue;
                 clear_hist(2 * NBF);
-                break;
-            case WT_ST_F3:
-                wait_flag(&st->ready[WT_RD_C]);   // sh2 is known since S; F2's digits are needed only if F3 runs
-                if (__ldcg(&st->failed) || __ldcg(&st->sh2) == 0) { skip = true; break; }
-                wait_flag(&st->ready[WT_RD_F2]);
-                lo_key = __ldcg(&st->lo_key); sh_lo = __ldcg(&st->sh2);
-                pa = __ldcg(&st->d2[0]); pb = __ldcg(&st->d2[1]); two = pa != pb;
+            } else {
+                if (s2 == 0) continue;
+                const unsigned int d0 = __ldcg(&st->d[0]), d1 = __ldcg(&st->d[1]);
+                const unsigned int* g2 = histf2(j);
+                const Found f = scan_find_pair<T, NBF>(g2, d0 != d1 ? g2 + NBF : g2, 0ull, 0ull, __ldcg(&st->r[0]), __ldcg(&st->r[1]), sh);
+                p0 = (d0 << take2) | f.d0; p1 = (d1 << take2) | f.d1;
+                if (owner && threadIdx.x == 0) { st->d2[0] = p0; st->d2[1] = p1; st->r2[0] = f.r0; st->r2[1] = f.r1; }
+                if (n_c == 0u) continue;
                 clear_hist(2 * NBF3);
-                break;
-            case WT_ST_A:
-                if (absolute) { thr = job.abs_threshold; zc = nzb = 0; break; }
-                wait_flag(&st->ready[WT_RD_T]);
-                if (__ldcg(&st->failed)) { skip = true; break; }
-                thr = __ldcg(&st->t); zc = nzb = 0;
-                break;
-            case WT_ST_X1:
-                clear_hist(NB1);
-                break;
-            case WT_ST_X2:
-                wait_flag(&st->ready[WT_RD_X1]);
-                pa = __ldcg(&st->d[0]); pb = __ldcg(&st->d[1]); two = pa != pb;
-                clear_hist(2 * NBF);
-                break;
-            case WT_ST_X3:
-                wait_flag(&st->ready[WT_RD_X2]);
-                pa = __ldcg(&st->d2[0]); pb = __ldcg(&st->d2[1]); two = pa != pb;
-                clear_hist(2 * NBF3);
-                break;
-            default:  // XA
-                wait_flag(&st->ready[WT_RD_XT]);
-                thr = __ldcg(&st->t); zc = nzb = 0;
-                break;
-        }
-    }
-
-    // ---- one item ----------------------------------------------------------------------------------------------------
-    __device__ __forceinline__ void run_item(int s, int j, int idx) {
-        if (s != stage || j != job_i) {
-            flush();
-            open(s, j);
-        }
-        ++pending;
-        if (skip) return;
-        const WtFJob& job = sh.job;
-        unsigned int* h = sh.hist;
-        switch (s) {
-            case WT_ST_S:
-            case WT_ST_X1:
-            case WT_ST_X2:
-            case WT_ST_X3: {   // one instantiation of the class's visit for the four histogram passes
-                HistOp op{h, s, pa, pb, two};
-                K::visit(bk, job, idx, s == WT_ST_S, ksm, op);
-            } break;
-            case WT_ST_C: {
-                const int lane = threadIdx.x & 31;
-                unsigned int* wbuf = sh.stage + (threadIdx.x >> 5) * WT_F_WSTAGE;
-                const unsigned int lo = lo_key, w = width;
-                const int s1 = sh_hi;
-                const unsigned int lt = (1u << lane) - 1u;
-                unsigned int nb = nbelow, wc = wcount;   // hot accumulators in registers for the pass
-                auto op = [&, h, wbuf, lo, w, s1, lt](unsigned int key, bool valid) {
-                    nb += (valid && key < lo);
-                    const unsigned int v = key - lo;
-                    const bool hit = valid && v < w;
-                    const unsigned int ballot = __ballot_sync(0xffffffffu, hit);
-                    if (ballot) {
-                        if (hit) {
-                            wbuf[wc + __popc(ballot & lt)] = key;
-                            atomicAdd(&h[v >> s1], 1u);
-                        }
-                        wc += __popc(ballot);
-                        if (wc > WT_F_WFLUSH) warp_flush(wc);
-                    }
-                };
-                K::visit(bk, job, idx, false, ksm, op);
-                nbelow = nb;
-                wcount = wc;
-            } break;
-            case WT_ST_F2:
-            case WT_ST_F3: {
-                WtFState* st = state(j);
-                const unsigned int n_c = __ldcg(&st->s_count);
-                const unsigned int lo = cand_boundary(n_c, idx, job.f_chunks), hi = cand_boundary(n_c, idx + 1, job.f_chunks);
-                const unsigned int lk = lo_key, p0 = pa, p1 = pb;
-                const bool tw = two;
-                if (s == WT_ST_F2) {
-                    const int s1 = sh_hi, s2 = sh_lo;
-                    const unsigned int mask = (1u << (s1 - s2)) - 1u;
-                    cand_for_each<T>(job.cand + lo, hi - lo, [=](unsigned int k) {
-                        const unsigned int v = k - lk, top = v >> s1;
+            }
+            const bool tw = p0 != p1;
+            for (unsigned int sl = sl0; sl < slices; sl += G) {
+                const unsigned int c0 = sl * WT_F_SLICE, len = n_c - c0 < WT_F_SLICE ? n_c - c0 : WT_F_SLICE;
+                if (round == 1) {
+                    const unsigned int mask = (1u << take2) - 1u;
+                    cand_for_each<T>(job.cand + c0, len, [=](unsigned int k) {
+                        const unsigned int v = k - lo, top = v >> s1;
                         if (top == p0) atomicAdd(&h[(v >> s2) & mask], 1u);
                         else if (tw && top == p1) atomicAdd(&h[NBF + ((v >> s2) & mask)], 1u);
                     });
                 } else {
-                    const int s2 = sh_lo;
                     const unsigned int mask = (1u << s2) - 1u;
-                    cand_for_each<T>(job.cand + lo, hi - lo, [=](unsigned int k) {
-                        const unsigned int v = k - lk, top = v >> s2;
+                    cand_for_each<T>(job.cand + c0, len, [=](unsigned int k) {
+                        const unsigned int v = k - lo, top = v >> s2;
                         if (top == p0) atomicAdd(&h[v & mask], 1u);
                         else if (tw && top == p1) atomicAdd(&h[NBF3 + (v & mask)], 1u);
                     });
                 }
-            } break;
-            default: {  // A / XA
-                unsigned int z = zc, nb = nzb;
-                K::apply(bk, job, idx, thr, ksm, z, nb);
-                zc = z;
-                nzb = nb;
-            } break;
+            }
+            if (round == 1) flush_bins(histf2(j), 2 * NBF); else flush_bins(histf3(j), 2 * NBF3);
         }
     }
 
-    // ticket -> (stage, job, index) through the segment table; `seg` caches the last hit (tickets only grow)
-    __device__ __forceinline__ void decode(int t, int& seg, int& s, int& j, int& idx) const {
-        int first = __ldg(&a.segs[seg].first), count = __ldg(&a.segs[seg].count);
-        if (t >= first + count) {
-            int lo = seg + 1, hi = a.n_segs - 1;
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (__ldg(&a.segs[mid].first) <= t) lo = mid; else hi = mid - 1;
+    // ---- X2 / X3: the exact path's second and third digit over every key of the failed jobs -------------------------------
+    __device__ __noinline__ void phase_exact(int which) {
+        for_each_segment(false, [&](int j, int first, int count) {
+            WtFState* st = state(j);
+            if (!__ldcg(&st->failed)) return;
+            const WtFJob& job = sh.job;
+            const unsigned long long z = (unsigned long long)job.zeros;
+            unsigned int p0, p1;
+            if (which == 2) {
+                const Found f = scan_find_two_level<T>(coarse(j), hist1(j), z, (unsigned long long)job.k0, (unsigned long long)job.k1, sh, 0);
+                p0 = f.d0; p1 = f.d1;
+                if (first == 0 && threadIdx.x == 0) { st->d[0] = p0; st->d[1] = p1; st->r[0] = f.r0; st->r[1] = f.r1; }
+                clear_hist(2 * NBF);
+            } else {
+                const unsigned int d0 = __ldcg(&st->d[0]), d1 = __ldcg(&st->d[1]);
+                const unsigned int* g2 = histf2(j);
+                const Found f = scan_find_pair<T, NBF>(g2, d0 != d1 ? g2 + NBF : g2, d0 == 0u ? z : 0ull, d1 == 0u ? z : 0ull,
+                                                       __ldcg(&st->r[0]), __ldcg(&st->r[1]), sh);
+                p0 = (d0 << 11) | f.d0; p1 = (d1 << 11) | f.d1;
+                if (first == 0 && threadIdx.x == 0) { st->d2[0] = p0; st->d2[1] = p1; st->r2[0] = f.r0; st->r2[1] = f.r1; }
+                clear_hist(2 * NBF3);
             }
-            seg = lo;
-            first = __ldg(&a.segs[seg].first);
-        }
-        s = __ldg(&a.segs[seg].stage);
-        j = __ldg(&a.segs[seg].job);
-        idx = t - first;
+            HistOp op{sh.hist, which == 2 ? HIST_X2 : HIST_X3, p0, p1, p0 != p1};
+            K::visit(bk, job, first, count, false, ksm, op);
+            if (which == 2) flush_bins(histf2(j), 2 * NBF); else flush_bins(histf3(j), 2 * NBF3);
+        });
     }
 
-    // fallback ticket -> (stage, job, index): stage-major over the failed jobs (rare path, linear walk)
-    __device__ bool decode_fallback(int t, int& s, int& j, int& idx) const {
-        for (int st = WT_ST_X1; st <= WT_ST_XA; ++st)
-            for (int q = 0; q < a.n_jobs; ++q) {
-                if (!__ldcg(&state(q)->failed)) continue;
-                const int n = __ldg(&a.jobs[q].chunks);
-                if (t < n) { s = st; j = q; idx = t; return true; }
-                t -= n;
+    // ---- A / XA: threshold from the last histogram; apply; counts -----------------------------------------------------------
+    __device__ __noinline__ void phase_apply(bool exact) {
+        for_each_segment(false, [&](int j, int first, int count) {
+            const WtFJob& job = sh.job;
+            WtFState* st = state(j);
+            float thr;
+            if (job.lerp_mode == WT_LERP_ABSOLUTE) {
+                if (exact) return;
+                thr = job.abs_threshold;
+            } else {
+                if (exact != (__ldcg(&st->failed) != 0)) return;
+                unsigned int key0, key1;
+                if (!exact) {
+                    const unsigned int lo = __ldcg(&st->lo_key), w = __ldcg(&st->width);
+                    const unsigned long long below = __ldcg(&st->below);
+                    int s1, take2, s2;
+                    tail_shifts(w, s1, take2, s2);
+                    unsigned int q0, q1;
+                    if (s2 == 0) {
+                        const unsigned int d0 = __ldcg(&st->d[0]), d1 = __ldcg(&st->d[1]);
+                        const unsigned int* g2 = histf2(j);
+                        const Found f = scan_find_pair<T, NBF>(g2, d0 != d1 ? g2 + NBF : g2, 0ull, 0ull, __ldcg(&st->r[0]), __ldcg(&st->r[1]), sh);
+                        q0 = (d0 << take2) | f.d0; q1 = (d1 << take2) | f.d1;
+                    } else {
+                        const unsigned int d0 = __ldcg(&st->d2[0]), d1 = __ldcg(&st->d2[1]);
+                        const unsigned int* g3 = histf3(j);
+                        const Found f = scan_find_pair<T, NBF3>(g3, d0 != d1 ? g3 + NBF3 : g3, 0ull, 0ull, __ldcg(&st->r2[0]), __ldcg(&st->r2[1]), sh);
+                        q0 = (d0 << s2) | f.d0; q1 = (d1 << s2) | f.d1;
+                    }
+                    unsigned long long e0, e1;
+                    explicit_ranks(job, e0, e1);
+                    const unsigned long long ez = lo == 1u ? below : 0ull;         // exact zeros among the explicit keys
+                    key0 = (job.k0 < job.zeros || e0 < ez) ? 0u : lo + q0;         // a rank inside the zeros is 0
+                    key1 = (job.k1 < job.zeros || e1 < ez) ? 0u : lo + q1;
+                } else {
+                    const unsigned int n0 = __ldcg(&st->d2[0]), n1 = __ldcg(&st->d2[1]);
+                    const unsigned long long z = (unsigned long long)job.zeros;
+                    const unsigned int* g3 = histf3(j);
+                    const Found f = scan_find_pair<T, NBF3>(g3, n0 != n1 ? g3 + NBF3 : g3, n0 == 0u ? z : 0ull, n1 == 0u ? z : 0ull,
+                                                            __ldcg(&st->r2[0]), __ldcg(&st->r2[1]), sh);
+                    key0 = (n0 << 8) | f.d0; key1 = (n1 << 8) | f.d1;
+                }
+                thr = lerp_threshold(__uint_as_float(key0), __uint_as_float(key1), job.gamma, job.lerp_mode);
+                if (first == 0 && threadIdx.x == 0) {
+                    st->a = __uint_as_float(key0); st->b = __uint_as_float(key1); st->t = thr;
+                    a.thresholds[job.layer] = thr;
+                }
             }
-        return false;
+            unsigned int zc = 0, nzb = 0;
+            K::apply(bk, job, first, count, thr, ksm, zc, nzb);
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+                zc += __shfl_down_sync(0xffffffffu, zc, d);
+                nzb += __shfl_down_sync(0xffffffffu, nzb, d);
+            }
+            if ((threadIdx.x & 31) == 0) {
+                if (zc) atomicAdd(&st->zc, (unsigned long long)zc);
+                if (nzb) atomicAdd(&st->nzb, (unsigned long long)nzb);
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {   // the CTA that completes the job's last item writes its counts
+                __threadfence();
+                const unsigned int prev = atomicAdd(&st->done, (unsigned int)count);
+                if (prev + (unsigned int)count == (unsigned int)job.items) {
+                    __threadfence();
+                    const long long numel = K::numel(job);
+                    const long long z = (long long)__ldcg(&st->zc);
+                    long long* c = a.counts + (size_t)job.layer * 4;
+                    c[0] = numel; c[1] = numel - z; c[2] = z; c[3] = (long long)__ldcg(&st->nzb);
+                }
+            }
+        });
+    }
+
+    __device__ __forceinline__ void stamp(int i) const {
+        if (a.stamps && threadIdx.x == 0) a.stamps[(size_t)blockIdx.x * WT_F_STAMP_SLOTS + i] = now_ns();
     }
 
     __device__ void run() {
-        // zero the scratch block of the next run (16-byte stores, grid-strided)
-        {
+        stamp(0);
+        if (a.n_jobs <= WT_F_JIDX) {
+            for (int i = threadIdx.x; i < a.n_jobs; i += T) {
+                sh.jidx[0][i] = __ldg(&a.jobs[i].item_begin);
+                sh.jidx[1][i] = __ldg(&a.jobs[i].s_begin);
+            }
+            __syncthreads();
+        }
+        {   // zero the scratch block of the next run (16-byte stores, grid-strided)
             int4* z = reinterpret_cast<int4*>(a.scratch_next);
             const unsigned long long n16 = a.scratch_bytes >> 4;
             for (unsigned long long i = (unsigned long long)blockIdx.x * T + threadIdx.x; i < n16; i += (unsigned long long)gridDim.x * T)
                 z[i] = make_int4(0, 0, 0, 0);
         }
-        WtFHeader* hd = header();
-        if (threadIdx.x == 0) sh.ticket = atomicAdd(&hd->ticket, 1);
-        __syncthreads();
-        int seg = 0;
-        bool fallback = false;
-        while (true) {
-            const int t = sh.ticket;
-            __syncthreads();
-            int next = 0, s, j, idx;
-            if (!fallback) {
-                if (t >= a.n_tickets) {
-                    flush();
-                    if (a.n_select == 0) return;
-                    // every select job has been verified (or has failed) before the jobs that failed are counted
-                    if (threadIdx.x == 0) {
-                        while (ld_acquire(&hd->verified) < (unsigned int)a.n_select) __nanosleep(100);
-                        sh.flag = (int)ld_acquire(&hd->fail_count);
-                    }
-                    __syncthreads();
-                    const int failed = sh.flag;
-                    __syncthreads();
-                    if (!failed) return;
-                    fallback = true;   // X1..XA of the failed jobs, from the second ticket counter
-                    if (threadIdx.x == 0) sh.ticket = atomicAdd(&hd->ticket2, 1);
-                    __syncthreads();
-                    continue;
-                }
-                if (threadIdx.x == 0) next = atomicAdd(&hd->ticket, 1);   // in flight while this item runs
-                decode(t, seg, s, j, idx);
-            } else {
-                if (!decode_fallback(t, s, j, idx)) break;
-                if (threadIdx.x == 0) next = atomicAdd(&hd->ticket2, 1);
+        if (a.n_select > 0) {
+            cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+            phase_hist_top(true);
+            stamp(1);
+            grid.sync();
+            phase_compact();
+            stamp(2);
+            grid.sync();
+            phase_tail(1);
+            stamp(3);
+            grid.sync();
+            if (__ldcg(&header()->wide)) {   // grid-uniform: set during C
+                phase_tail(2);
+                grid.sync();
             }
-            run_item(s, j, idx);
-            if (threadIdx.x == 0) sh.ticket = next;
-            __syncthreads();
+            stamp(4);
+            phase_apply(false);
+            stamp(5);
+            if (__ldcg(&header()->fail_count)) {   // grid-uniform: final since the barrier after T1
+                phase_hist_top(false);
+                grid.sync();
+                phase_exact(2);
+                grid.sync();
+                phase_exact(3);
+                grid.sync();
+                phase_apply(true);
+                stamp(6);
+            }
+        } else {
+            phase_apply(false);
+            stamp(5);
         }
-        flush();
     }
 };
 
@@ -861,14 +844,15 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_CTAS) wt_fused_kernel(const
 template <class K>
 constexpr size_t smem_bytes() { return ((sizeof(Shared<K::THREADS>) + 127) / 128) * 128 + K::SMEM_BYTES; }
 
-// launch helper: grid = min(tickets, resident CTAs)
+// grid = what fits the device minus `reserve`, at most one CTA per item; cooperative when the class runs a select
 template <class K>
-int launch(const WtBank& bank, const WtFArgs& args, int max_grid, cudaStream_t stream) {
+int launch(const WtBank& bank, const WtFArgs& args, int reserve, double share, cudaStream_t stream, int* grid_out) {
     static int blocks_per_sm[64] = {0};  // per device; racing threads compute the same value
     WtDeviceInfo di;
     int rc = wt_device_info(&di);
     if (rc) return rc;
     WT_CHECK(di.device >= 0 && di.device < 64, WT_E_UNSUPPORTED, "device ordinal %d out of range", di.device);
+    WT_CHECK(di.coop, WT_E_UNSUPPORTED, "device does not support cooperative launch");
     const size_t smem = smem_bytes<K>();
     if (blocks_per_sm[di.device] == 0) {
         WT_CUDA(cudaFuncSetAttribute(wt_fused_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -877,12 +861,22 @@ int launch(const WtBank& bank, const WtFArgs& args, int max_grid, cudaStream_t s
         WT_CHECK(nb > 0, WT_E_CUDA, "fused kernel does not fit on an SM");
         blocks_per_sm[di.device] = nb;
     }
-    int grid = blocks_per_sm[di.device] * di.sm_count;
-    if (max_grid > 0 && grid > max_grid) grid = max_grid;
-    if (grid > args.n_tickets) grid = args.n_tickets;
+    const int cap = blocks_per_sm[di.device] * di.sm_count;
+    int grid = cap - reserve;
+    const int fair = (int)ceil(share * cap);
+    if (grid > fair) grid = fair;
+    if (grid > args.total_items) grid = args.total_items;
     if (grid < 1) grid = 1;
-    wt_fused_kernel<K><<<grid, K::THREADS, smem, stream>>>(bank, args);
-    WT_CUDA(cudaGetLastError());
+    if (grid_out) *grid_out = grid;
+    if (args.n_select > 0) {
+        WtBank b = bank;
+        WtFArgs a = args;
+        void* params[] = {&b, &a};
+        WT_CUDA(cudaLaunchCooperativeKernel((const void*)wt_fused_kernel<K>, dim3(grid), dim3(K::THREADS), params, smem, stream));
+    } else {
+        wt_fused_kernel<K><<<grid, K::THREADS, smem, stream>>>(bank, args);
+        WT_CUDA(cudaGetLastError());
+    }
     return WT_OK;
 }
 

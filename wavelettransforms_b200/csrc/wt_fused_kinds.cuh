@@ -5,7 +5,7 @@
 //                       (SURVEY F5); also <2-D tensors (dwt_pruning.py:58-62).  Keys = |w|.
 //   SmallKind<H,W,F,Z>  conv-kernel planes 1x1 / 3x3 / 5x5 / 7x7 at levels 1..6, periodization: one thread per plane, the
 //                       whole multi-level transform in registers (wt_small_core.cuh), planes staged through shared memory
-//                       with 1-D TMA bulk copies (cp.async.bulk + mbarrier, double-buffered inside an item).  Keys = |c| of
+//                       with 1-D TMA bulk copies (cp.async.bulk + mbarrier, double-buffered over a segment's tiles).  Keys = |c| of
 //                       the coefficients, recomputed from the weights wherever they are needed; never stored.
 #pragma once
 #include "wt_fused.cuh"
@@ -15,63 +15,64 @@ namespace wtf {
 
 // ======================================================================================================================
 struct FlatKind {
-#ifndef WT_F_FLAT_THREADS
-#define WT_F_FLAT_THREADS 256
-#define WT_F_FLAT_MIN_CTAS 2
-#endif
-    static constexpr int THREADS = WT_F_FLAT_THREADS;
-    static constexpr int MIN_CTAS = WT_F_FLAT_MIN_CTAS;
+    static constexpr int THREADS = 256;
+    static constexpr int MIN_CTAS = 4;
     static constexpr size_t SMEM_BYTES = 0;
-    static constexpr int UNROLL = WT_F_FLAT_CHUNK / (4 * WT_F_FLAT_THREADS);   // float4 loads in flight per thread
-    static constexpr int CHUNK = THREADS * UNROLL * 4;     // 8192 elements per item
-    static_assert(CHUNK == WT_F_FLAT_CHUNK, "host geometry");
+    static constexpr int UNROLL = 4;                 // float4 loads in flight per thread
+    static constexpr int CHUNK = WT_F_FLAT_CHUNK;    // elements per item: one trip of the vector loop
+    static_assert(CHUNK == THREADS * UNROLL * 4, "one item = one trip");
 
     __device__ static void init(unsigned char*) {}
     __device__ static long long numel(const WtFJob& job) { return job.units; }
 
-    // op(key, valid) for every element of [x, x + len): all lanes call together, trip counts are CTA-uniform
+    // op(keys[16]) over every element of [x, x + len): all lanes call together, trip counts are CTA-uniform
     template <class Op>
     __device__ __forceinline__ static void span(const float* x, long long len, Op& op) {
         long long done = 0;
         if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
             const long long nvec = len >> 2;
             const float4* x4 = reinterpret_cast<const float4*>(x);
-            for (long long v0 = 0; v0 < nvec; v0 += (long long)THREADS * UNROLL) {
+            for (long long v0 = 0; v0 < nvec; v0 += THREADS * UNROLL) {
                 const long long v = v0 + threadIdx.x;
                 float4 r[UNROLL];
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u)
-                    r[u] = (v + (long long)u * THREADS < nvec) ? __ldcg(&x4[v + (long long)u * THREADS]) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (v + u * THREADS < nvec) r[u] = __ldcg(&x4[v + u * THREADS]);
+                unsigned int key[UNROLL * 4];
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u) {
-                    const bool ok = v + (long long)u * THREADS < nvec;
-                    op(abs_key(r[u].x), ok); op(abs_key(r[u].y), ok); op(abs_key(r[u].z), ok); op(abs_key(r[u].w), ok);
+                    const bool ok = v + u * THREADS < nvec;
+                    key[u * 4 + 0] = ok ? abs_key(r[u].x) : WT_F_NOKEY; key[u * 4 + 1] = ok ? abs_key(r[u].y) : WT_F_NOKEY;
+                    key[u * 4 + 2] = ok ? abs_key(r[u].z) : WT_F_NOKEY; key[u * 4 + 3] = ok ? abs_key(r[u].w) : WT_F_NOKEY;
                 }
+                op(key);
             }
             done = nvec << 2;
         }
         for (long long i0 = done; i0 < len; i0 += THREADS) {  // tail, or everything when x is not 16-byte aligned
-            const bool ok = i0 + threadIdx.x < len;
-            op(ok ? abs_key(__ldcg(&x[i0 + threadIdx.x])) : 0u, ok);
+            unsigned int key[1];
+            key[0] = (i0 + threadIdx.x < len) ? abs_key(__ldcg(&x[i0 + threadIdx.x])) : WT_F_NOKEY;
+            op(key);
         }
     }
 
     template <class Op>
-    __device__ __forceinline__ static void visit(const WtBank&, const WtFJob& job, int idx, bool sampled, unsigned char*, Op& op) {
+    __device__ __forceinline__ static void visit(const WtBank&, const WtFJob& job, int first, int count, bool sampled, unsigned char*,
+                                                 Op& op) {
         const int s = job.sample_shift;
         if (!sampled || s == 0) {
-            const long long base = (long long)idx * CHUNK;
+            const long long base = (long long)first * CHUNK;
             long long len = job.units - base;
-            if (len > CHUNK) len = CHUNK;
+            if (len > (long long)count * CHUNK) len = (long long)count * CHUNK;
             span(job.in + base, len, op);
             return;
         }
-        // sample item: a window of 4096 >> s elements out of every 4096-element tile, at an offset that rotates with the
-        // tile index; 2 << s tiles per item (one trip of the loop below)
+        // sample item = 16 tiles of 4096 elements: a window of 4096 >> s elements out of every tile, at an offset that
+        // rotates with the tile index
         const long long n_tiles = (job.units + 4095) >> 12;
-        const long long tile0 = (long long)idx * (2 << s);
+        const long long tile0 = (long long)first * 16;
         long long tiles = n_tiles - tile0;
-        if (tiles > (2 << s)) tiles = 2 << s;
+        if (tiles > (long long)count * 16) tiles = (long long)count * 16;
         const float* x = job.in + (tile0 << 12);
         const long long len = job.units - (tile0 << 12);
         const int wshift = 12 - s;      // log2(window elements)
@@ -79,29 +80,27 @@ struct FlatKind {
         const unsigned int wmask = (1u << s) - 1u, vmask = (1u << vshift) - 1u;
         const long long total = tiles << vshift;
         const bool aligned = (reinterpret_cast<uintptr_t>(x) & 15u) == 0;
-        for (long long v0 = 0; v0 < total; v0 += (long long)THREADS * UNROLL) {
-            float4 r[UNROLL];
-            bool ok[UNROLL];
+        for (long long v0 = 0; v0 < total; v0 += THREADS * UNROLL) {
+            unsigned int key[UNROLL * 4];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) {
-                const long long v = v0 + threadIdx.x + (long long)u * THREADS;
-                ok[u] = false;
-                r[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                const long long v = v0 + threadIdx.x + u * THREADS;
+                float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+                bool ok = false;
                 if (v < total) {
                     const long long tile = v >> vshift;
                     const unsigned int win = ((unsigned int)(tile0 + tile) * 5u + 3u) & wmask;
                     const long long off = (tile << 12) + ((long long)win << wshift) + (long long)(((unsigned int)v & vmask) << 2);
                     if (off + 4 <= len) {
-                        ok[u] = true;
-                        if (aligned) r[u] = __ldcg(reinterpret_cast<const float4*>(x + off));
-                        else r[u] = make_float4(__ldcg(x + off), __ldcg(x + off + 1), __ldcg(x + off + 2), __ldcg(x + off + 3));
+                        ok = true;
+                        if (aligned) r = __ldcg(reinterpret_cast<const float4*>(x + off));
+                        else r = make_float4(__ldcg(x + off), __ldcg(x + off + 1), __ldcg(x + off + 2), __ldcg(x + off + 3));
                     }
                 }
+                key[u * 4 + 0] = ok ? abs_key(r.x) : WT_F_NOKEY; key[u * 4 + 1] = ok ? abs_key(r.y) : WT_F_NOKEY;
+                key[u * 4 + 2] = ok ? abs_key(r.z) : WT_F_NOKEY; key[u * 4 + 3] = ok ? abs_key(r.w) : WT_F_NOKEY;
             }
-#pragma unroll
-            for (int u = 0; u < UNROLL; ++u) {
-                op(abs_key(r[u].x), ok[u]); op(abs_key(r[u].y), ok[u]); op(abs_key(r[u].z), ok[u]); op(abs_key(r[u].w), ok[u]);
-            }
+            op(key);
         }
     }
 
@@ -112,13 +111,13 @@ struct FlatKind {
         return o;
     }
 
-    // out = |x| < t ? 0 : x for the item; x may alias out (in-place callers), so no read-only path.  Layer-sharded runs
+    // out = |x| < t ? 0 : x for the items; x may alias out (in-place callers), so no read-only path.  Layer-sharded runs
     // store every value to the same offset of each peer's buffer too, straight from the registers.
-    __device__ __forceinline__ static void apply(const WtBank&, const WtFJob& job, int idx, float t, unsigned char*, unsigned int& zc,
-                                                 unsigned int& nzb) {
-        const long long base = (long long)idx * CHUNK;
+    __device__ __forceinline__ static void apply(const WtBank&, const WtFJob& job, int first, int count, float t, unsigned char*,
+                                                 unsigned int& zc, unsigned int& nzb) {
+        const long long base = (long long)first * CHUNK;
         long long len = job.units - base;
-        if (len > CHUNK) len = CHUNK;
+        if (len > (long long)count * CHUNK) len = (long long)count * CHUNK;
         const float* x = job.in + base;
         float* o = job.out + base;
         const int np = job.peers.n;
@@ -127,19 +126,20 @@ struct FlatKind {
             const long long nvec = len >> 2;
             const float4* x4 = reinterpret_cast<const float4*>(x);
             float4* o4 = reinterpret_cast<float4*>(o);
-            const long long v = threadIdx.x;
-            float4 r[UNROLL];
+            for (long long v = threadIdx.x; v < nvec; v += THREADS * UNROLL) {
+                float4 r[UNROLL];
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u)
-                if (v + (long long)u * THREADS < nvec) r[u] = __ldcg(&x4[v + (long long)u * THREADS]);
+                for (int u = 0; u < UNROLL; ++u)
+                    if (v + u * THREADS < nvec) r[u] = __ldcg(&x4[v + u * THREADS]);
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) {
-                if (v + (long long)u * THREADS < nvec) {
-                    r[u].x = prune_one(r[u].x, t, zc, nzb); r[u].y = prune_one(r[u].y, t, zc, nzb);
-                    r[u].z = prune_one(r[u].z, t, zc, nzb); r[u].w = prune_one(r[u].w, t, zc, nzb);
-                    __stcs(&o4[v + (long long)u * THREADS], r[u]);
-                    for (int q = 0; q < np; ++q)
-                        __stcs(reinterpret_cast<float4*>(reinterpret_cast<char*>(&o4[v + (long long)u * THREADS]) + job.peers.delta[q]), r[u]);
+                for (int u = 0; u < UNROLL; ++u) {
+                    if (v + u * THREADS < nvec) {
+                        r[u].x = prune_one(r[u].x, t, zc, nzb); r[u].y = prune_one(r[u].y, t, zc, nzb);
+                        r[u].z = prune_one(r[u].z, t, zc, nzb); r[u].w = prune_one(r[u].w, t, zc, nzb);
+                        __stcs(&o4[v + u * THREADS], r[u]);
+                        for (int q = 0; q < np; ++q)
+                            __stcs(reinterpret_cast<float4*>(reinterpret_cast<char*>(&o4[v + u * THREADS]) + job.peers.delta[q]), r[u]);
+                    }
                 }
             }
             done = nvec << 2;
@@ -158,18 +158,20 @@ struct SmallKind {
     static constexpr int HW = H * W;
     static constexpr int THREADS = WT_F_SMALL_THREADS(H, W);
     static constexpr int MIN_CTAS = (HW <= 9) ? 3 : 1;
-    static constexpr int TILE = THREADS;                    // planes per tile: one per thread
-    static constexpr int CHUNK_TILES = WT_F_SMALL_CHUNK_TILES;  // tiles per item
+    static constexpr int TILE = THREADS;   // planes per item: one per thread
     static constexpr int NCOEF_MAX = [] {
         int n = 0, h = H, w = W;
         for (int l = 0; l < WT_SMALL_MAX_LEVEL; ++l) { h = (h + 1) / 2; w = (w + 1) / 2; n += 3 * h * w; }
         return n + h * w;
     }();
 
+    // input ring: NST tiles in flight per CTA (the persistent CTA has few warps to hide the HBM latency of a tile behind;
+    // the ring does it: bytes in flight per SM = CTAs x (NST - 1) x tile bytes)
+    static constexpr int NST = (HW <= 9) ? 3 : 2;
     struct Smem {
-        float in[2][TILE * HW];
+        float in[NST][TILE * HW];
         float out[TILE * HW];
-        unsigned long long bar[2];
+        unsigned long long bar[NST];
         unsigned int phase;   // bit b: parity the next wait on bar[b] uses (thread 0 owns it, re-read after a CTA barrier)
     };
     static constexpr size_t SMEM_BYTES = sizeof(Smem);
@@ -177,8 +179,7 @@ struct SmallKind {
     __device__ static void init(unsigned char* ksm) {
         Smem& sm = *reinterpret_cast<Smem*>(ksm);
         if (threadIdx.x == 0) {
-            mbar_init(&sm.bar[0], 1);
-            mbar_init(&sm.bar[1], 1);
+            for (int b = 0; b < NST; ++b) mbar_init(&sm.bar[b], 1);
             mbar_fence_init();
             sm.phase = 0u;
         }
@@ -186,22 +187,14 @@ struct SmallKind {
     }
     __device__ static long long numel(const WtFJob& job) { return job.units * HW; }
 
-    // tile index of slot i of item idx
-    __device__ __forceinline__ static long long tile_of(const WtFJob& job, long long n_tiles, int idx, int i, bool sampled) {
-        const long long q = (long long)idx * CHUNK_TILES + i;
+    // tile of (sample) item q: the sample takes one tile out of every 2^s, at an offset that rotates with the group index
+    __device__ __forceinline__ static long long tile_of(const WtFJob& job, long long n_tiles, long long q, bool sampled) {
         const int s = job.sample_shift;
         if (!sampled || s == 0) return q;
-        // sampled: one tile out of every 2^s, at an offset that rotates with the group index
         const long long g0 = q << s;
         long long avail = n_tiles - g0;
         if (avail > (1LL << s)) avail = 1LL << s;
         return g0 + (long long)(((unsigned long long)q * 5ull + 3ull) % (unsigned long long)avail);
-    }
-    __device__ __forceinline__ static int tiles_in_item(const WtFJob& job, long long n_tiles, int idx, bool sampled) {
-        const int s = sampled ? job.sample_shift : 0;
-        const long long groups = (n_tiles + (1LL << s) - 1) >> s;
-        long long left = groups - (long long)idx * CHUNK_TILES;
-        return (int)(left > CHUNK_TILES ? CHUNK_TILES : (left < 0 ? 0 : left));
     }
 
     // starts the copy of `tile` into buffer b; returns true when it went out as a TMA bulk copy (CTA-uniform)
@@ -220,52 +213,63 @@ struct SmallKind {
         return tma_ok;
     }
 
-    // body(x, valid, cnt, p0) for every tile of the item, x = this thread's plane (zeros when !valid)
+    // body(x, valid, cnt, p0) for the tile of every item in [first, first + count), x = this thread's plane (zeros when
+    // !valid); the copies of the next NST - 1 tiles are in flight while body runs.  body must contain a CTA barrier after
+    // which no thread reads the input ring (x is in registers by then): it frees the buffer for the copy issued next.
     template <class Body>
-    __device__ __forceinline__ static void stream_tiles(const WtFJob& job, int idx, bool sampled, Smem& sm, Body& body) {
-        const long long n_tiles = (job.units + TILE - 1) / TILE;
-        const int count = tiles_in_item(job, n_tiles, idx, sampled);
+    __device__ __forceinline__ static void stream_tiles(const WtFJob& job, int first, int count, bool sampled, Smem& sm, Body& body) {
         if (count <= 0) return;
+        const long long n_tiles = (job.units + TILE - 1) / TILE;
         unsigned int phase = sm.phase;   // stable: thread 0 updates it only after the last CTA barrier of this function
-        bool ok_cur = issue(job, sm, tile_of(job, n_tiles, idx, 0, sampled), 0);
+        unsigned int tma = 0u;           // bit b: the tile in buffer b came by TMA (wait on its mbarrier)
+#pragma unroll
+        for (int p = 0; p < NST - 1; ++p)
+            if (p < count && issue(job, sm, tile_of(job, n_tiles, first + p, sampled), p)) tma |= 1u << p;
+        int b = 0, bn = NST - 1;   // buffer of tile i / of tile i + NST - 1
         for (int i = 0; i < count; ++i) {
-            const int b = i & 1;
-            bool ok_next = false;
-            if (i + 1 < count) ok_next = issue(job, sm, tile_of(job, n_tiles, idx, i + 1, sampled), b ^ 1);
-            if (ok_cur) {
+            if (i + NST - 1 < count) {   // buffer bn held tile i - 1: every thread passed the barrier in its body
+                if (issue(job, sm, tile_of(job, n_tiles, first + i + NST - 1, sampled), bn)) tma |= 1u << bn; else tma &= ~(1u << bn);
+            }
+            if (tma & (1u << b)) {
                 mbar_wait(&sm.bar[b], (phase >> b) & 1u);
                 phase ^= 1u << b;
             } else {
                 __syncthreads();
             }
-            const long long p0 = tile_of(job, n_tiles, idx, i, sampled) * TILE;
+            const long long p0 = tile_of(job, n_tiles, first + i, sampled) * TILE;
             const long long left = job.units - p0;
             const int cnt = left < TILE ? (int)left : TILE;
             const bool valid = (int)threadIdx.x < cnt;
             float x[HW];
 #pragma unroll
             for (int e = 0; e < HW; ++e) x[e] = valid ? sm.in[b][threadIdx.x * HW + e] : 0.0f;
-            body(x, valid, cnt, p0);   // contains the CTA barrier that frees buffer b for the copy after next
-            ok_cur = ok_next;
+            body(x, valid, cnt, p0);
+            b = (b + 1 == NST) ? 0 : b + 1;
+            bn = (bn + 1 == NST) ? 0 : bn + 1;
         }
         if (threadIdx.x == 0) sm.phase = phase;
         __syncthreads();
     }
 
     template <class Op>
-    __device__ __forceinline__ static void visit(const WtBank& bk, const WtFJob& job, int idx, bool sampled, unsigned char* ksm, Op& op) {
+    __device__ __forceinline__ static void visit(const WtBank& bk, const WtFJob& job, int first, int count, bool sampled,
+                                                 unsigned char* ksm, Op& op) {
         Smem& sm = *reinterpret_cast<Smem*>(ksm);
         const int level = job.level;
         auto body = [&](float (&x)[HW], bool valid, int, long long) {
             __syncthreads();   // every thread holds its plane: the buffer may be refilled
-            auto put = [&](int, float v) { op(abs_key(v), valid); };
+            unsigned int key[NCOEF_MAX];
+#pragma unroll
+            for (int i = 0; i < NCOEF_MAX; ++i) key[i] = WT_F_NOKEY;   // coefficients the job's level does not have
+            auto put = [&](int i, float v) { key[i] = valid ? abs_key(v) : WT_F_NOKEY; };
             wtsmall::SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::analyze(x, level, bk, put);
+            op(key);
         };
-        stream_tiles(job, idx, sampled, sm, body);
+        stream_tiles(job, first, count, sampled, sm, body);
     }
 
-    __device__ __forceinline__ static void apply(const WtBank& bk, const WtFJob& job, int idx, float t, unsigned char* ksm, unsigned int& zc,
-                                                 unsigned int& nzb) {
+    __device__ __forceinline__ static void apply(const WtBank& bk, const WtFJob& job, int first, int count, float t, unsigned char* ksm,
+                                                 unsigned int& zc, unsigned int& nzb) {
         Smem& sm = *reinterpret_cast<Smem*>(ksm);
         const int level = job.level;
         auto body = [&](float (&x)[HW], bool valid, int cnt, long long p0) {
@@ -308,8 +312,8 @@ struct SmallKind {
                 }
             }
         };
-        stream_tiles(job, idx, false, sm, body);
-        if (threadIdx.x == 0) bulk_wait_all();   // sm.out is free and the stores are performed before the item is counted done
+        stream_tiles(job, first, count, false, sm, body);
+        if (threadIdx.x == 0) bulk_wait_all();   // sm.out is free and the stores are performed before the items count as done
         __syncthreads();
     }
 };
