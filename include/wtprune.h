@@ -165,6 +165,17 @@ int wt_dwt_prune_f32(const WtLayerDesc* layers, int n_layers, int wavelet_id, in
 int wt_select_abs_f32(const float* x, int64_t n, int64_t implicit_zeros, int64_t k0, int64_t k1,
                       float* ab_out, void* stream);
 
+/* The same select for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  This entry point has NO counterpart in the reference.
+ * Its scratch (histograms, state, candidate keys: about 4.2 MB) is a fixed device array inside
+ * the library that every GPU loading the library holds until exit, so the call allocates nothing; n is limited to
+ * WT_SELECT_NOALLOC_MAX_N values (larger -> WT_E_INVALID, use wt_select_abs_f32).  All calls share the array: calls that
+ * overlap on the GPU (different streams or host threads without ordering between them) race -- serialise them.
+ * The results are written to ab_out in stream order; the call does not synchronise. */
+#define WT_SELECT_NOALLOC_MAX_N (1 << 22)
+int wt_select_abs_noalloc_f32(const float* x, int64_t n, int64_t implicit_zeros, int64_t k0, int64_t k1,
+                              float* ab_out, void* stream);
+
 /* wavedec2 + coeffs_to_array: x [batch][H][W] -> packed [batch][side_h][side_w] (padding = 0),
  * exactly the array dwt_pruning.py:69-70 hands to the thresholding. */
 int wt_wavedec2_packed_f32(const float* x, int64_t batch, int H, int W, int wavelet_id, int level,

@@ -27,7 +27,7 @@ EXPORTS = [
     'wt_packed_shape', 'wt_percentile_plan', 'wt_plan_create', 'wt_plan_destroy', 'wt_plan_device_bytes',
     'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device',
     'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers',
-    'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
+    'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_select_abs_noalloc_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
     'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32',
 ]
 
@@ -67,6 +67,7 @@ def lib():
     L.wt_plan_phase_times.argtypes = [vp, ci, P(fl), P(ci), ctypes.c_char_p, ci]
     L.wt_dwt_prune_f32.argtypes = [P(WtLayerDesc), ci, ci, ci, ci, dbl, ci, vp, P(i64), P(i64), P(fl)]
     L.wt_select_abs_f32.argtypes = [vp, i64, i64, i64, i64, vp, vp]
+    L.wt_select_abs_noalloc_f32.argtypes = [vp, i64, i64, i64, i64, vp, vp]
     L.wt_wavedec2_packed_f32.argtypes = [vp, i64, ci, ci, ci, ci, ci, vp, vp]
     L.wt_waverec2_packed_f32.argtypes = [vp, i64, ci, ci, ci, ci, ci, vp, vp]
     L.wt_min_weight_prune_f32.argtypes = [P(vp), P(i64), P(i64), ci, vp, P(i64)]
