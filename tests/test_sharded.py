@@ -104,3 +104,64 @@ def test_layout_and_lpt():
     lay8 = sharded.ShardLayout(shapes, 8)
     assert max(lay8.load) == 2359296 and abs(lay8.balance - 0.5917) < 0.01
     assert workloads.lpt_assignment([5, 5, 4, 3, 3], 2) == [0, 1, 0, 1, 1]
+
+
+class _FakePeerBuffer:
+    """stands in for sharded.PeerBuffer on CPU: a plain flat buffer, no peers to store into, gloo barrier"""
+
+    def __init__(self, layout, world):
+        self.flat = torch.zeros(world * layout.shard_elems, dtype=torch.float32)
+        self.deltas = [0] * (world - 1)
+        self.barriers = 0
+
+    def barrier(self):
+        self.barriers += 1
+        dist.barrier()
+
+
+def _fallback_worker(rank, world, port, out_q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from wavelettransforms_b200 import sharded
+        ws = _weights()
+        levels = [0] * len(ws)
+        base = _oracle_fn('haar', 50.0, True)
+        calls = []
+
+        def fn(xs, outs, levels, peer_deltas=None):
+            calls.append(peer_deltas is not None)
+            if peer_deltas is not None and rank == 1:      # this rank's layers are "off the mirrored paths"
+                raise NotImplementedError('layer runs on the generic tiled path')
+            return base(xs, outs, levels)
+        layout = sharded.ShardLayout([w.shape for w in ws], world)
+        pb = _FakePeerBuffer(layout, world)
+        pruned, counts, flat, _ = sharded.prune_sharded(ws, levels, fn, layout=layout, gather='peer_store', peer_buffer=pb)
+        out_q.put((rank, [p.clone().numpy() for p in pruned], counts, calls, pb.barriers))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_peer_store_falls_back_on_all_ranks_together(oracle_lib):
+    """one rank refusing the peer-store mode must not leave the others blocked in the barrier: every rank
+    agrees (all-reduce MIN) and all of them take the all-gather"""
+    from oracle import reference_flow as rf
+    world = 2
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_fallback_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = [rf.multi_resolution_analysis([w], 'haar', 0, 50.0, numpy_semantics='legacy_1_22', clamp_level=False)[0][0].numpy()
+            for w in _weights()]
+    for rank, pruned, counts, calls, barriers in results:
+        assert calls == [True, False]          # tried with peers, then every rank redid its shard without
+        assert barriers == 1                   # the entry barrier of a reused buffer only: no peer-store barrier after the fallback
+        for got, exp in zip(pruned, want):
+            assert np.array_equal(got.view(np.uint32), exp.view(np.uint32))

@@ -104,15 +104,15 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 
 // Calls op(float) on x[0..len): float4 loads, UNROLL of them in flight per thread.
 template <class Op>
-__device__ __forceinline__ void span_for_each(const float* __restrict__ x, long long len, Op op) {
+__device__ __forceinline__ void span_for_each(const float* x, long long len, Op op) {
     if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
         const long long nvec = len >> 2;
-        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
+        const float4* x4 = reinterpret_cast<const float4*>(x);
         for (long long v = threadIdx.x; v < nvec; v += (long long)T * UNROLL) {
             float4 r[UNROLL];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u)
-                if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
+                if (v + (long long)u * T < nvec) r[u] = __ldcg(&x4[v + (long long)u * T]);
             if (WT_SEL_PREFETCH) {
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u)
@@ -122,9 +122,9 @@ __device__ __forceinline__ void span_for_each(const float* __restrict__ x, long 
             for (int u = 0; u < UNROLL; ++u)
                 if (v + (long long)u * T < nvec) { op(r[u].x); op(r[u].y); op(r[u].z); op(r[u].w); }
         }
-        for (long long i = (nvec << 2) + threadIdx.x; i < len; i += T) op(__ldg(&x[i]));
+        for (long long i = (nvec << 2) + threadIdx.x; i < len; i += T) op(__ldcg(&x[i]));
     } else {
-        for (long long i = threadIdx.x; i < len; i += T) op(__ldg(&x[i]));
+        for (long long i = threadIdx.x; i < len; i += T) op(__ldcg(&x[i]));
     }
 }
 
@@ -468,7 +468,7 @@ __device__ __forceinline__ void warp_flush(const unsigned int* wbuf, unsigned in
     wcount = 0;
 }
 
-__device__ void hist2_compact_span(const float* __restrict__ x, long long len, unsigned int p0, unsigned int p1, bool two,
+__device__ void hist2_compact_span(const float* x, long long len, unsigned int p0, unsigned int p1, bool two,
                                    Shared& sh, unsigned int* g_cnt, unsigned int* __restrict__ cand, unsigned int cap) {
     unsigned int* h = sh.hist;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -485,7 +485,7 @@ __device__ void hist2_compact_span(const float* __restrict__ x, long long len, u
     long long done = 0;
     if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
         const long long nvec = len >> 2;
-        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
+        const float4* x4 = reinterpret_cast<const float4*>(x);
         for (long long v0 = 0; v0 < nvec; v0 += (long long)T * UNROLL) {  // CTA-uniform trip count
             const long long v = v0 + threadIdx.x;
             unsigned int key[UNROLL * 4];
@@ -493,7 +493,7 @@ __device__ void hist2_compact_span(const float* __restrict__ x, long long len, u
             float4 r[UNROLL];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u)
-                if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
+                if (v + (long long)u * T < nvec) r[u] = __ldcg(&x4[v + (long long)u * T]);
             if (WT_SEL_PREFETCH) {
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u)
@@ -529,7 +529,7 @@ __device__ void hist2_compact_span(const float* __restrict__ x, long long len, u
     }
     for (long long i0 = done; i0 < len; i0 += T) {  // tail, or everything when x is not 16-byte aligned
         const bool ok = i0 + threadIdx.x < len;
-        const unsigned int key = ok ? abs_key(__ldg(&x[i0 + threadIdx.x])) : 0u;
+        const unsigned int key = ok ? abs_key(__ldcg(&x[i0 + threadIdx.x])) : 0u;
         const bool hit = ok && matches(key);
         const unsigned int ballot = __ballot_sync(0xffffffffu, hit);
         if (ballot) {
@@ -569,7 +569,7 @@ __device__ __forceinline__ int cand_shift(unsigned int n_bins) { return 7 + (32 
 __device__ __forceinline__ int cand_shift2(int cs) { return cs > 11 ? cs - 11 : 0; }
 
 // S0 over one segment: 12-bit histogram of the sample windows of `tiles` tiles starting at job tile `tile0`
-__device__ __forceinline__ void sample_span(const float* __restrict__ x, long long len, int tile0, int tiles, int s,
+__device__ __forceinline__ void sample_span(const float* x, long long len, int tile0, int tiles, int s,
                                             unsigned int* h) {
     if (s == 0) {
         span_for_each(x, len, [h](float v) { atomicAdd(&h[abs_key(v) >> 19], 1u); });
@@ -593,8 +593,8 @@ __device__ __forceinline__ void sample_span(const float* __restrict__ x, long lo
                 const long long off = (tile << 12) + ((long long)win << wshift) + (long long)(((unsigned int)v & vmask) << 2);
                 if (off + 4 <= len) {
                     ok[u] = true;
-                    if (aligned) r[u] = __ldg(reinterpret_cast<const float4*>(x + off));
-                    else r[u] = make_float4(__ldg(x + off), __ldg(x + off + 1), __ldg(x + off + 2), __ldg(x + off + 3));
+                    if (aligned) r[u] = __ldcg(reinterpret_cast<const float4*>(x + off));
+                    else r[u] = make_float4(__ldcg(x + off), __ldcg(x + off + 1), __ldcg(x + off + 2), __ldcg(x + off + 3));
                 }
             }
         }
@@ -623,7 +623,7 @@ __device__ void phase_s0_sample(const WtSelArgs& a, Shared& sh, int t_begin, int
 
 // S1 over one span: count the keys below lo_key, compact the keys with key - lo_key < width into the job's
 // candidate list.  Same warp-private staging as hist2_compact_span, and nothing else: no shared-memory atomics.
-__device__ void range_compact_span(const float* __restrict__ x, long long len, unsigned int lo_key, unsigned int width,
+__device__ void range_compact_span(const float* x, long long len, unsigned int lo_key, unsigned int width,
                                    Shared& sh, unsigned long long* g_below, unsigned int* g_cnt,
                                    unsigned int* __restrict__ cand, unsigned int cap) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -633,7 +633,7 @@ __device__ void range_compact_span(const float* __restrict__ x, long long len, u
     long long done = 0;
     if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
         const long long nvec = len >> 2;
-        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(x);
+        const float4* x4 = reinterpret_cast<const float4*>(x);
         for (long long v0 = 0; v0 < nvec; v0 += (long long)T * UNROLL) {  // CTA-uniform trip count
             const long long v = v0 + threadIdx.x;
             unsigned int key[UNROLL * 4];
@@ -641,7 +641,7 @@ __device__ void range_compact_span(const float* __restrict__ x, long long len, u
             float4 r[UNROLL];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u)
-                if (v + (long long)u * T < nvec) r[u] = __ldg(&x4[v + (long long)u * T]);
+                if (v + (long long)u * T < nvec) r[u] = __ldcg(&x4[v + (long long)u * T]);
             if (WT_SEL_PREFETCH) {
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u)
@@ -681,7 +681,7 @@ __device__ void range_compact_span(const float* __restrict__ x, long long len, u
     }
     for (long long i0 = done; i0 < len; i0 += T) {  // tail, or everything when x is not 16-byte aligned
         const bool ok = i0 + threadIdx.x < len;
-        const unsigned int key = ok ? abs_key(__ldg(&x[i0 + threadIdx.x])) : 0u;
+        const unsigned int key = ok ? abs_key(__ldcg(&x[i0 + threadIdx.x])) : 0u;
         nbelow += ok && key < lo_key;
         const bool hit = ok && (key - lo_key < width);
         const unsigned int ballot = __ballot_sync(0xffffffffu, hit);
@@ -1094,7 +1094,12 @@ __device__ void phase4_apply(const WtSelArgs& a, Shared& sh, int t_begin, int t_
         for (long long i = done + threadIdx.x; i < len; i += T) o[i] = apply_one(x[i], t, zc, nzb);
         // layer-sharded run: the span just written (every thread re-reads exactly what it stored, still in L2) also goes
         // to the same slot of every peer's buffer; out of line so the single-GPU loop keeps its registers
-        if (__ldg(&a.jobs[j].peers.n)) mirror_span(o, len, &a.jobs[j].peers);
+        // (the apply loop may have taken its scalar path -- x misaligned -- while mirror_span vectorises on o's alignment
+        // alone: then a thread re-reads elements other threads stored, so the CTA meets here first)
+        if (__ldg(&a.jobs[j].peers.n)) {
+            __syncthreads();
+            mirror_span(o, len, &a.jobs[j].peers);
+        }
         // every element of the span is visited exactly once: thread 0 contributes the span length
         block_add3(a.counts + (size_t)job.layer * 4, zc, nzb, threadIdx.x == 0 ? (unsigned int)len : 0u, sh.hist);
         acc.end(14);

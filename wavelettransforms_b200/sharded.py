@@ -105,7 +105,12 @@ def prune_sharded(weights: List[torch.Tensor], levels: Sequence[int], prune_fn: 
     dev = weights[0].device if weights else torch.device('cpu')
     peer = gather == 'peer_store' and world > 1
     if peer:
-        peer_buffer = peer_buffer or PeerBuffer(layout, dev, group)
+        if peer_buffer is None:
+            peer_buffer = PeerBuffer(layout, dev, group)
+        else:
+            # a reused buffer: a fast rank must not store over NVLink into a peer that is still reading the previous
+            # call's result (PeerBuffer.__init__ ends with the same barrier for a fresh one)
+            peer_buffer.barrier()
         flat = peer_buffer.flat
     else:
         flat = torch.zeros(world * layout.shard_elems, dtype=torch.float32, device=dev)
@@ -114,11 +119,26 @@ def prune_sharded(weights: List[torch.Tensor], levels: Sequence[int], prune_fn: 
     xs = [weights[i].contiguous() for i in mine]
     outs = [layout.view(flat, i) for i in mine]          # kernels store straight into the send slot
     counts_local = torch.zeros((len(weights), 4), dtype=torch.int64)
+    my_levels = [int(levels[i]) for i in mine]
+    c = None
+    if peer:
+        # A rank whose layers the mirroring kernels do not cover (generic tiled path ...) gets NotImplementedError from
+        # Plan.set_peers BEFORE anything is enqueued.  A rank-local exception cannot be recovered collectively, so the
+        # ranks agree first: all of them store to their peers, or all of them fall back to the NCCL all-gather together.
+        ok = 1
+        try:
+            if mine:
+                c = prune_fn(xs, outs, my_levels, peer_deltas=peer_buffer.deltas)
+        except NotImplementedError:
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if not int(flag.item()):
+            peer = False
+            c = None       # ranks that did run redo their shard without mirroring: same values, the gather overwrites the rest
+    if c is None and mine:
+        c = prune_fn(xs, outs, my_levels)
     if mine:
-        if peer:
-            c = prune_fn(xs, outs, [int(levels[i]) for i in mine], peer_deltas=peer_buffer.deltas)
-        else:
-            c = prune_fn(xs, outs, [int(levels[i]) for i in mine])
         counts_local[mine] = torch.from_numpy(np.asarray(c, dtype=np.int64))
     counts = counts_local.to(dev)
     if peer:
