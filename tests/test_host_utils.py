@@ -44,3 +44,27 @@ def test_background_save_snapshots_then_writes(tmp_path, monkeypatch):
     monkeypatch.setattr(config, 'async_save', False)
     assert utils.save_model(m, str(tmp_path / 'fg')) is None
     assert torch.equal(torch.load(os.path.join(tmp_path, 'fg', 'pytorch_model.bin'))['weight'], torch.zeros_like(want))
+
+
+def test_get_layer_prefix_and_print_helpers(capsys):
+    """ResNet/utils.py:220-223 (class-name prefix), :165-206 (print helpers)"""
+    m = torch.nn.Sequential(torch.nn.Conv2d(1, 2, 3), torch.nn.Sequential(torch.nn.Conv2d(2, 2, 1)))
+    assert utils.get_layer(m, 'ResNetForImageClassification.1.0') is m[1][0]
+    assert utils.get_layer(m, '1..0') is m[1][0]
+    utils.print_model_summary(m)
+    utils.print_model_structure(m)
+    out = capsys.readouterr().out
+    assert 'Total Params: 20' in out and '  0 - Conv2d' in out
+
+
+def test_load_model_reads_config_path_and_rejects_files(tmp_path):
+    """ResNet/utils.py:17-22"""
+    import pytest
+    from transformers import ResNetConfig, ResNetForImageClassification
+    cfg = ResNetConfig(layer_type='basic', embedding_size=8, hidden_sizes=[8, 16], depths=[1, 1], num_labels=3)
+    ResNetForImageClassification(cfg).save_pretrained(str(tmp_path / 'm'))
+    model = utils.load_model(str(tmp_path / 'm'), str(tmp_path / 'm' / 'config.json'))
+    assert model.config.hidden_sizes == [8, 16]
+    assert utils.load_model(str(tmp_path / 'm')).config.num_labels == 3
+    with pytest.raises(ValueError, match='not a valid directory'):
+        utils.load_model(str(tmp_path / 'm' / 'config.json'), None)

@@ -35,6 +35,30 @@ def test_doc_known_answers():
     np.testing.assert_allclose(r, 1.0, rtol=1e-6)
 
 
+def test_periodization_known_answers_by_hand():
+    """Closed forms of pywt.dwt(x, w, mode='periodization') for x = 1..N worked out by hand from the published filters
+    (haar: s = 1/sqrt 2; db2: rec_lo = [(1+r), (3+r), (3-r), (1-r)] / (4 sqrt 2), r = sqrt 3): the mode of record of the
+    reference (dwt_pruning.py:35), even / odd lengths, the wrap on both ends.  Pins alignment and the odd-length rule
+    (repeat the last sample) independently of the oracle's own index arithmetic."""
+    s, r, q = 1.0 / np.sqrt(2.0), np.sqrt(3.0), 4.0 * np.sqrt(2.0)
+    cases = {
+        ('haar', 4): ([3 * s, 7 * s], [-s, -s]),
+        ('haar', 6): ([3 * s, 7 * s, 11 * s], [-s, -s, -s]),
+        ('haar', 7): ([3 * s, 7 * s, 11 * s, 14 * s], [-s, -s, -s, 0.0]),
+        ('db2', 4): ([2 * np.sqrt(2.0), 3 * np.sqrt(2.0)], [(1 - r) / np.sqrt(2.0), (1 + r) / np.sqrt(2.0)]),
+        ('db2', 6): ([(18 + 2 * r) / q, (28 - 4 * r) / q, (38 + 2 * r) / q], [(6 - 6 * r) / q, 0.0, (6 + 6 * r) / q]),
+        ('db2', 7): ([(19 + 3 * r) / q, (28 - 4 * r) / q, (44 - 4 * r) / q, (49 + 5 * r) / q],
+                     [(7 - 7 * r) / q, 0.0, 0.0, (5 + 7 * r) / q]),
+    }
+    for (w, n), (ca_want, cd_want) in cases.items():
+        ca, cd = o.dwt(np.arange(1, n + 1, dtype=np.float32), w, 'periodization')
+        np.testing.assert_allclose(ca, ca_want, rtol=2e-6, atol=2e-6, err_msg=f'{w} N={n} cA')
+        np.testing.assert_allclose(cd, cd_want, rtol=2e-6, atol=2e-6, err_msg=f'{w} N={n} cD')
+        # and back (idwt of an odd-length signal returns N + 1 samples, the last one repeated)
+        back = o.idwt(ca, cd, w, 'periodization')
+        np.testing.assert_allclose(back[:n], np.arange(1, n + 1), rtol=1e-5, atol=1e-5)
+
+
 @pytest.mark.parametrize('wavelet', WAVELETS)
 def test_n1_periodization(wavelet):
     # N=1: cA = sqrt(2) x, cD ~ 0 for any wavelet whose dec_lo sums to sqrt(2)

@@ -16,9 +16,15 @@ OUTPUT_ROOT = os.environ.get('WT_OUTPUT_DIR', 'SavedModels')
 
 
 def load_model(model_path, config_path=None):
-    """utils.py:6-25 -- HF AutoModelForImageClassification on the CPU"""
-    from transformers import AutoModelForImageClassification
-    return AutoModelForImageClassification.from_pretrained(model_path)
+    """utils.py:6-25 -- HF AutoModelForImageClassification on the CPU, configuration read from `config_path`
+    (the model directory itself when omitted); ValueError when `model_path` is not a directory (:17-22)"""
+    from transformers import AutoConfig, AutoModelForImageClassification
+    if not os.path.isdir(model_path):
+        raise ValueError(f"Provided model path {model_path} is not a valid directory.")
+    config = AutoConfig.from_pretrained(config_path if config_path else model_path)
+    model = AutoModelForImageClassification.from_pretrained(model_path, config=config)
+    print("Pre-trained model loaded successfully.")
+    return model
 
 
 _save_pool = None
@@ -126,10 +132,41 @@ def check_and_set_pruned_instance_path(pruned_instance):
     return path
 
 
+def print_model_summary(model):
+    """utils.py:165-190 -- weight shapes and parameter counts of the model's direct children"""
+    total_params = 0
+    print("Model Summary:")
+    print("Layer Name" + "\t" * 7 + "Output Shape" + "\t" * 5 + "Param #")
+    print("=" * 100)
+    for name, module in model.named_children():
+        if hasattr(module, 'weight') and hasattr(module.weight, 'size'):
+            print(f"{name}\t{module.weight.size()}\t{module.weight.numel()}")
+            total_params += module.weight.numel()
+            if hasattr(module, 'bias') and hasattr(module.bias, 'size'):
+                total_params += module.bias.numel()
+    print("=" * 100)
+    print(f"Total Params: {total_params}")
+
+
+def print_model_structure(model, depth=0):
+    """utils.py:193-206 -- the module tree, two spaces per level"""
+    indent = " " * (depth * 2)
+    for name, module in model.named_children():
+        print(f"{indent}{name} - {module.__class__.__name__}")
+        if list(module.children()):
+            print_model_structure(module, depth + 1)
+
+
 def get_layer(model, layer_name):
-    """utils.py:209-238 -- dotted lookup; None when a component is missing"""
+    """utils.py:209-238 -- dotted lookup; None when a component is missing; a leading
+    'ResNetForImageClassification.' (:220-223) and empty components are ignored"""
+    prefix = 'ResNetForImageClassification.'
+    if layer_name.startswith(prefix):
+        layer_name = layer_name[len(prefix):]
     cur = model
     for part in layer_name.split('.'):
+        if not part:
+            continue
         if part.isdigit() and hasattr(cur, '__getitem__'):
             try:
                 cur = cur[int(part)]
