@@ -6,9 +6,11 @@
 //   wt_count_f32            : torch.count_nonzero and calculate_sparsity's |p| < 1e-6 count
 //                             (testing_suite/eval_model.py:7-20)
 //
-// Min-weight reuses the exact radix select of wt_select.cu for the k-th smallest magnitude `a`,
-// then zeroes every |w| < a plus the first (k - #less) entries equal to a in flat-index order
-// (torch.topk leaves tie order unspecified; lowest index first is this library's documented rule).
+// Min-weight is ONE launch of the select kernel of wt_select.cu in the common case: ranks k-1 and k with an interpolation
+// weight of 1 make its fused level-0 apply zero every |w| < sorted[k], which are exactly the k smallest whenever
+// a = sorted[k-1] < b = sorted[k].  Only when a == b (a tie across the boundary) the three small kernels below run for
+// that tensor: they zero the first (k - #less) entries equal to a in flat-index order (torch.topk leaves tie order
+// unspecified; lowest index first is this library's documented rule).  Otherwise they return at once.
 #include <algorithm>
 
 #include "wt_common.cuh"
@@ -24,6 +26,11 @@ struct MwJob {
     int sel_job;  // index into the select state
     int pad;
 };
+
+// does tensor `job` need the tie passes?  (k = 0: nothing to zero; a = 0: the ties are zeros already)
+__device__ __forceinline__ bool mw_tie(const MwJob& job, const WtSelState& st) {
+    return job.k > 0 && st.a == st.b && st.a > 0.0f;
+}
 
 __device__ __forceinline__ int find_mw_job(const MwJob* __restrict__ jobs, int n_jobs, int tile) {
     int lo = 0, hi = n_jobs - 1;
@@ -43,6 +50,7 @@ mw_count_kernel(const MwJob* __restrict__ jobs, int n_jobs, const WtSelState* __
     const int j = find_mw_job(jobs, n_jobs, tile);
     const MwJob job = jobs[j];
     const float a = state[job.sel_job].a;
+    if (!mw_tie(job, state[job.sel_job])) return;   // the select's own apply already zeroed exactly k entries
     const long long base = (long long)(tile - job.tile_begin) * WT_SEL_TILE;
     const int cnt = (int)min((long long)WT_SEL_TILE, job.n - base);
     unsigned int eq = 0, less = 0;
@@ -68,11 +76,12 @@ mw_count_kernel(const MwJob* __restrict__ jobs, int n_jobs, const WtSelState* __
 
 // pass B: exclusive scan of tile_eq within each job (one CTA per job; ties are rare, tiles few)
 __global__ void __launch_bounds__(256)
-mw_scan_kernel(const MwJob* __restrict__ jobs, const unsigned int* __restrict__ tile_eq,
+mw_scan_kernel(const MwJob* __restrict__ jobs, const WtSelState* __restrict__ state, const unsigned int* __restrict__ tile_eq,
                unsigned long long* __restrict__ tile_eq_prefix) {
     __shared__ unsigned long long s_warp[8];
     __shared__ unsigned long long s_carry;
     const MwJob job = jobs[blockIdx.x];
+    if (!mw_tie(job, state[job.sel_job])) return;
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
     for (int t0 = 0; t0 < job.n_tiles; t0 += 256) {
@@ -107,6 +116,7 @@ mw_apply_kernel(const MwJob* __restrict__ jobs, int n_jobs, const WtSelState* __
     const int j = find_mw_job(jobs, n_jobs, tile);
     const MwJob job = jobs[j];
     const float a = state[job.sel_job].a;
+    if (!mw_tie(job, state[job.sel_job])) return;
     const long long base = (long long)(tile - job.tile_begin) * WT_SEL_TILE;
     const int cnt = (int)min((long long)WT_SEL_TILE, job.n - base);
     const bool none = (job.k <= 0), all = (job.k >= job.n);
@@ -156,6 +166,14 @@ mw_apply_kernel(const MwJob* __restrict__ jobs, int n_jobs, const WtSelState* __
         for (int w = 0; w < MW_THREADS / 32; ++w) t += s_nz[w];
         if (t) atomicAdd(&nonzero_out[j], t);
     }
+}
+
+// count_nonzero per tensor: from the tie passes where they ran, else from the select's apply
+__global__ void mw_finalize_kernel(const MwJob* __restrict__ jobs, int n_jobs, const WtSelState* __restrict__ state,
+                                   const long long* __restrict__ counts, unsigned long long* __restrict__ nonzero_out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_jobs) return;
+    if (!mw_tie(jobs[j], state[jobs[j].sel_job])) nonzero_out[j] = (unsigned long long)counts[(size_t)jobs[j].sel_job * 4 + 1];
 }
 
 __global__ void __launch_bounds__(256) scatter_zero_kernel(float* __restrict__ w, long long n,
@@ -246,9 +264,12 @@ extern "C" int wt_min_weight_prune_f32(float* const* w, const int64_t* n, const 
         m.w = w[i]; m.n = n[i]; m.k = k[i]; m.tile_begin = tiles; m.n_tiles = (int)nt; m.sel_job = (int)sjobs.size(); m.pad = 0;
         WtSelJob s;
         memset(&s, 0, sizeof(s));
-        s.x = w[i]; s.out = nullptr; s.n = n[i]; s.zeros = 0;
-        s.k0 = s.k1 = std::min<long long>(std::max<long long>(k[i] - 1, 0), n[i] - 1);
-        s.gamma = 0.0; s.lerp_mode = WT_LERP_NEP50; s.tile_begin = tiles; s.n_tiles = (int)nt; s.layer = (int)sjobs.size();
+        // ranks k-1 and k, interpolation weight 1: threshold = sorted[k], the apply zeroes |w| < sorted[k] in place
+        // (k = 0: threshold = the minimum, nothing is below it)
+        s.x = w[i]; s.out = w[i]; s.n = n[i]; s.zeros = 0;
+        s.k0 = std::min<long long>(std::max<long long>(k[i] - 1, 0), n[i] - 1);
+        s.k1 = std::min<long long>(k[i], n[i] - 1);
+        s.gamma = k[i] > 0 ? 1.0 : 0.0; s.lerp_mode = WT_LERP_NEP50; s.tile_begin = tiles; s.n_tiles = (int)nt; s.layer = (int)sjobs.size();
         s.cand_cap = wt_select_cand_cap(n[i]);
         s.sample_shift = wt_select_sample_shift(n[i]);
         tiles += (int)nt;
@@ -292,7 +313,7 @@ extern "C" int wt_min_weight_prune_f32(float* const* w, const int64_t* n, const 
         memset(&a, 0, sizeof(a));
         wt_select_bind(&a, dev + o_scr, nj);
         a.jobs = reinterpret_cast<WtSelJob*>(dev + o_sj);
-        a.n_jobs = nj; a.n_tiles = tiles; a.any_apply = 0;
+        a.n_jobs = nj; a.n_tiles = tiles; a.any_apply = 1;
         a.thresholds = reinterpret_cast<float*>(dev + o_thr);
         a.counts = reinterpret_cast<long long*>(dev + o_cnt);
         rc = wt_select_launch(a, stream);
@@ -303,8 +324,9 @@ extern "C" int wt_min_weight_prune_f32(float* const* w, const int64_t* n, const 
         unsigned long long* less = reinterpret_cast<unsigned long long*>(dev + o_less);
         unsigned long long* dnz = reinterpret_cast<unsigned long long*>(dev + o_nz);
         mw_count_kernel<<<tiles, MW_THREADS, 0, stream>>>(dj, nj, a.state, teq, less);
-        mw_scan_kernel<<<nj, 256, 0, stream>>>(dj, teq, tpx);
+        mw_scan_kernel<<<nj, 256, 0, stream>>>(dj, a.state, teq, tpx);
         mw_apply_kernel<<<tiles, MW_THREADS, 0, stream>>>(dj, nj, a.state, tpx, less, dnz);
+        mw_finalize_kernel<<<(nj + 127) / 128, 128, 0, stream>>>(dj, nj, a.state, a.counts, dnz);
         MW_TRY(cudaGetLastError());
         MW_TRY(cudaMemcpyAsync(nz.data(), dnz, nj * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
         MW_TRY(cudaStreamSynchronize(stream));

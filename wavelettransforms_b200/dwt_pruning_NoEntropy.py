@@ -63,12 +63,33 @@ def wavelet_pruning(model, wavelet: str, level: int, threshold: float, csv_path:
     total_pruned_count = 0
     total_non_zero_params = 0
     try:
-        for name, module in model.named_modules():
-            if isinstance(module, nn.Conv2d):
-                numel, non_zero, pruned = prune_layer_weights(module, wavelet, level, threshold)
-                total_pruned_count += pruned
-                total_non_zero_params += non_zero
-                log_pruning_details(writer, guid, wavelet, level, threshold, 'selective', numel, non_zero, pruned, name)
+        # ONE plan for the whole model (the layers are independent: dwt_pruning_NoEntropy.py:79-89 handles them one by
+        # one); per-layer bookkeeping afterwards from the counts the kernels left
+        _lib.wavelet_lookup(wavelet)
+        if level < 0:
+            raise ValueError(f"Level value of {level} is too low . Minimum level is 0.")
+        layers = [(name, module) for name, module in model.named_modules() if isinstance(module, nn.Conv2d)]
+        params = [[p for p in module.parameters()] for _, module in layers]
+        flat_params = [p for ps in params for p in ps]
+        if flat_params:
+            dev = engine.cuda_device()
+            xs = [engine.to_device_f32(p, dev) for p in flat_params]
+            levels = [level if p.ndim >= 2 else 0 for p in flat_params]
+            res = engine.prune_device_tensors(xs, levels, wavelet, 'periodization', _lib.THRESHOLD_ABSOLUTE, float(threshold))
+        at = 0
+        for (name, module), ps in zip(layers, params):
+            numel = sum(p.numel() for p in ps)
+            sl = slice(at, at + len(ps))
+            non_zero = int(res.nonzero_before[sl].sum()) if ps else 0
+            pruned = int((res.nonzero_before[sl] - res.counts[sl, 1]).sum()) if ps else 0
+            with torch.no_grad():
+                for param, o in zip(ps, res.outputs[sl] if ps else []):
+                    if param.requires_grad:
+                        param.copy_(o.view(param.shape).to(param.device))
+            at += len(ps)
+            total_pruned_count += pruned
+            total_non_zero_params += non_zero
+            log_pruning_details(writer, guid, wavelet, level, threshold, 'selective', numel, non_zero, pruned, name)
     finally:
         log_file.close()
     save_model(model, selective_pruned_dir)

@@ -158,6 +158,26 @@ def scatter_zero_(w: torch.Tensor, idx: torch.Tensor) -> int:
     return int(out.item())
 
 
+def scatter_zero_group_(ws: List[torch.Tensor], idxs: List[torch.Tensor]) -> List[int]:
+    """scatter_zero_ for a whole model with ONE host synchronisation: every layer's scatter + count is enqueued
+    back to back (the counts land in one device tensor), then a single D2H brings all of them back.  The reference
+    syncs once per layer (random_pruning.py:57-58)."""
+    if not ws:
+        return []
+    dev = ws[0].device
+    counts = torch.empty(len(ws), dtype=torch.int64, device=dev)
+    L, s = _lib.lib(), _stream_ptr()
+    keep = []
+    for i, (w, idx) in enumerate(zip(ws, idxs)):
+        _check_fp32(w)
+        if not w.is_contiguous():
+            raise ValueError('scatter_zero_group_ needs contiguous tensors')
+        idx = idx.to(device=dev, dtype=torch.int64).contiguous()
+        keep.append(idx)
+        _lib.check(L.wt_scatter_zero_f32(w.data_ptr(), w.numel(), idx.data_ptr(), idx.numel(), counts[i:].data_ptr(), s))
+    return [int(v) for v in counts.cpu().tolist()]
+
+
 def count_nonzero_and_below(x: torch.Tensor, eps: float = 1e-6) -> Tuple[int, int]:
     """(torch.count_nonzero(x), (|x| < eps).sum())  -- calculate_sparsity, testing_suite/eval_model.py:7-20"""
     _check_fp32(x)
