@@ -46,26 +46,41 @@ METRIC = 'pruned weight elems/s (DWT fwd+threshold+inv)'
 UNIT = 'elems/s'
 BYTES_PER_ELEM = 8  # read the fp32 weight once + write the pruned fp32 weight once
 
-# name -> (arch, wavelet, level, percentile, clamp_level)
-WORKLOADS = {
-    # north_star target: all ResNet-18 conv layers through a level-5 bior decomposition.  Unclamped =
-    # the decomposition dwt_pruning_NoEntropy.py:41 runs (3x3 planes: 3->2->1->1->1->1), with the
-    # percentile threshold of dwt_pruning.py:25-32.  The real transform on every layer.
-    'resnet18_bior4.4_L5_p50_unclamped': ('resnet18', 'bior4.4', 5, 50.0, False),
-    # the same call through dwt_pruning.py's clamp (:64-65): dec_len 10 => level 0 on every ResNet
-    # plane => select + zero, no transform.  What the reference's stored runs executed.
-    'resnet18_bior4.4_L5_p50_clamped': ('resnet18', 'bior4.4', 5, 50.0, True),
-    # deepest real transform the clamped reference ever runs: haar, 3x3 -> L1, 7x7 -> L2
-    'resnet18_haar_L5_p50_clamped': ('resnet18', 'haar', 5, 50.0, True),
-    'resnet18_bior2.2_L3_p50_unclamped': ('resnet18', 'bior2.2', 3, 50.0, False),
-    # BASELINE.json configs[0]: the reference's own CPU-runnable case (dec_len 6 => clamps to level 0)
-    'resnet18_bior1.3_L1_p50_clamped': ('resnet18', 'bior1.3', 1, 50.0, True),
-    'resnet50_bior2.2_L3_p50_unclamped': ('resnet50', 'bior2.2', 3, 50.0, False),
-    'resnet152_bior2.2_L3_p50_unclamped': ('resnet152', 'bior2.2', 3, 50.0, False),
-}
-DEFAULT_WORKLOAD = 'resnet18_bior4.4_L5_p50_unclamped'
-VARIANTS = ['resnet18_bior4.4_L5_p50_clamped', 'resnet18_haar_L5_p50_clamped', 'resnet18_bior2.2_L3_p50_unclamped',
-            'resnet18_bior1.3_L1_p50_clamped']
+# Workload names: <arch>_<wavelet>_L<level>_p<percentile>_<clamped|unclamped>
+#   unclamped = the decomposition dwt_pruning_NoEntropy.py:41 runs (3x3 planes: 3->2->1->1->1->1) with the percentile
+#               threshold of dwt_pruning.py:25-32: the real transform on every layer (the north-star target);
+#   clamped   = the same call through dwt_pruning.py's clamp (:64-65): every wavelet with dec_len >= 6 gets level 0 on
+#               ResNet planes => select + zero, no transform -- what the reference's stored runs executed.
+import re
+
+
+class Workloads(dict):
+    """name -> (arch, wavelet, level, percentile, clamp_level); any well-formed name is accepted"""
+    PAT = re.compile(r'^(resnet18|resnet50|resnet152)_([a-z0-9.]+)_L(\d+)_p([0-9.]+)_(clamped|unclamped)$')
+
+    def __missing__(self, name):
+        m = self.PAT.match(name)
+        if not m:
+            raise KeyError(name)
+        v = (m.group(1), m.group(2), int(m.group(3)), float(m.group(4)), m.group(5) == 'clamped')
+        self[name] = v
+        return v
+
+    def __contains__(self, name):
+        return bool(self.PAT.match(str(name)))
+
+
+WORKLOADS = Workloads()
+# Headline: all ResNet-18 conv layers through a level-5 bior4.4 decomposition at the 90th percentile.  (Round 1 quoted
+# p = 50, where the threshold of this decomposition is 3.5e-19 -- 24 of the 49 packed cells of a 3x3 plane are padding
+# zeros and the level-3..5 details are rounding noise -- and NOTHING is pruned; at p = 90 the threshold is ~0.02, 49 % of
+# the weights go, and the select works on long candidate lists.  p = 50 stays as a variant.)
+DEFAULT_WORKLOAD = 'resnet18_bior4.4_L5_p90_unclamped'
+VARIANTS = ['resnet18_bior4.4_L5_p90_clamped',      # what dwt_pruning.py itself executes for this call: level 0
+            'resnet18_haar_L5_p90_clamped',         # deepest real transform the clamped reference runs: 3x3 -> L1, 7x7 -> L2
+            'resnet18_bior2.2_L3_p90_unclamped',
+            'resnet18_bior4.4_L5_p50_unclamped',    # round 1's headline (prunes nothing)
+            'resnet18_bior1.3_L1_p50_clamped']      # BASELINE.json configs[0]: the reference's own CPU-runnable case
 NUMPY_SEMANTICS = 'legacy_1_22'  # the reference's pin (requirements.txt:2)
 
 
@@ -75,13 +90,44 @@ def parse_args():
     ap.add_argument('--steps', type=int, default=200)
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--workload', default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument('--workload', default=DEFAULT_WORKLOAD)
     ap.add_argument('--replicas', type=int, default=8, help='rotating model replicas per GPU (defeats L2 reuse)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-variants', action='store_true')
-    ap.add_argument('--sharded-workload', default='resnet152_bior2.2_L3_p50_unclamped', choices=sorted(WORKLOADS))
+    ap.add_argument('--sharded-workload', default='resnet152_bior2.2_L3_p90_unclamped')
+    ap.add_argument('--no-sweep', action='store_true')
     ap.add_argument('--cpu-sample-seconds', type=float, default=15.0)
     return ap.parse_args()
+
+
+def base_config(name, replicas=8):
+    """the `config` object of BOTH arms (ours and --impl reference): identical keys and values, so the driver can see that
+    the two lines describe the same workload"""
+    from wavelettransforms_b200 import workloads
+    arch, wavelet, level, pct, clamp = WORKLOADS[name]
+    census = workloads.conv_census(arch)
+    elems = sum(int(np.prod(s)) for _, s in census)
+    levels = host_effective_levels(census, wavelet, level, clamp)
+    return {'workload': name, 'layers': len(census), 'elems_per_step_per_gpu': elems, 'levels': sorted(set(levels)),
+            'mode': 'periodization', 'numpy_semantics': NUMPY_SEMANTICS,
+            'l2_policy': f'GPU arm: {replicas} rotating replicas of the model per GPU, inputs+outputs '
+                         f'{replicas * 2 * elems * 4 / 1e6:.0f} MB > 126 MB L2, so no step finds its input in L2; the CPU arm has none'}
+
+
+# dec_len of the 17 flag wavelets (SURVEY A.1): the clamp needs no GPU library
+DEC_LEN = {'haar': 2, 'db1': 2, 'db2': 4, 'sym2': 4, 'db4': 8, 'sym4': 8, 'db6': 12, 'sym6': 12, 'coif1': 6, 'coif2': 12, 'coif3': 18,
+           'bior1.3': 6, 'rbio1.3': 6, 'bior2.2': 6, 'rbio2.2': 6, 'bior4.4': 10, 'rbio4.4': 10}
+
+
+def host_effective_levels(census, wavelet, level, clamp):
+    """effective_levels without the CUDA library (pywt.dwt_max_level)"""
+    F = DEC_LEN[wavelet]
+    out = []
+    for _, shp in census:
+        n = min(shp[-2:])
+        mx = 0 if (F <= 1 or n < F - 1) else int(np.floor(np.log2(n // (F - 1))))
+        out.append(min(level, mx) if clamp else level)
+    return out
 
 
 def dist_env():
@@ -206,6 +252,13 @@ class DeviceWorkload:
     def step(self, i, stream):
         self.plans[i % len(self.plans)].run(stream)
 
+    def pruned_fraction(self):
+        """zeros in the output of one step / elements (a headline that prunes nothing is not a headline)"""
+        stream = int(torch.cuda.current_stream().cuda_stream)
+        self.plans[0].run(stream)
+        counts, _, _ = self.plans[0].results(stream)
+        return float(counts[:, 2].sum()) / float(self.elems)
+
     def close(self):
         for p in self.plans:
             p.close()
@@ -285,6 +338,37 @@ def phase_elems(wl, phase):
     return 0
 
 
+def phase_bytes(wl, phase):
+    """bytes the launch group `phase` has to move for its own job in this pipeline (what it reads once + what it writes
+    once): the denominator of its own roofline fraction.  (The whole path's algorithmic bytes are 8 B per weight.)"""
+    from wavelettransforms_b200 import _lib
+    def per_layer(sel):
+        w = c = 0
+        for (_, s), lv in zip(wl.census, wl.levels):
+            if not sel(s, lv):
+                continue
+            n = int(np.prod(s))
+            w += n
+            if lv > 0:
+                b = int(np.prod(s[:-2]))
+                c += b * _lib.packed_shape(s[-2], s[-1], wl.wavelet, lv)[2]
+            else:
+                c += n
+        return w, c
+    if phase.startswith('fused_'):
+        w, _ = per_layer(lambda s, lv: (lv == 0) if phase == 'fused_flat' else (lv > 0 and f'{s[-2]}x{s[-1]}' == phase.split('_')[1]))
+        return 8 * w
+    if phase.startswith('small_'):
+        hw = phase.rsplit('_', 1)[1]
+        w, c = per_layer(lambda s, lv: lv > 0 and f'{s[-2]}x{s[-1]}' == hw)
+        return 4 * w + 4 * c                  # analysis: weights in, coefficients out; synthesis: the reverse
+    if phase.startswith('select'):
+        w0, _ = per_layer(lambda s, lv: lv == 0)
+        _, c1 = per_layer(lambda s, lv: lv > 0)
+        return 4 * c1 + 8 * w0                # one read of the coefficients; level-0 layers: read + pruned write
+    return 0
+
+
 def time_e2e(name, steps, warmup, world, dev):
     """host buffers in, host buffers out, through the C-ABI host-I/O plan; returns (ms, h2d, d2h bytes/step)"""
     from wavelettransforms_b200 import _lib, engine, workloads
@@ -322,7 +406,7 @@ def _cpu_prune_layer(args):
     from oracle import reference_flow as rf
     w = torch.from_numpy(seed_w).view(shape)
     t0 = time.perf_counter()
-    out, zeros = rf.multi_resolution_analysis([w], wavelet, level, pct, numpy_semantics='live', clamp_level=clamp)
+    out, zeros = rf.multi_resolution_analysis([w], wavelet, level, pct, numpy_semantics=NUMPY_SEMANTICS, clamp_level=clamp)
     return idx, time.perf_counter() - t0, zeros
 
 
@@ -355,7 +439,7 @@ def run_cpu_baseline(name, budget_s):
     return {
         'value': elems / spent, 'unit': UNIT, 'cores': 1, 'kind': 'port',
         'sample': f'{len(used)} of {len(ws)} conv layers of {name} ({elems} elems, smallest first), '
-                  f'{spent:.1f} s on one core; oracle C DWT + live numpy percentile/where '
+                  f'{spent:.1f} s on one core; oracle C DWT + numpy partition / where, numpy-1.22 percentile arithmetic '
                   f'(oracle/reference_flow.py)',
     }
 
@@ -399,13 +483,13 @@ def run_reference_arm(args):
         dt = time.perf_counter() - t0
     value = acc * args.steps / dt
     sample = (f'{len(chosen)} of {len(ws)} conv layers per step ({acc} elems), process pool of {nproc} on '
-              f'{cores} host cores; oracle C DWT + live numpy percentile/where (oracle/reference_flow.py); '
+              f'{cores} host cores; oracle C DWT + numpy partition / where with the numpy-1.22 percentile arithmetic of the reference pin (oracle/reference_flow.py); '
               f'no compiled reference exists (pure Python over PyWavelets, absent here)')
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': name, 'numpy_semantics': 'live'},
+        'config': base_config(name, args.replicas),
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': nproc, 'kind': 'port', 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
@@ -456,21 +540,28 @@ def run_ours(args):
     e2e_value = wl.elems * args.steps * world / (e2e_ms * 1e-3)
     consistent = verify_e2e_against_device(wl, host_out, e2e_counts)
 
-    # dominant kernel = the launch group with the largest live average duration
+    # roofline: `frac` is the WHOLE STEP on the path's algorithmic bytes (8 B per weight: read it once, write the pruned
+    # weight once); the launch groups are listed with their own bytes; the dominant one = largest live average duration
     kern = [(n, t, ln) for n, t, ln in phases if n not in ('memset', 'h2d', 'd2h')]
     dom = max(kern, key=lambda x: x[1])
-    dom_elems = phase_elems(wl, dom[0])
-    achieved = BYTES_PER_ELEM * dom_elems / (dom[1] * 1e-3) / 1e9
-    step_gbs = BYTES_PER_ELEM * wl.elems / (ms / args.steps * 1e-3) / 1e9
+    step_ms = ms / args.steps
+    step_gbs = BYTES_PER_ELEM * wl.elems / (step_ms * 1e-3) / 1e9
+    kernels = {}
+    for n, t, ln in kern:
+        b = phase_bytes(wl, n)
+        kernels[n] = {'ms': round(t, 5), 'launches': ln, 'own_bytes': b, 'own_gbs': round(b / (t * 1e-3) / 1e9, 1) if t > 0 else None,
+                      'own_frac': round(b / (t * 1e-3) / 1e9 / peak_gbs, 4) if t > 0 else None,
+                      'share_of_step': round(t / sum(x[1] for x in phases), 4)}
     roofline = {
-        'bound': 'hbm', 'kernel': dom[0], 'achieved': achieved, 'peak': peak_gbs, 'unit': 'GB/s',
-        'frac': achieved / peak_gbs, 'traffic': load_traffic(dom[0]),
-        'peak_source': peak_src, 'algorithmic_bytes_per_launch': BYTES_PER_ELEM * dom_elems,
-        'kernel_ms': dom[1], 'binding_resource': binding_resource(args.workload),
-        'whole_step': {'achieved': step_gbs, 'frac': step_gbs / peak_gbs,
-                       'note': '8 B x all weight elems / device ms_per_step (all launch groups)'},
-        'phases_ms': {n: round(t, 5) for n, t, _ in phases},
-        'timing': 'second pass over the same K steps with cudaEvents between launch groups',
+        'bound': 'hbm', 'achieved': step_gbs, 'peak': peak_gbs, 'unit': 'GB/s', 'frac': step_gbs / peak_gbs,
+        'what': 'whole step: 8 B x all weight elements / device ms_per_step (every launch group of the plan)',
+        'algorithmic_bytes_per_step': BYTES_PER_ELEM * wl.elems,
+        'traffic': load_traffic('step:' + args.workload), 'peak_source': peak_src,
+        'binding_resource': binding_resource(args.workload),
+        'dominant_kernel': dict(kernels[dom[0]], name=dom[0], traffic=load_traffic(dom[0])),
+        'kernels': kernels,
+        'timing': 'second pass over the same K steps with cudaEvents between launch groups (groups run serially there; the '
+                  'timed steps fork independent groups onto side streams)',
     }
     variants = {}
     if not args.no_variants and world == 1:
@@ -483,17 +574,17 @@ def run_ours(args):
             vgb = BYTES_PER_ELEM * v.elems / (vms / args.steps * 1e-3) / 1e9
             variants[vn] = {'value': v.elems * args.steps / (vms * 1e-3), 'ms_per_step': vms / args.steps,
                             'hbm_frac_whole_step': vgb / peak_gbs, 'launches_per_step': v.plans[0].num_launches,
+                            'select_path': v.plans[0].select_path, 'pruned_fraction': v.pruned_fraction(),
+                            'binding_resource': binding_resource(vn),
                             'phases_ms': {n: round(t, 5) for n, t, _ in vph}}
             v.close()
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': args.workload, 'model': None, 'layers': len(wl.census), 'elems_per_step_per_gpu': wl.elems,
-                   'levels': sorted(set(wl.levels)), 'mode': 'periodization', 'numpy_semantics': NUMPY_SEMANTICS,
-                   'l2_policy': f'{args.replicas} rotating replicas per GPU, inputs+outputs '
-                                f'{args.replicas * 2 * wl.elems * 4 / 1e6:.0f} MB > 126 MB L2',
-                   'parallelism': f'{world} independent replicas (no data-path collective)' if world > 1 else 'single GPU'},
+        'config': base_config(args.workload, args.replicas),
+        'parallelism': f'{world} independent replicas (no data-path collective)' if world > 1 else 'single GPU',
+        'select_path': wl.plans[0].select_path, 'pruned_fraction': wl.pruned_fraction(),
         'clocks': clocks,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                 'ms_per_step': e2e_ms / args.steps, 'matches_device_path_bitwise': consistent,
@@ -503,12 +594,17 @@ def run_ours(args):
         'roofline': roofline,
         'variants': variants,
     }
-    del line['config']['model']
     if not args.no_variants and world == 1:
         line['siblings'] = time_siblings(args.steps, dev)
+        line['noentropy_absolute'] = time_noentropy(dev, peak_gbs, args.steps)
+        line['dropin_call'] = time_dropin_call()
+        if not args.no_sweep:
+            line['sweep'] = time_sweep(dev, peak_gbs, args.steps)
     if not args.no_variants:
-        line['bank'] = time_bank(args.steps, dev, peak_gbs)
-        line['layer_sharded'] = time_layer_sharded(args.sharded_workload, min(args.steps, 100), min(args.warmup, 5), world, dev)
+        line['bank'] = time_bank(args.steps, dev, peak_gbs, world)
+        line['layer_sharded'] = {}
+        for swl in dict.fromkeys([args.sharded_workload, 'resnet50_bior2.2_L3_p90_unclamped', 'resnet18_bior2.2_L3_p90_unclamped']):
+            line['layer_sharded'][swl] = time_layer_sharded(swl, min(args.steps, 50), min(args.warmup, 5), world, dev)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line['cpu_baseline'] = run_cpu_baseline(args.workload, args.cpu_sample_seconds)
     wl.close()
@@ -577,6 +673,19 @@ def time_layer_sharded(name, steps, warmup, world, dev):
         pb.barrier()
 
     out = {}
+    # the unsharded model on ONE GPU, timed on every rank in the same run: the numerator of the strong-scaling efficiency
+    single_ms = None
+    if world > 1:
+        full = []
+        for _ in range(2):
+            xs = [w.to(dev) for w in host]
+            os_ = [torch.empty_like(x) for x in xs]
+            items = [(x.data_ptr(), o.data_ptr()) + engine.plane_geometry(x.shape) + (lv,) for x, o, lv in zip(xs, os_, levels)]
+            full.append((_lib.Plan(items, wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, pct, NUMPY_SEMANTICS), xs, os_))
+        single_ms = max_over_ranks(_time_plans([f[0] for f in full], steps, warmup), world, dev)
+        for f in full:
+            f[0].close()
+        del full
     modes = [('prune_only', False, step), ('prune_allgather', True, step)]
     if peer:
         modes.append(('prune_peer_store', True, peer_step))
@@ -595,6 +704,10 @@ def time_layer_sharded(name, steps, warmup, world, dev):
         barrier(world)
         ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
         out[label] = {'value': elems * steps / (ms * 1e-3), 'ms_per_step': ms / steps}
+        if single_ms:
+            out[label]['efficiency_vs_1gpu'] = round(single_ms / (world * ms / steps), 4)
+    if single_ms:
+        out['single_gpu_ms_per_step'] = single_ms
     if peer:
         # the peer-stored buffer of every rank must equal the all-gathered one, bit for bit
         step0 = modes[0][2]
@@ -607,46 +720,186 @@ def time_layer_sharded(name, steps, warmup, world, dev):
             pl.close()
     for p, _ in plans:
         p.close()
-    out.update(workload=name, scaling='strong', layers=len(census), elems=elems, lpt_balance=layout.balance,
+    out.update(workload=name, scaling='strong', n_gpus=world, layers=len(census), elems=elems, lpt_balance=layout.balance,
                allgather_bytes_per_rank=layout.shard_elems * 4 * max(world - 1, 0))
     return out
 
 
+def _time_plans(plans, steps, warmup):
+    stream = int(torch.cuda.current_stream().cuda_stream)
+    for i in range(warmup):
+        plans[i % len(plans)].run(stream)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        plans[(warmup + i) % len(plans)].run(stream)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def time_sweep(dev, peak_gbs, steps):
+    """BASELINE.json configs[1]: ResNet-18, {bior1.3, 2.2, 4.4, rbio1.3, 2.2, 4.4} x levels 1..5 x p in {10, 30, 50, 70, 90},
+    unclamped (the real transform) and clamped (dwt_pruning.py:64-65: dec_len >= 6 => level 0 for EVERY point of this grid,
+    so the clamped leg is wavelet- and level-independent and is run once per p).  Device-resident, 3 rotating replicas
+    (inputs + outputs 268 MB > L2), CUDA events."""
+    from wavelettransforms_b200 import _lib, engine, workloads
+    census = workloads.conv_census('resnet18')
+    host = workloads.random_init_weights(census, seed=0)
+    elems = sum(w.numel() for w in host)
+    R = 3
+    ins = [[w.to(dev) for w in host] for _ in range(R)]
+    outs = [[torch.empty_like(x) for x in xs] for xs in ins]
+    n = max(4, min(steps, 10))
+    stream = int(torch.cuda.current_stream().cuda_stream)
+
+    def point(wavelet, level, pct, clamp):
+        levels = host_effective_levels(census, wavelet, level, clamp)
+        plans = [_lib.Plan([(x.data_ptr(), o.data_ptr()) + engine.plane_geometry(x.shape) + (lv,) for x, o, lv in zip(xs, os_, levels)],
+                           wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, float(pct), NUMPY_SEMANTICS) for xs, os_ in zip(ins, outs)]
+        ms = _time_plans(plans, n, 2)
+        plans[0].run(stream)
+        counts, _, _ = plans[0].results(stream)
+        path = plans[0].select_path
+        for p in plans:
+            p.close()
+        return {'wavelet': wavelet, 'level': level, 'p': pct, 'ms': round(ms, 5), 'gelems_s': round(elems / (ms * 1e-3) / 1e9, 2),
+                'hbm_frac': round(BYTES_PER_ELEM * elems / (ms * 1e-3) / 1e9 / peak_gbs, 4),
+                'pruned_fraction': round(float(counts[:, 2].sum()) / elems, 5), 'select_path': path}
+
+    def summary(points):
+        v = sorted(points, key=lambda q: q['gelems_s'])
+        med = v[len(v) // 2]
+        tag = lambda q: f"{q['wavelet']} L{q['level']} p{q['p']}"
+        return {'n': len(v), 'min': {'config': tag(v[0]), 'gelems_s': v[0]['gelems_s'], 'hbm_frac': v[0]['hbm_frac']},
+                'median': {'config': tag(med), 'gelems_s': med['gelems_s'], 'hbm_frac': med['hbm_frac']},
+                'max': {'config': tag(v[-1]), 'gelems_s': v[-1]['gelems_s'], 'hbm_frac': v[-1]['hbm_frac']},
+                'configs_that_prune_nothing': sum(1 for q in v if q['pruned_fraction'] == 0.0),
+                'select_paths': {k: sum(1 for q in v if q['select_path'] == k) for k in sorted({str(q['select_path']) for q in v})}}
+
+    ps = [10, 30, 50, 70, 90]
+    unclamped = [point(w, L, p, False) for w in ('bior1.3', 'bior2.2', 'bior4.4', 'rbio1.3', 'rbio2.2', 'rbio4.4')
+                 for L in (1, 2, 3, 4, 5) for p in ps]
+    clamped = [point('bior4.4', 5, p, True) for p in ps]
+    return {'workload': 'resnet18 conv layers', 'elems': elems, 'unit': 'G elems/s', 'steps_per_point': n,
+            'unclamped': dict(summary(unclamped), points=unclamped),
+            'clamped_level0': dict(summary(clamped), points=clamped,
+                                   note='every (wavelet, level) of the grid clamps to level 0 on ResNet planes: one run per p')}
+
+
+def time_noentropy(dev, peak_gbs, steps):
+    """dwt_pruning_NoEntropy.py's flow (absolute threshold, no clamp) on ResNet-18: the fused recompute kernels (WT_FUSED=all:
+    one pass per plane class) against the round-1 kernels (WT_FUSED=off) and the library's default routing (fused for
+    level-0 layers only)"""
+    from wavelettransforms_b200 import _lib, engine, workloads
+    census = workloads.conv_census('resnet18')
+    host = workloads.random_init_weights(census, seed=0)
+    elems = sum(w.numel() for w in host)
+    R = 3
+    ins = [[w.to(dev) for w in host] for _ in range(R)]
+    outs = [[torch.empty_like(x) for x in xs] for xs in ins]
+    out = {}
+    prev = os.environ.get('WT_FUSED')
+    for label, wavelet, level in (('level0 (any wavelet, L0)', 'bior4.4', 0), ('haar L1', 'haar', 1), ('db2 L2', 'db2', 2), ('bior4.4 L5', 'bior4.4', 5)):
+        row = {}
+        for mode in ('default', 'all', 'off'):
+            if mode == 'default':
+                os.environ.pop('WT_FUSED', None)
+            else:
+                os.environ['WT_FUSED'] = mode
+            plans = [_lib.Plan([(x.data_ptr(), o.data_ptr()) + engine.plane_geometry(x.shape) + (level,) for x, o in zip(xs, os_)],
+                               wavelet, 'periodization', _lib.THRESHOLD_ABSOLUTE, 0.02, NUMPY_SEMANTICS) for xs, os_ in zip(ins, outs)]
+            ms = _time_plans(plans, max(4, min(steps, 20)), 3)
+            row[{'default': 'default_routing', 'all': 'fused_kernels', 'off': 'round1_kernels'}[mode]] = {
+                'ms_per_step': round(ms, 5), 'launches_per_step': plans[0].num_launches,
+                'hbm_frac_whole_step': round(BYTES_PER_ELEM * elems / (ms * 1e-3) / 1e9 / peak_gbs, 4)}
+            for p in plans:
+                p.close()
+        out[label] = row
+    if prev is None:
+        os.environ.pop('WT_FUSED', None)
+    else:
+        os.environ['WT_FUSED'] = prev
+    return out
+
+
+def time_dropin_call():
+    """the call the reference's driver makes (main_pruning.py:185-186): dwt_pruning.wavelet_pruning(model_on_cpu, ...) --
+    pageable host weights, per-call plan, results back on the model's device, per-layer CSV, save_pretrained.  Wall clock."""
+    import shutil
+    from transformers import ResNetConfig, ResNetForImageClassification
+    from wavelettransforms_b200 import dwt_pruning, utils
+    arch, wavelet, level, pct, clamp = WORKLOADS[DEFAULT_WORKLOAD]
+    tmp = tempfile.mkdtemp(prefix='wt_dropin_')
+    old_root, old_save = utils.OUTPUT_ROOT, dwt_pruning.save_model
+    out = {}
+    try:
+        utils.OUTPUT_ROOT = os.path.join(tmp, 'SavedModels')
+        torch.manual_seed(0)
+        base = ResNetForImageClassification(ResNetConfig(layer_type='basic', hidden_sizes=[64, 128, 256, 512], depths=[2, 2, 2, 2]))
+        import copy
+        for label, save in (('save_excluded', False), ('save_included', True)):
+            dwt_pruning.save_model = old_save if save else (lambda model, d: None)
+            ts = []
+            for rep in range(3):
+                m = copy.deepcopy(base)
+                t0 = time.perf_counter()
+                dwt_pruning.wavelet_pruning(m, wavelet, level, pct, os.path.join(tmp, 'experiment_log.csv'), f'{rep:08x}')
+                ts.append(time.perf_counter() - t0)
+            out[label] = {'ms': round(min(ts[1:]) * 1e3, 2), 'first_call_ms': round(ts[0] * 1e3, 2)}
+        out['call'] = f"dwt_pruning.wavelet_pruning(cpu_model, '{wavelet}', {level}, {pct}, csv, guid) -- the clamped flow of the driver"
+        out['elems'] = 11166912
+    finally:
+        utils.OUTPUT_ROOT, dwt_pruning.save_model = old_root, old_save
+        shutil.rmtree(tmp, ignore_errors=True)
+    return out
+
+
 def time_siblings(steps, dev):
-    """BASELINE config 3: the two sibling maskers on ResNet-18 at 50 % (device-resident, in place, every step on a
+    """BASELINE config 3: the two sibling maskers on ResNet-18 at 10..90 % (device-resident, in place, every step on a
     fresh copy of the weights; per-call allocation and the host synchronisation of the entry points included)"""
     from wavelettransforms_b200 import engine, workloads
     census = workloads.conv_census('resnet18')
     host = workloads.random_init_weights(census, seed=0)
     elems = sum(w.numel() for w in host)
-    n = max(4, min(steps, 32))
+    n = max(4, min(steps, 16))
     out = {}
     for which in ('min_weight', 'random'):
-        copies = [[w.to(dev) for w in host] for _ in range(n + 2)]
-        torch.cuda.synchronize()
+        rows = {}
+        for sparsity in (0.1, 0.3, 0.5, 0.7, 0.9):
+            copies = [[w.to(dev) for w in host] for _ in range(n + 2)]
+            torch.cuda.synchronize()
 
-        def one(ws):
-            if which == 'min_weight':    # min_weight_pruning.py:66-74 for every layer, one grouped call
-                engine.min_weight_prune_(ws, [int(w.numel() * 0.5) for w in ws])
-            else:                        # random_pruning.py:51-58 per layer (torch.randperm is the RNG)
-                for w in ws:
-                    flat = w.view(-1)
-                    engine.scatter_zero_(flat, torch.randperm(flat.numel(), device=dev)[: flat.numel() // 2])
-        one(copies[0])
-        one(copies[1])
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for i in range(n):
-            one(copies[2 + i])
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        out[which] = {'value': elems * n / dt, 'unit': UNIT, 'ms_per_step': dt / n * 1e3, 'steps': n,
-                      'sparsity': 0.5, 'workload': 'resnet18 conv layers, 50 %'}
-        del copies
+            def one(ws):
+                if which == 'min_weight':    # min_weight_pruning.py:66-74 for every layer, one grouped call
+                    engine.min_weight_prune_(ws, [int(w.numel() * sparsity) for w in ws])
+                else:                        # random_pruning.py:51-58: torch.randperm per layer (the RNG of record), grouped scatter + count
+                    engine.scatter_zero_group_([w.view(-1) for w in ws],
+                                               [torch.randperm(w.numel(), device=dev)[: int(w.numel() * sparsity)] for w in ws])
+            one(copies[0])
+            one(copies[1])
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for i in range(n):
+                one(copies[2 + i])
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            rows[f'{int(sparsity * 100)}%'] = {'value': elems * n / dt, 'ms_per_step': dt / n * 1e3}
+            del copies
+        out[which] = dict(rows['50%'], unit=UNIT, steps=n, sparsity=0.5, workload='resnet18 conv layers, 50 %', sweep=rows)
+    # what torch.randperm alone costs (it stays the RNG so masks match the reference's bit for bit)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(4):
+        for w in host:
+            torch.randperm(w.numel(), device=dev)
+    torch.cuda.synchronize()
+    out['random']['randperm_only_ms'] = (time.perf_counter() - t0) / 4 * 1e3
     return out
 
 
-def time_bank(steps, dev, peak_gbs):
+def time_bank(steps, dev, peak_gbs, world=1):
     """BASELINE config 5 (a slice of the synthetic weight bank per GPU, seeds 1000+i): 32 tensors of 512x512x3x3 and
     2 matrices of 4096x4096, level-5 db4 at p = 50 through dwt_pruning's clamp (3x3 planes: level 0 = select + zero;
     4096x4096: the full five-level transform on the generic tiled path).  Device-resident, cudaEvents."""
@@ -671,10 +924,14 @@ def time_bank(steps, dev, peak_gbs):
             plan.run(stream)
         e1.record()
         torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / n
+        ms_local = e0.elapsed_time(e1) / n
+        barrier(world)
+        ms = max_over_ranks(ms_local, world, dev)      # every rank prunes its own slice of the bank: no collective, weak scaling
         elems = sum(x.numel() for x in xs)
         gbs = BYTES_PER_ELEM * elems / (ms * 1e-3) / 1e9
-        out[label] = {'value': elems / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms, 'elems': elems, 'steps': n,
+        out[label] = {'value': elems * world / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms, 'elems': elems * world,
+                      'elems_per_gpu': elems, 'n_gpus': world, 'scaling': 'weak', 'steps': n, 'binding_resource':
+                      'hbm (level-0 select+zero)' if len(shapes[0]) == 4 else 'fp32_issue + shared-memory latency (db4 round trip, no FMA)',
                       'launches_per_step': plan.num_launches, 'hbm_frac_whole_step': gbs / peak_gbs,
                       'l2_policy': f'inputs + outputs {2 * elems * 4 / 1e6:.0f} MB > 126 MB L2'}
         plan.close()

@@ -139,6 +139,9 @@ int wt_plan_results(WtPlan* plan, void* stream, int64_t* counts, int64_t* nonzer
  * per-kernel durations; leave it off on the production path (each event costs ~1 us of stream time).
  */
 int wt_plan_set_timing(WtPlan* plan, int enable);
+/* which select the plan's percentile threshold runs through: 0 sampled (one full pass + short candidate lists),
+ * 1 radix (three passes), 2 fused recompute kernels, -1 none (absolute threshold / empty plan).  Reporting aid. */
+int wt_plan_select_path(const WtPlan* plan);
 /* Layer-sharded runs (north star: layers dealt to the GPUs of a box, the pruned state reassembled on every rank).
  * Every rank's output tensors live in a flat buffer of ONE layout that is mapped into all peers (CUDA VMM /
  * symmetric memory); byte_deltas[q] = (peer q's mapping of ITS buffer) - (this rank's buffer).  The kernels that

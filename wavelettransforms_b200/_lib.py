@@ -26,7 +26,7 @@ EXPORTS = [
     'wt_version', 'wt_last_error', 'wt_wavelet_lookup', 'wt_wavelet_filters', 'wt_dwt_max_level', 'wt_dwt_coeff_len',
     'wt_packed_shape', 'wt_percentile_plan', 'wt_plan_create', 'wt_plan_destroy', 'wt_plan_device_bytes',
     'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device',
-    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers',
+    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path',
     'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_select_abs_noalloc_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
     'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32',
 ]
@@ -63,6 +63,7 @@ def lib():
     L.wt_plan_results.argtypes = [vp, vp, P(i64), P(i64), P(fl)]
     L.wt_plan_counts_device.argtypes = [vp, P(vp)]
     L.wt_plan_set_timing.argtypes = [vp, ci]
+    L.wt_plan_select_path.argtypes = [vp]
     L.wt_plan_set_peers.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_int64)]
     L.wt_plan_phase_times.argtypes = [vp, ci, P(fl), P(ci), ctypes.c_char_p, ci]
     L.wt_dwt_prune_f32.argtypes = [P(WtLayerDesc), ci, ci, ci, ci, dbl, ci, vp, P(i64), P(i64), P(fl)]
@@ -195,6 +196,10 @@ class Plan:
             check(n)
         raw = names.raw
         return [(raw[i * 64:(i + 1) * 64].split(b'\0', 1)[0].decode(), float(ms[i]), int(ln[i])) for i in range(n)]
+
+    @property
+    def select_path(self):
+        return {0: 'sampled', 1: 'radix', 2: 'fused', -1: None}[lib().wt_plan_select_path(self._h)]
 
     @property
     def device_bytes(self):

@@ -595,17 +595,21 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     P->d_cand.assign(n_layers, nullptr); P->cand_cap.assign(n_layers, 0);
     const int F = P->bank.F;
     // Which layers take the fused recompute kernels (wt_fused.cuh) -- decided by measurement on the B200:
-    //   absolute thresholds, level 0 or filters of <= 4 taps (HBM-bound): ONE pass, 2-4x faster than the round-1 kernels;
+    //   absolute thresholds at level 0 (dwt_pruning_NoEntropy.py:35-45 on a <2-D tensor or with level 0): ONE pass over a
+    //   whole model, 29 us against 118 us of per-layer launches for ResNet-18 (47 % of the measured HBM rate);
+    //   small planes, absolute: the persistent CTAs hold few warps (80 registers, 68 KB of shared memory each) and lose to
+    //   the one-tile-per-CTA kernels of wt_small.cu, which hide the HBM latency with occupancy (haar L1: 90 us vs 62 us);
     //   percentile thresholds: bit-exact and 1.1x the algorithmic DRAM traffic, but four latency-bound phases against the
-    //   select's three on a 45 MB model, and a slower streaming loop on large data: the round-1 kernels stay the default.
-    // WT_FUSED=all|abs|off overrides (all: every layer the fused kernels support; WT_LEGACY_PATH = off).
+    //   select's three on a 45 MB model and a slower streaming loop on large data (2.4 GB: 974 us vs 758 us).
+    // So the round-1 kernels stay the default everywhere else.  WT_FUSED=all|abs|off overrides (all: every layer the fused
+    // kernels support -- tests/test_gpu_fused.py keeps that path bit-exact; WT_LEGACY_PATH = off).
     int fused_mode = 1;
     if (const char* e = getenv("WT_FUSED")) fused_mode = !strcmp(e, "all") ? 2 : (!strcmp(e, "off") ? 0 : 1);
     if (getenv("WT_LEGACY_PATH")) fused_mode = 0;
     auto wants_fused = [&](const WtLayerDesc& L) {
         if (fused_mode == 2) return true;
         if (fused_mode == 0) return false;
-        return threshold_kind == WT_THRESHOLD_ABSOLUTE && (L.level == 0 || F <= 4);
+        return threshold_kind == WT_THRESHOLD_ABSOLUTE && L.level == 0;
     };
 
     // ---- classify + size ----
@@ -973,6 +977,15 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     WT_CHECK(mark_rc == WT_OK, WT_E_CUDA, "wt_plan_run: cudaEvent failure while timing phases");
     P->n_launches = launches;
     return WT_OK;
+}
+
+extern "C" int wt_plan_select_path(const WtPlan* P) {
+    if (!P) return -1;
+    if (P->host_io) return P->children.empty() ? -1 : wt_plan_select_path(P->children[0]);
+    if (P->thr_kind != WT_THRESHOLD_PERCENTILE) return -1;
+    for (const auto& c : P->fused) if (c.n_select > 0) return 2;
+    if (P->sel_jobs.empty()) return -1;
+    return wt_select_path(P->sel_args.n_tiles, P->sel_args.short_lists);
 }
 
 extern "C" int wt_plan_set_timing(WtPlan* P, int enable) {
