@@ -109,7 +109,7 @@ def base_config(name, replicas=8):
     elems = sum(int(np.prod(s)) for _, s in census)
     levels = host_effective_levels(census, wavelet, level, clamp)
     return {'workload': name, 'layers': len(census), 'elems_per_step_per_gpu': elems, 'levels': sorted(set(levels)),
-            'mode': 'periodization', 'numpy_semantics': NUMPY_SEMANTICS,
+            'mode': 'periodization', 'numpy_semantics': NUMPY_SEMANTICS, 'arithmetic': 'faithful (fp32 multiply then add, no FMA)',
             'l2_policy': f'GPU arm: {replicas} rotating replicas of the model per GPU, inputs+outputs '
                          f'{replicas * 2 * elems * 4 / 1e6:.0f} MB > 126 MB L2, so no step finds its input in L2; the CPU arm has none'}
 
@@ -228,7 +228,7 @@ class ClockSampler:
 class DeviceWorkload:
     """R replicas of the model's conv weights on the GPU, one device-I/O plan per replica."""
 
-    def __init__(self, name, replicas, dev):
+    def __init__(self, name, replicas, dev, arithmetic='faithful'):
         from wavelettransforms_b200 import _lib, engine, workloads
         self.name = name
         arch, self.wavelet, self.level, self.pct, self.clamp = WORKLOADS[name]
@@ -245,6 +245,8 @@ class DeviceWorkload:
                      for x, o, lv in zip(xs, os_, self.levels)]
             self.plans.append(_lib.Plan(items, self.wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, self.pct,
                                         NUMPY_SEMANTICS, host_io=False))
+            if arithmetic != 'faithful':
+                self.plans[-1].set_arithmetic(arithmetic)
             self.ins.append(xs)
             self.outs.append(os_)
         torch.cuda.synchronize()
@@ -578,6 +580,18 @@ def run_ours(args):
                             'binding_resource': binding_resource(vn),
                             'phases_ms': {n: round(t, 5) for n, t, _ in vph}}
             v.close()
+    # the named fast mode beside the faithful arithmetic (never mixed into `value`): same workload, every DWT multiply-add fused
+    fast = None
+    if not args.no_variants and world == 1 and max(wl.levels) > 0:
+        fw = DeviceWorkload(args.workload, args.replicas, dev, arithmetic='fma_taporder')
+        fms, _ = time_device_steps(fw, args.steps, args.warmup, world, dev)
+        fph = phase_profile(fw, min(args.steps, 50))
+        fast = {'arithmetic': 'fma_taporder (same tap order, FFMA; oracle twin orc_set_arithmetic(1); masks may differ from the reference)',
+                'value': fw.elems * args.steps / (fms * 1e-3), 'ms_per_step': fms / args.steps,
+                'speedup_vs_faithful_step': (ms / args.steps) / (fms / args.steps),
+                'hbm_frac_whole_step': BYTES_PER_ELEM * fw.elems / (fms / args.steps * 1e-3) / 1e9 / peak_gbs,
+                'pruned_fraction': fw.pruned_fraction(), 'phases_ms': {n: round(t, 5) for n, t, _ in fph}}
+        fw.close()
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
@@ -592,6 +606,7 @@ def run_ours(args):
         'gpu_launches': launches,
         'launches_per_step': wl.plans[0].num_launches,
         'roofline': roofline,
+        'fast_mode': fast,
         'variants': variants,
     }
     if not args.no_variants and world == 1:

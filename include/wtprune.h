@@ -139,6 +139,16 @@ int wt_plan_results(WtPlan* plan, void* stream, int64_t* counts, int64_t* nonzer
  * per-kernel durations; leave it off on the production path (each event costs ~1 us of stream time).
  */
 int wt_plan_set_timing(WtPlan* plan, int enable);
+/* Arithmetic of the DWT multiply-adds.  WT_ARITH_FAITHFUL (default): fp32 multiply, then fp32 add, no FMA,
+ * the order of oracle/dwt_oracle.c -- the arithmetic every bit-exactness claim of this library refers to.
+ * WT_ARITH_FMA_TAPORDER: the same taps in the same order with every multiply-add fused into one FFMA (one rounding
+ * instead of two).  A NAMED FAST MODE for the fp32-issue-bound decompositions (long filters on 3x3 planes), never chosen
+ * silently: bit-exact against the oracle's twin (orc_set_arithmetic(1)), within 1e-5 relative / 1e-6 absolute of the
+ * faithful weights, but exact zeros of a round trip are not preserved, so masks and zero counts can differ
+ * from the reference's.  Small-plane layers only (WT_E_UNSUPPORTED for plans with layers on the generic tiled path). */
+#define WT_ARITH_FAITHFUL 0
+#define WT_ARITH_FMA_TAPORDER 1
+int wt_plan_set_arithmetic(WtPlan* plan, int arithmetic);
 /* which select the plan's percentile threshold runs through: 0 sampled (one full pass + short candidate lists),
  * 1 radix (three passes), 2 fused recompute kernels, -1 none (absolute threshold / empty plan).  Reporting aid. */
 int wt_plan_select_path(const WtPlan* plan);

@@ -57,8 +57,29 @@ def lib():
         L.orc_percentile_threshold.restype = ctypes.c_float
         L.orc_absolute_threshold.argtypes = [fp, i64, ctypes.c_float]
         L.orc_filters.argtypes = [ci] + [ctypes.POINTER(ctypes.c_double)] * 4
+        L.orc_set_arithmetic.argtypes = [ci]
         _LIB = L
     return _LIB
+
+
+ARITHMETICS = {'faithful': 0, 'fma_taporder': 1}
+
+
+class arithmetic:
+    """with oracle.arithmetic('fma_taporder'): ...  -- the oracle twin of the library's named fast mode (same tap
+    order, every multiply-add fused); 'faithful' (no FMA) is the default and the reference's arithmetic"""
+
+    def __init__(self, name):
+        self.value = ARITHMETICS[name]
+
+    def __enter__(self):
+        self.prev = lib().orc_get_arithmetic()
+        lib().orc_set_arithmetic(self.value)
+        return self
+
+    def __exit__(self, *exc):
+        lib().orc_set_arithmetic(self.prev)
+        return False
 
 
 def _fp(a):

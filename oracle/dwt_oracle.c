@@ -30,6 +30,11 @@
  *     extended sample is formed first (ext_sample: an index map, a negation, or one subtract +
  *     multiply + add for smooth, running subtract / add for antireflect), then multiplied by the tap;
  *   - dwt2: axis -2 first, then axis -1.  idwt2: axis -1 first, then axis -2.
+ *
+ * Arithmetic twin (orc_set_arithmetic(1), "fma_taporder"): the SAME tap order with every multiply-add
+ * contracted into one fused multiply-add, acc = fmaf(tap, sample, acc) -- the oracle of the library's
+ * named fast mode (wt_plan_set_arithmetic).  It is NOT the reference's arithmetic: exact zeros of a
+ * round trip are not preserved; it is held to the faithful result by tolerance only.
  */
 #include <math.h>
 #include <stdint.h>
@@ -52,6 +57,16 @@
 #define ORC_MODE_ANTIREFLECT 8
 #define ORC_NUM_MODES 9
 #define ORC_MAX_LEVEL 32
+
+static int g_arith = 0; /* 0 faithful (multiply, then add), 1 fma_taporder */
+void orc_set_arithmetic(int a) { g_arith = a ? 1 : 0; }
+int orc_get_arithmetic(void) { return g_arith; }
+/* acc + tap * v in the selected arithmetic */
+static inline float mac(float acc, float tap, float v) {
+    if (g_arith) return fmaf(tap, v, acc);
+    float p = tap * v;
+    return acc + p;
+}
 
 int orc_wavelet_index(const char* name) {
     for (int i = 0; i < ORC_NUM_WAVELETS; ++i)
@@ -217,10 +232,7 @@ static void dwt1d_band(const float* x, int n, int xs, const float* f, int F, int
     int base = (mode == ORC_MODE_PERIODIZATION) ? F / 2 : 1;
     for (int o = 0; o < no; ++o) {
         float acc = 0.0f;
-        for (int j = 0; j < F; ++j) {
-            float p = f[j] * ext_sample(x, n, xs, base + 2 * o - j, mode);
-            acc = acc + p;
-        }
+        for (int j = 0; j < F; ++j) acc = mac(acc, f[j], ext_sample(x, n, xs, base + 2 * o - j, mode));
         out[(int64_t)o * os] = acc;
     }
 }
@@ -241,10 +253,8 @@ static void idwt1d(const float* ca, const float* cd, int n, int cs, const float*
                 int oo = pmod(2 * (i - start) + shift + 1, 2 * n);
                 for (int j = 0; j < F / 2; ++j) {
                     float v = c[(int64_t)pmod(i - j, n) * cs];
-                    float pe = r[2 * j] * v;
-                    float po = r[2 * j + 1] * v;
-                    out[(int64_t)oe * os] = out[(int64_t)oe * os] + pe;
-                    out[(int64_t)oo * os] = out[(int64_t)oo * os] + po;
+                    out[(int64_t)oe * os] = mac(out[(int64_t)oe * os], r[2 * j], v);
+                    out[(int64_t)oo * os] = mac(out[(int64_t)oo * os], r[2 * j + 1], v);
                 }
             }
         }
@@ -256,10 +266,8 @@ static void idwt1d(const float* ca, const float* cd, int n, int cs, const float*
                 float se = 0.0f, so = 0.0f;
                 for (int j = 0; j < F / 2; ++j) {
                     float v = c[(int64_t)(i - j) * cs];
-                    float pe = r[2 * j] * v;
-                    float po = r[2 * j + 1] * v;
-                    se = se + pe;
-                    so = so + po;
+                    se = mac(se, r[2 * j], v);
+                    so = mac(so, r[2 * j + 1], v);
                 }
                 int o = 2 * (i - F / 2 + 1);
                 out[(int64_t)o * os] = out[(int64_t)o * os] + se;

@@ -14,6 +14,7 @@ MODES = {'periodization': 0, 'symmetric': 1, 'zero': 2, 'constant': 3, 'reflect'
          'antisymmetric': 7, 'antireflect': 8}
 NUMPY_SEMANTICS = {'legacy_1_22': 0, 'nep50_2x': 1}
 THRESHOLD_PERCENTILE, THRESHOLD_ABSOLUTE = 0, 1
+ARITHMETICS = {'faithful': 0, 'fma_taporder': 1}
 
 
 class WtLayerDesc(ctypes.Structure):
@@ -26,7 +27,7 @@ EXPORTS = [
     'wt_version', 'wt_last_error', 'wt_wavelet_lookup', 'wt_wavelet_filters', 'wt_dwt_max_level', 'wt_dwt_coeff_len',
     'wt_packed_shape', 'wt_percentile_plan', 'wt_plan_create', 'wt_plan_destroy', 'wt_plan_device_bytes',
     'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device',
-    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path',
+    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path', 'wt_plan_set_arithmetic',
     'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_select_abs_noalloc_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
     'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32',
 ]
@@ -64,6 +65,7 @@ def lib():
     L.wt_plan_counts_device.argtypes = [vp, P(vp)]
     L.wt_plan_set_timing.argtypes = [vp, ci]
     L.wt_plan_select_path.argtypes = [vp]
+    L.wt_plan_set_arithmetic.argtypes = [vp, ci]
     L.wt_plan_set_peers.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_int64)]
     L.wt_plan_phase_times.argtypes = [vp, ci, P(fl), P(ci), ctypes.c_char_p, ci]
     L.wt_dwt_prune_f32.argtypes = [P(WtLayerDesc), ci, ci, ci, ci, dbl, ci, vp, P(i64), P(i64), P(fl)]
@@ -182,6 +184,12 @@ class Plan:
         d = [int(x) for x in byte_deltas]
         arr = (ctypes.c_int64 * max(len(d), 1))(*d)
         check(lib().wt_plan_set_peers(self._h, len(d), arr))
+
+    def set_arithmetic(self, name):
+        """'faithful' (default: no FMA, the oracle's arithmetic) or 'fma_taporder' (named fast mode, see wtprune.h)"""
+        if name not in ARITHMETICS:
+            raise ValueError(f"unknown arithmetic '{name}' (expected one of {sorted(ARITHMETICS)})")
+        check(lib().wt_plan_set_arithmetic(self._h, ARITHMETICS[name]))
 
     def set_timing(self, enable=True):
         check(lib().wt_plan_set_timing(self._h, 1 if enable else 0))

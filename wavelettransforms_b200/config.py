@@ -11,6 +11,10 @@ pruning method starts while safetensors serialises (once the kernels take micros
 critical path of main_pruning.py:175-209).  Off by default: the reference returns with the files on disk.
 utils.wait_for_saves() joins; it also runs at interpreter exit.
 
+arithmetic: 'faithful' (default: fp32 multiply then add, no FMA -- the arithmetic of the oracle and of every
+  bit-exactness claim) or 'fma_taporder' (named fast mode: the same taps in the same order, every multiply-add fused; for
+  the fp32-issue-bound decompositions; masks / zero counts may differ from the reference's).  WT_ARITHMETIC overrides.
+
 verbose: re-enables the reference's per-layer debug prints (dwt_pruning.py:29-30,121-122).
 """
 import os
@@ -18,3 +22,4 @@ import os
 numpy_semantics = os.environ.get('WT_NUMPY_SEMANTICS', 'legacy_1_22')
 verbose = os.environ.get('WT_VERBOSE', '0') not in ('0', '', 'false', 'False')
 async_save = os.environ.get('WT_ASYNC_SAVE', '0') not in ('0', '', 'false', 'False')
+arithmetic = os.environ.get('WT_ARITHMETIC', 'faithful')

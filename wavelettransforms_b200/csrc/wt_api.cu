@@ -917,7 +917,7 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         auto& c = P->small[k];
         snprintf(label, sizeof(label), "small_analysis_%dx%d", c.H, c.W);
         mark(label);
-        rc = wt_small_analysis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev,
+        rc = wt_small_analysis_launch(c.H, c.W, P->bank, P->arithmetic, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev,
                                       class_stream(k));
         if (rc) return rc;
         if (c.n_tiles) ++launches;
@@ -953,7 +953,7 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         auto& c = P->small[k];
         snprintf(label, sizeof(label), "small_synthesis_%dx%d", c.H, c.W);
         mark(label);
-        rc = wt_small_synthesis_launch(c.H, c.W, P->bank, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->thresholds_dev,
+        rc = wt_small_synthesis_launch(c.H, c.W, P->bank, P->arithmetic, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->thresholds_dev,
                                        P->counts_dev, class_stream(k));
         if (rc) return rc;
         if (c.n_tiles) ++launches;
@@ -976,6 +976,26 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     mark(nullptr);
     WT_CHECK(mark_rc == WT_OK, WT_E_CUDA, "wt_plan_run: cudaEvent failure while timing phases");
     P->n_launches = launches;
+    return WT_OK;
+}
+
+extern "C" int wt_plan_set_arithmetic(WtPlan* P, int arithmetic) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    WT_CHECK(arithmetic == WT_ARITH_FAITHFUL || arithmetic == WT_ARITH_FMA_TAPORDER, WT_E_INVALID, "unknown arithmetic %d", arithmetic);
+    if (arithmetic == WT_ARITH_FMA_TAPORDER) {
+        WT_CHECK(P->generic.empty(), WT_E_UNSUPPORTED,
+                 "fma_taporder: not available for layers on the generic tiled path (large or odd planes, non-periodization modes)");
+#ifndef WT_WITH_FMA_KERNELS
+        for (const auto& c : P->fused)
+            WT_CHECK(c.H == 0, WT_E_UNSUPPORTED, "fma_taporder: this build has no fused small-plane kernels in that arithmetic "
+                                                 "(WT_BUILD_FMA=1); the default routing does not use them");
+#endif
+    }
+    for (WtPlan* c : P->children) {
+        int rc = wt_plan_set_arithmetic(c, arithmetic);
+        if (rc) return rc;
+    }
+    P->arithmetic = arithmetic;
     return WT_OK;
 }
 

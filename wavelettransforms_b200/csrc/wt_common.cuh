@@ -291,7 +291,8 @@ struct WtSmallJob {
 bool wt_small_supported(int H, int W, int F, int level, int mode);
 // number of real coefficients per plane (periodization)
 int wt_small_ncoef(int H, int W, int level);
-int wt_small_analysis_launch(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+// fma: 0 faithful arithmetic (multiply, then add: the oracle's and the reference's), 1 fma_taporder (same tap order, fused)
+int wt_small_analysis_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
                              long long* counts, cudaStream_t stream);
-int wt_small_synthesis_launch(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+int wt_small_synthesis_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
                               const float* thresholds, long long* counts, cudaStream_t stream);

@@ -60,7 +60,7 @@ def _effective_levels(shapes, wavelet, level, clamp_level=True):
 
 def multi_resolution_analysis(weights: List[torch.Tensor], wavelet: str, level: int, percentile: float,
                               mode: str = 'periodization', *, numpy_semantics: Optional[str] = None,
-                              clamp_level: bool = True) -> Tuple[List[torch.Tensor], int]:
+                              clamp_level: bool = True, arithmetic: Optional[str] = None) -> Tuple[List[torch.Tensor], int]:
     """dwt_pruning.py:35-95.  Returns new tensors (dtype/device/shape of the inputs, inputs untouched)
     and the total number of zeros in them (torch.sum(pruned == 0), :88)."""
     _lib.wavelet_lookup(wavelet)  # ValueError for unknown names, as pywt.Wavelet does
@@ -77,7 +77,7 @@ def multi_resolution_analysis(weights: List[torch.Tensor], wavelet: str, level: 
     if len(live) != len(xs):
         raise IndexError('index -1 is out of bounds for axis 0 with size 0')  # np.percentile on an empty array
     res = engine.prune_device_tensors(xs, levels, wavelet, mode, _lib.THRESHOLD_PERCENTILE, float(percentile),
-                                      numpy_semantics)
+                                      numpy_semantics, arithmetic=arithmetic)
     pruned = [o.view(w.shape).to(w.device) for o, w in zip(res.outputs, weights)]
     return pruned, int(res.counts[:, 2].sum())
 

@@ -12,7 +12,7 @@ from .utils import (append_to_experiment_log, check_and_set_pruned_instance_path
 
 
 def multi_resolution_analysis(weights: List[torch.Tensor], wavelet: str, level: int, threshold: float,
-                              mode: str = 'periodization') -> Tuple[List[torch.Tensor], int]:
+                              mode: str = 'periodization', *, arithmetic=None) -> Tuple[List[torch.Tensor], int]:
     """dwt_pruning_NoEntropy.py:12-62: wavedec2(level) with no clamp, coeff_arr[|c| < threshold] = 0,
     waverec2, crop.  Returns (new tensors, sum over tensors of nonzeros(before) - nonzeros(after))."""
     _lib.wavelet_lookup(wavelet)
@@ -25,7 +25,7 @@ def multi_resolution_analysis(weights: List[torch.Tensor], wavelet: str, level: 
     dev = engine.cuda_device()
     xs = [engine.to_device_f32(w, dev) for w in weights]
     levels = [level if w.ndim >= 2 else 0 for w in weights]
-    res = engine.prune_device_tensors(xs, levels, wavelet, mode, _lib.THRESHOLD_ABSOLUTE, float(threshold))
+    res = engine.prune_device_tensors(xs, levels, wavelet, mode, _lib.THRESHOLD_ABSOLUTE, float(threshold), arithmetic=arithmetic)
     pruned = [o.view(w.shape).to(w.device) for o, w in zip(res.outputs, weights)]
     total = int((res.nonzero_before - res.counts[:, 1]).sum())
     return pruned, total

@@ -59,7 +59,7 @@ class PruneResult:
 def prune_device_tensors(xs: List[torch.Tensor], levels: Sequence[int], wavelet: str, mode: str, threshold_kind: int,
                          threshold_value: float, numpy_semantics: Optional[str] = None,
                          outs: Optional[List[torch.Tensor]] = None,
-                         peer_deltas: Optional[Sequence[int]] = None) -> PruneResult:
+                         peer_deltas: Optional[Sequence[int]] = None, arithmetic: Optional[str] = None) -> PruneResult:
     """xs: contiguous float32 CUDA tensors.  One plan, one launch sequence for the whole group.  peer_deltas: the
     kernels also store every output at out + delta (symmetric-memory mappings of the same buffer on the other ranks)."""
     sem = numpy_semantics or config.numpy_semantics
@@ -76,6 +76,9 @@ def prune_device_tensors(xs: List[torch.Tensor], levels: Sequence[int], wavelet:
         items.append((x.data_ptr(), o.data_ptr(), b, h, w, lv))
     plan = _lib.Plan(items, wavelet, mode, threshold_kind, threshold_value, sem, host_io=False)
     try:
+        arith = arithmetic or config.arithmetic
+        if arith != 'faithful':
+            plan.set_arithmetic(arith)
         if peer_deltas:
             plan.set_peers(peer_deltas)
         s = _stream_ptr()
