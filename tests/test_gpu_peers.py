@@ -55,6 +55,7 @@ def test_small_plane_mirror(monkeypatch, mode, misalign):
 
 
 def test_absolute_mirror_on_the_fused_path(monkeypatch):
+    """absolute thresholds mirror on the fused kernels only: level-0 layers by default, small planes with WT_FUSED=all"""
     from wavelettransforms_b200 import _lib
-    shapes = [(70, 33, 3, 3), (128, 64, 1, 1), (50, 50)]
-    _run(monkeypatch, 'abs', shapes, [1, 1, 0], 'db2', _lib.THRESHOLD_ABSOLUTE, 0.02, False)
+    _run(monkeypatch, 'abs', [(50, 50), (4099,), (16, 8, 3, 3)], [0, 0, 0], 'db2', _lib.THRESHOLD_ABSOLUTE, 0.02, False)
+    _run(monkeypatch, 'all', [(70, 33, 3, 3), (128, 64, 1, 1), (50, 50)], [1, 1, 0], 'db2', _lib.THRESHOLD_ABSOLUTE, 0.02, False)

@@ -209,8 +209,11 @@ struct WtPlan {
     WtSelArgs sel_args;
     // zeroed every run: [select scratch | counts]
     WtPeers peers = {};  // layer-sharded runs: byte distance to every peer's mapping of the output buffer
-    char* zero_block = nullptr;
+    char* zero_block = nullptr;    // the block the last / current run uses
     size_t zero_bytes = 0;
+    char* zero_blocks[2] = {nullptr, nullptr};  // percentile plans: two blocks alternate, the select kernel of run n zeroes run n + 1's
+    size_t counts_off = 0;         // offset of the counts inside a zero block
+    int zpar = 0;
     float* thresholds_dev = nullptr;
     long long* counts_dev = nullptr;
 
@@ -683,6 +686,7 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     const size_t sel_scratch = wt_select_scratch_bytes(std::max(n_sel, 1));
     const size_t off_zero = take(sel_scratch + (size_t)std::max(n_layers, 1) * 4 * sizeof(long long));
     const size_t zero_bytes = bytes - off_zero;
+    const size_t off_zero2 = take(zero_bytes);
     for (int i = 0; i < n_layers; ++i)
         if (P->path[i] == PATH_SMALL || P->path[i] == PATH_GENERIC) off_coef[i] = take((size_t)P->ncoef[i] * sizeof(float));
     if (threshold_kind == WT_THRESHOLD_PERCENTILE)
@@ -723,6 +727,12 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     P->thresholds_dev = reinterpret_cast<float*>(P->dev + off_thr);
     P->zero_block = P->dev + off_zero;
     P->zero_bytes = zero_bytes;
+    P->zero_blocks[0] = P->dev + off_zero;
+    P->zero_blocks[1] = P->dev + off_zero2;
+    P->counts_off = align_up(sel_scratch, 16);
+    e = cudaMemset(P->zero_blocks[0], 0, zero_bytes);
+    if (e == cudaSuccess) e = cudaMemset(P->zero_blocks[1], 0, zero_bytes);
+    if (e != cudaSuccess) { wt_set_error("cudaMemset failed: %s", cudaGetErrorString(e)); wt_plan_destroy(P); return WT_E_CUDA; }
     wt_select_bind(&P->sel_args, P->zero_block, std::max(n_sel, 1));
     P->counts_dev = reinterpret_cast<long long*>(P->zero_block + align_up(sel_scratch, 16));
     P->sel_args.jobs = P->sel_jobs_dev;
@@ -855,9 +865,21 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     char label[64];
     // counts / select scratch of the launches that accumulate with atomics (generic path, legacy kernels); the fused
     // classes zero their own scratch for the next run and store their counts, so a fused-only plan enqueues no memset
-    const size_t counts_off = (size_t)(reinterpret_cast<char*>(P->counts_dev) - P->zero_block);
-    const bool split_zero = P->legacy_zero && !P->timing && !P->aux.empty() && counts_off > 0 && counts_off < P->zero_bytes;
-    if (P->legacy_zero) {
+    // Percentile plans with a select launch enqueue no memset either: two blocks alternate and the select kernel of
+    // this run zeroes the block of the next one (every kernel that accumulates into the block runs in stream order after it).
+    const bool self_zero = P->thr_kind == WT_THRESHOLD_PERCENTILE && !P->sel_jobs.empty();
+    if (self_zero) {
+        P->zero_block = P->zero_blocks[P->zpar];
+        P->counts_dev = reinterpret_cast<long long*>(P->zero_block + P->counts_off);
+        wt_select_rebind(&P->sel_args, P->zero_block, (int)P->sel_jobs.size());
+        P->sel_args.counts = P->counts_dev;
+        P->sel_args.zero_next = P->zero_blocks[P->zpar ^ 1];
+        P->sel_args.zero_next_bytes = P->zero_bytes;
+        P->zpar ^= 1;
+    }
+    const size_t counts_off = P->counts_off;
+    const bool split_zero = !self_zero && P->legacy_zero && !P->timing && !P->aux.empty() && counts_off > 0 && counts_off < P->zero_bytes;
+    if (P->legacy_zero && !self_zero) {
         mark("memset");
         if (split_zero) WT_CUDA(cudaMemsetAsync(P->zero_block + counts_off, 0, P->zero_bytes - counts_off, stream));
         else WT_CUDA(cudaMemsetAsync(P->zero_block, 0, P->zero_bytes, stream));

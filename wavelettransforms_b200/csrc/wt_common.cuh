@@ -136,6 +136,8 @@ struct WtSelArgs {
     float* thresholds;          // [n_layers]
     long long* counts;          // [n_layers][4] {numel, nonzero, zeros, nonzero_before}
     int any_apply;              // at least one job has out != nullptr
+    char* zero_next;            // nullable: a block this launch zeroes for the NEXT run of the plan (two scratch blocks alternate,
+    unsigned long long zero_next_bytes;  // so a step enqueues no memset); multiple of 16 bytes
 };
 
 // candidate capacity (keys) the plan reserves for a population of n explicit values
@@ -160,6 +162,8 @@ static inline int wt_select_sample_shift(long long n) {
 size_t wt_select_scratch_bytes(int n_jobs);  // hist1+hist2+hist3+done+state, contiguous, memset to 0 before launch
 // lays out args over a zeroed scratch block
 void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
+// only re-points the scratch-relative fields (histograms, state, flags) at another zeroed block of the same layout
+void wt_select_rebind(WtSelArgs* a, void* scratch, int n_jobs);
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
 #define WT_SEL_SAMPLED_MIN_TILES 10240  // 40 Mi keys
 #ifndef WT_SEL_TAIL_MAX

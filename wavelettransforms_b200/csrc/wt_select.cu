@@ -1123,6 +1123,12 @@ __global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs 
     acc.slot = a.stamps ? a.stamps + (size_t)blockIdx.x * 16 : nullptr;
     acc.t0 = 0;
     acc.stamp(0);
+    if (a.zero_next) {   // the scratch + counts block of the plan's next run (in place of a memset in front of every step)
+        int4* z = reinterpret_cast<int4*>(a.zero_next);
+        const unsigned long long n16 = a.zero_next_bytes >> 4;
+        for (unsigned long long i = (unsigned long long)blockIdx.x * T + threadIdx.x; i < n16; i += (unsigned long long)gridDim.x * T)
+            z[i] = make_int4(0, 0, 0, 0);
+    }
     if (a.path == 0) {
         phase_s0_sample(a, sh, t_begin, t_end, acc);
         acc.stamp(1);
@@ -1200,7 +1206,7 @@ size_t wt_select_scratch_bytes(int n_jobs) {
     return per * (size_t)n_jobs + 256;
 }
 
-void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
+void wt_select_rebind(WtSelArgs* a, void* scratch, int n_jobs) {
     char* p = static_cast<char*>(scratch);
     a->hist1 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * WT_SEL_BINS1 * 8;
     a->hist2 = reinterpret_cast<unsigned long long*>(p); p += (size_t)n_jobs * WT_SEL_CBINS1 * 8;
@@ -1210,6 +1216,12 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
     a->fail_flag = reinterpret_cast<int*>(p);  // inside the 256 spare bytes
     a->wide_flag = a->fail_flag + 1;
     a->big_flag = a->fail_flag + 2;
+}
+
+void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs) {
+    wt_select_rebind(a, scratch, n_jobs);
+    a->zero_next = nullptr;
+    a->zero_next_bytes = 0;
     a->path = -1;  // resolved at launch: wt_select_path()
     a->short_lists = 0;
     a->stamps = nullptr;  // tuning aid, set by the plan when WT_SELECT_STAMPS is in the environment
