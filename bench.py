@@ -672,7 +672,11 @@ def time_layer_sharded(name, steps, warmup, world, dev):
                          for x, i in zip(plans[r][1], mine)]
                 pl = _lib.Plan(items, wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, pct, NUMPY_SEMANTICS)
                 pl.set_peers(pb.deltas)
-                peer.append((pl, pb))
+                pm = None
+                if pb.multicast_delta is not None:     # NVLS: the same plan storing once through the multicast mapping
+                    pm = _lib.Plan(items, wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, pct, NUMPY_SEMANTICS)
+                    pm.set_multicast(pb.multicast_delta)
+                peer.append((pl, pb, pm))
         except Exception as e:      # symmetric memory unavailable on this box, or a layer off the mirrored paths
             print(f'[bench] peer-store mode unavailable: {e}', file=sys.stderr)
             peer = None
@@ -682,10 +686,47 @@ def time_layer_sharded(name, steps, warmup, world, dev):
             peer = None
 
     def peer_step(i, _):
-        pl, pb = peer[i % R]
+        pl, pb, _pm = peer[i % R]
         if mine:
             pl.run(stream)
         pb.barrier()
+
+    def mc_step(i, _):
+        _pl, pb, pm = peer[i % R]
+        if mine:
+            pm.run(stream)
+        pb.barrier()
+
+    # fourth mode: the gather overlapped with the pruning -- layers in G size-ordered groups, each with its own LPT layout,
+    # flat buffer and plan; group g's all-gather runs on a side stream while group g + 1 is pruned (sharded.prune_sharded_pipelined)
+    pipe = None
+    if world > 1:
+        G = 4
+        groups = sharded.layer_groups(layout.numels, G)
+        side = torch.cuda.Stream(device=dev)
+        pipe = []
+        for _ in range(R):
+            rep = []
+            for idx in groups:
+                lay = sharded.ShardLayout([census[i][1] for i in idx], world)
+                fl = torch.zeros(world * lay.shard_elems, dtype=torch.float32, device=dev)
+                own = lay.owned(rank)
+                xs = [host[idx[k]].to(dev) for k in own]
+                items = [(x.data_ptr(), lay.view(fl, k).data_ptr()) + engine.plane_geometry(x.shape) + (levels[idx[k]],)
+                         for x, k in zip(xs, own)]
+                pl = _lib.Plan(items, wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, pct, NUMPY_SEMANTICS) if own else None
+                rep.append((pl, xs, fl, fl[rank * lay.shard_elems:(rank + 1) * lay.shard_elems]))
+            pipe.append(rep)
+
+    def pipe_step(i, _):
+        main = torch.cuda.current_stream()
+        for pl, _, fl, shard in pipe[i % R]:
+            if pl is not None:
+                pl.run(stream)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                torch.distributed.all_gather_into_tensor(fl, shard)
+        main.wait_stream(side)
 
     out = {}
     # the unsharded model on ONE GPU, timed on every rank in the same run: the numerator of the strong-scaling efficiency
@@ -702,8 +743,14 @@ def time_layer_sharded(name, steps, warmup, world, dev):
             f[0].close()
         del full
     modes = [('prune_only', False, step), ('prune_allgather', True, step)]
+    if pipe:
+        modes.append(('prune_allgather_pipelined', True, pipe_step))
     if peer:
         modes.append(('prune_peer_store', True, peer_step))
+        has_mc = torch.tensor([1 if all(p[2] is not None for p in peer) else 0], device=dev)
+        torch.distributed.all_reduce(has_mc, op=torch.distributed.ReduceOp.MIN)
+        if int(has_mc.item()):
+            modes.append(('prune_multicast_store', True, mc_step))
     for label, gather, step in modes:
         for i in range(warmup):
             step(i, gather)
@@ -731,8 +778,36 @@ def time_layer_sharded(name, steps, warmup, world, dev):
         torch.cuda.synchronize()
         barrier(world)
         out['prune_peer_store']['matches_allgather_bitwise'] = bool(torch.equal(flats[0], peer[0][1].flat))
-        for pl, _ in peer:
+        if 'prune_multicast_store' in out:
+            peer[0][1].flat.zero_()
+            torch.cuda.synchronize()
+            barrier(world)
+            mc_step(0, True)
+            torch.cuda.synchronize()
+            barrier(world)
+            out['prune_multicast_store']['matches_allgather_bitwise'] = bool(torch.equal(flats[0], peer[0][1].flat))
+            out['prune_multicast_store']['how'] = 'one multimem.st per pruned weight to the NVSwitch multicast mapping (egress = own shard)'
+        for pl, _, pm in peer:
             pl.close()
+            if pm is not None:
+                pm.close()
+    if pipe:
+        # the pipelined buffers against the single all-gather, layer by layer
+        modes[0][2](0, True)
+        pipe_step(0, True)
+        torch.cuda.synchronize()
+        barrier(world)
+        ok, gi = True, 0
+        for idx, (pl, _, fl, _) in zip(sharded.layer_groups(layout.numels, 4), pipe[0]):
+            lay = sharded.ShardLayout([census[i][1] for i in idx], world)
+            for k, i in enumerate(idx):
+                ok = ok and bool(torch.equal(lay.view(fl, k), layout.view(flats[0], i)))
+        out['prune_allgather_pipelined']['matches_allgather_bitwise'] = ok
+        out['prune_allgather_pipelined']['groups'] = 4
+        for rep in pipe:
+            for pl, _, _, _ in rep:
+                if pl is not None:
+                    pl.close()
     for p, _ in plans:
         p.close()
     out.update(workload=name, scaling='strong', n_gpus=world, layers=len(census), elems=elems, lpt_balance=layout.balance,

@@ -160,6 +160,11 @@ int wt_plan_select_path(const WtPlan* plan);
  * caller still needs one cross-rank barrier before reading.  n_peers = 0 switches it off.  WT_E_UNSUPPORTED for plans
  * with layers on the generic tiled path or absolute thresholds (their kernels do not mirror stores). */
 int wt_plan_set_peers(WtPlan* plan, int n_peers, const int64_t* byte_deltas);
+/* The same over NVSwitch multicast (NVLS): byte_delta = (multicast mapping of the flat buffer, e.g. torch symmetric memory's
+ * multicast_ptr) - (this rank's buffer).  Every pruned weight is then stored ONCE more, with multimem.st, and the switch
+ * replicates it into every rank's buffer: a rank's NVLink egress is its shard instead of (ranks - 1) x its shard.
+ * Percentile plans whose layers run on the small-plane or level-0 select kernels (WT_E_UNSUPPORTED otherwise). */
+int wt_plan_set_multicast(WtPlan* plan, int64_t byte_delta);
 int wt_plan_phase_times(WtPlan* plan, int max_phases, float* ms, int* launches, char* names,
                         int name_stride);
 /* device address of the int64 [n_layers][4] result block {numel, nonzero, zeros, nonzero_before} */

@@ -68,8 +68,11 @@ def test_sharded_gpu_peer_store_equals_allgather(wtlib, oracle_lib, pg):
                                                        numpy_semantics='legacy_1_22', group=pg)
         b, cb, flat_b, _ = sharded.prune_model_sharded(ws, wavelet, level, 50.0, clamp_level=clamp,
                                                        numpy_semantics='legacy_1_22', group=pg, gather='peer_store')
+        c, cc, flat_c, _ = sharded.prune_model_sharded(ws, wavelet, level, 50.0, clamp_level=clamp,
+                                                       numpy_semantics='legacy_1_22', group=pg, gather='multicast')
         torch.cuda.synchronize()
         assert torch.equal(flat_a, flat_b) and np.array_equal(ca, cb)
+        assert torch.equal(flat_a, flat_c) and np.array_equal(ca, cc)      # NVLS multicast stores (peer stores without NVLS)
         for i, w in enumerate(host):
             want, _ = rf.multi_resolution_analysis([w], wavelet, level, 50.0, numpy_semantics='legacy_1_22', clamp_level=clamp)
             assert np.array_equal(b[i].cpu().numpy().view(np.uint32), want[0].numpy().view(np.uint32)), census[i][0]

@@ -50,6 +50,11 @@ def _worker(rank, world, port, wavelet, level, pct, clamp, out_q):
         ws = _weights()
         levels = [min(level, rf.calculate_max_level(w.shape, wavelet)) if clamp else level for w in ws]
         pruned, counts, flat, layout = sharded.prune_sharded(ws, levels, _oracle_fn(wavelet, pct, clamp))
+        # the pipelined variant (groups of layers, one gather per group) must give the same tensors and counts
+        pruned2, counts2 = sharded.prune_sharded_pipelined(ws, levels, _oracle_fn(wavelet, pct, clamp), n_groups=3)
+        assert np.array_equal(counts, counts2)
+        for a, b in zip(pruned, pruned2):
+            assert torch.equal(a, b)
         out_q.put((rank, [p.clone().numpy() for p in pruned], counts, layout.owner))
     finally:
         dist.destroy_process_group()
@@ -104,6 +109,9 @@ def test_layout_and_lpt():
     lay8 = sharded.ShardLayout(shapes, 8)
     assert max(lay8.load) == 2359296 and abs(lay8.balance - 0.5917) < 0.01
     assert workloads.lpt_assignment([5, 5, 4, 3, 3], 2) == [0, 1, 0, 1, 1]
+    groups = sharded.layer_groups(lay8.numels, 4)
+    assert sorted(sum(groups, [])) == list(range(len(shapes))) and len(groups) == 4
+    assert lay8.numels[groups[0][0]] == max(lay8.numels)      # large layers first
 
 
 class _FakePeerBuffer:

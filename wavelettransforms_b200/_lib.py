@@ -27,7 +27,7 @@ EXPORTS = [
     'wt_version', 'wt_last_error', 'wt_wavelet_lookup', 'wt_wavelet_filters', 'wt_dwt_max_level', 'wt_dwt_coeff_len',
     'wt_packed_shape', 'wt_percentile_plan', 'wt_plan_create', 'wt_plan_destroy', 'wt_plan_device_bytes',
     'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device',
-    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path', 'wt_plan_set_arithmetic',
+    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path', 'wt_plan_set_arithmetic', 'wt_plan_set_multicast',
     'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_select_abs_noalloc_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
     'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32',
 ]
@@ -66,6 +66,7 @@ def lib():
     L.wt_plan_set_timing.argtypes = [vp, ci]
     L.wt_plan_select_path.argtypes = [vp]
     L.wt_plan_set_arithmetic.argtypes = [vp, ci]
+    L.wt_plan_set_multicast.argtypes = [vp, i64]
     L.wt_plan_set_peers.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_int64)]
     L.wt_plan_phase_times.argtypes = [vp, ci, P(fl), P(ci), ctypes.c_char_p, ci]
     L.wt_dwt_prune_f32.argtypes = [P(WtLayerDesc), ci, ci, ci, ci, dbl, ci, vp, P(i64), P(i64), P(fl)]
@@ -184,6 +185,10 @@ class Plan:
         d = [int(x) for x in byte_deltas]
         arr = (ctypes.c_int64 * max(len(d), 1))(*d)
         check(lib().wt_plan_set_peers(self._h, len(d), arr))
+
+    def set_multicast(self, byte_delta):
+        """mirror every output store once through the multicast (NVLS) mapping at out + byte_delta"""
+        check(lib().wt_plan_set_multicast(self._h, int(byte_delta)))
 
     def set_arithmetic(self, name):
         """'faithful' (default: no FMA, the oracle's arithmetic) or 'fma_taporder' (named fast mode, see wtprune.h)"""

@@ -832,7 +832,25 @@ extern "C" int wt_plan_set_peers(WtPlan* P, int n_peers, const int64_t* byte_del
             WT_CHECK((byte_deltas[q] & 15) == 0, WT_E_INVALID, "wt_plan_set_peers: peer mappings must keep 16-byte alignment");
     }
     P->peers.n = n_peers;
+    P->peers.mc = 0;
     for (int q = 0; q < n_peers; ++q) P->peers.delta[q] = (long long)byte_deltas[q];
+    int rc = build_tables(P);
+    if (rc) return rc;
+    return upload_tables(P);
+}
+
+extern "C" int wt_plan_set_multicast(WtPlan* P, int64_t byte_delta) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    WT_CHECK(!P->host_io, WT_E_UNSUPPORTED, "wt_plan_set_multicast: host-I/O plans have no device output buffer to mirror");
+    WT_CHECK(P->thr_kind == WT_THRESHOLD_PERCENTILE, WT_E_UNSUPPORTED, "wt_plan_set_multicast: percentile plans only");
+    WT_CHECK((byte_delta & 15) == 0, WT_E_INVALID, "wt_plan_set_multicast: the multicast mapping must keep 16-byte alignment");
+    for (size_t i = 0; i < P->layers.size(); ++i)
+        WT_CHECK(P->path[i] != PATH_GENERIC && P->path[i] != PATH_FUSED, WT_E_UNSUPPORTED,
+                 "wt_plan_set_multicast: layer %d runs on a path whose kernels do not store through multicast addresses", (int)i);
+    memset(&P->peers, 0, sizeof(P->peers));
+    P->peers.n = 1;
+    P->peers.mc = 1;
+    P->peers.delta[0] = (long long)byte_delta;
     int rc = build_tables(P);
     if (rc) return rc;
     return upload_tables(P);

@@ -56,8 +56,19 @@ void wt_level_sizes(int n, int F, int mode, int level, int* sizes);
 #define WT_MAX_PEERS 7
 struct WtPeers {
     int n;
+    int mc;                         // 1: delta[0] is the distance to the MULTICAST mapping of the buffer (NVLS): one
+                                    // multimem.st per value, replicated to every rank inside the NVSwitch
     long long delta[WT_MAX_PEERS];  // byte distance from this rank's buffer to the peer's mapping of its own
 };
+#ifdef __CUDACC__
+// stores through a multicast (NVLS) address: the switch replicates the value into every GPU of the multicast group
+__device__ __forceinline__ void wt_mc_store4(void* p, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void wt_mc_store1(void* p, float v) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+#endif
 
 // ---- select (wt_select.cu) ----------------------------------------------------------------------
 // One job = one population whose order statistics are wanted: the explicit values x[0..n) plus

@@ -1026,6 +1026,16 @@ __device__ void phase3_hist_cand(const WtSelArgs& a, Shared& sh, int t_begin, in
 __device__ __noinline__ void mirror_span(const float* o, long long len, const WtPeers* __restrict__ peers) {
     const int np = __ldg(&peers->n);
     long long done = 0;
+    if (__ldg(&peers->mc)) {   // NVLS: one store per value to the multicast mapping
+        char* g = reinterpret_cast<char*>(const_cast<float*>(o)) + __ldg(&peers->delta[0]);
+        if ((reinterpret_cast<uintptr_t>(o) & 15u) == 0) {
+            const long long nvec = len >> 2;
+            for (long long v = threadIdx.x; v < nvec; v += T) wt_mc_store4(g + v * 16, reinterpret_cast<const float4*>(o)[v]);
+            done = nvec << 2;
+        }
+        for (long long i = done + threadIdx.x; i < len; i += T) wt_mc_store1(g + i * 4, o[i]);
+        return;
+    }
     if ((reinterpret_cast<uintptr_t>(o) & 15u) == 0) {
         const long long nvec = len >> 2;
         const float4* o4 = reinterpret_cast<const float4*>(o);

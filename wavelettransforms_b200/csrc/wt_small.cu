@@ -106,17 +106,40 @@ __device__ __forceinline__ void stage_out(float* g, const float* s, int cnt) {
     }
 }
 
-// stores the CTA's staged output tile at the same slot of every peer's buffer (plain global stores over NVLink)
+// Stores the CTA's staged output tile at the same slot of every peer's buffer over NVLink.  One elected thread hands the
+// copies to the TMA engine as bulk stores from the shared-memory tile the kernel holds anyway (cp.async.bulk, one per
+// peer), so the SM does not sit on NVLink stores: it only waits until the engine has READ the tile (wait_group.read)
+// before the CTA retires; the writes drain on their own and are complete when the kernel is.  (Round 1 issued plain
+// 16-byte stores from all threads: 7 sequential peer stores per element stalled the LSU, the peer-store mode won only
+// 0.10 ms over the all-gather at 8 GPUs.)  Misaligned tiles fall back to the thread stores.
 __device__ __noinline__ void mirror_tile(const float* s, float* out, const WtPeers* __restrict__ peers, int nel) {
     const int n = __ldg(&peers->n);
-    for (int q = 0; q < n; ++q) {
-        float* g = reinterpret_cast<float*>(reinterpret_cast<char*>(out) + __ldg(&peers->delta[q]));
+    const unsigned int bytes = (unsigned int)nel * 4u;
+    if (__ldg(&peers->mc)) {   // NVLS: one store per value to the multicast mapping, the switch replicates it to every rank
+        char* g = reinterpret_cast<char*>(out) + __ldg(&peers->delta[0]);
         if (((reinterpret_cast<uintptr_t>(g) & 15u) == 0) && (nel & 3) == 0) {
             for (int i = threadIdx.x; i < (nel >> 2); i += WT_SMALL_THREADS)
-                reinterpret_cast<float4*>(g)[i] = reinterpret_cast<const float4*>(s)[i];
+                wt_mc_store4(g + (size_t)i * 16, reinterpret_cast<const float4*>(s)[i]);
         } else {
-            for (int i = threadIdx.x; i < nel; i += WT_SMALL_THREADS) g[i] = s[i];
+            for (int i = threadIdx.x; i < nel; i += WT_SMALL_THREADS) wt_mc_store1(g + (size_t)i * 4, s[i]);
         }
+        return;
+    }
+    if (((reinterpret_cast<uintptr_t>(out) & 15u) == 0) && (bytes & 15u) == 0) {   // deltas are multiples of 16 (wt_plan_set_peers)
+        if (threadIdx.x == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            for (int q = 0; q < n; ++q) {
+                char* g = reinterpret_cast<char*>(out) + __ldg(&peers->delta[q]);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g), "r"(smem_u32(s)), "r"(bytes) : "memory");
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+        return;
+    }
+    for (int q = 0; q < n; ++q) {
+        float* g = reinterpret_cast<float*>(reinterpret_cast<char*>(out) + __ldg(&peers->delta[q]));
+        for (int i = threadIdx.x; i < nel; i += WT_SMALL_THREADS) g[i] = s[i];
     }
 }
 

@@ -79,7 +79,9 @@ def prune_device_tensors(xs: List[torch.Tensor], levels: Sequence[int], wavelet:
         arith = arithmetic or config.arithmetic
         if arith != 'faithful':
             plan.set_arithmetic(arith)
-        if peer_deltas:
+        if isinstance(peer_deltas, tuple) and peer_deltas and peer_deltas[0] == 'multicast':
+            plan.set_multicast(peer_deltas[1])
+        elif peer_deltas:
             plan.set_peers(peer_deltas)
         s = _stream_ptr()
         plan.run(s)

@@ -81,6 +81,9 @@ class PeerBuffer:
             raise RuntimeError('symmetric memory: the local mapping is not the tensor itself')
         # byte distance from this rank's buffer to each peer's mapping of its own
         self.deltas = [int(p) - mine for r, p in enumerate(self.handle.buffer_ptrs) if r != self.rank]
+        # NVSwitch multicast mapping of the same buffer (0 when the fabric / driver has no NVLS): one multimem.st reaches every rank
+        mc = int(getattr(self.handle, 'multicast_ptr', 0) or 0)
+        self.multicast_delta = (mc - mine) if mc else None
         self.flat.zero_()               # slot padding reads as zero, like the torch.zeros buffer of the NCCL mode
         torch.cuda.current_stream().synchronize()
         self.handle.barrier()           # nobody stores into a peer that is still clearing
@@ -98,12 +101,14 @@ def prune_sharded(weights: List[torch.Tensor], levels: Sequence[int], prune_fn: 
     numel, nonzero after, zeros after, nonzero before; flat buffer; layout).  gather=False skips both
     collectives (prune-only timing): then only the owned layers' views are meaningful.  gather='peer_store'
     (CUDA, world > 1): the flat buffer lives in symmetric memory and the kernels store into every rank's copy
-    themselves; one device-side barrier replaces the all-gather (pass `peer_buffer` to reuse an allocation)."""
+    themselves; one device-side barrier replaces the all-gather (pass `peer_buffer` to reuse an allocation).
+    gather='multicast': the same through the NVSwitch multicast mapping of the buffer (one multimem.st per value, replicated
+    inside the switch: a rank sends its shard once instead of world - 1 times); peer stores where there is no NVLS."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     layout = layout or ShardLayout([w.shape for w in weights], world)
     dev = weights[0].device if weights else torch.device('cpu')
-    peer = gather == 'peer_store' and world > 1
+    peer = gather in ('peer_store', 'multicast') and world > 1
     if peer:
         if peer_buffer is None:
             peer_buffer = PeerBuffer(layout, dev, group)
@@ -128,7 +133,9 @@ def prune_sharded(weights: List[torch.Tensor], levels: Sequence[int], prune_fn: 
         ok = 1
         try:
             if mine:
-                c = prune_fn(xs, outs, my_levels, peer_deltas=peer_buffer.deltas)
+                use_mc = gather == 'multicast' and peer_buffer.multicast_delta is not None
+                c = prune_fn(xs, outs, my_levels,
+                             peer_deltas=('multicast', peer_buffer.multicast_delta) if use_mc else peer_buffer.deltas)
         except NotImplementedError:
             ok = 0
         flag = torch.tensor([ok], dtype=torch.int32, device=dev)
@@ -150,6 +157,65 @@ def prune_sharded(weights: List[torch.Tensor], levels: Sequence[int], prune_fn: 
         dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
     pruned = [layout.view(flat, i) for i in range(len(weights))]
     return pruned, counts.cpu().numpy(), flat, layout
+
+
+def layer_groups(numels: Sequence[int], n_groups: int) -> List[List[int]]:
+    """Layers in descending size, cut into `n_groups` runs of about equal total size (so the first group holds the few
+    largest layers): the unit of the pipelined gather.  Deterministic from the shapes: every rank computes the same."""
+    order = sorted(range(len(numels)), key=lambda i: (-numels[i], i))
+    total = sum(numels)
+    groups, acc, cur = [], 0, []
+    for i in order:
+        cur.append(i)
+        acc += numels[i]
+        if len(groups) < n_groups - 1 and acc >= total * (len(groups) + 1) / n_groups:
+            groups.append(cur)
+            cur = []
+    if cur:
+        groups.append(cur)
+    return groups
+
+
+def prune_sharded_pipelined(weights: List[torch.Tensor], levels: Sequence[int], prune_fn: PruneFn, n_groups: int = 4,
+                            group: Optional[dist.ProcessGroup] = None):
+    """prune_sharded with the gather OVERLAPPED with the pruning: the layers are dealt into `n_groups` size-ordered groups,
+    each with its own LPT assignment and flat buffer; as soon as the kernels of group g are enqueued its all-gather starts
+    on a side stream while group g + 1 is pruned (round 1 gathered once, after the last kernel: at 8 GPUs the gather was
+    60 % of the step with nothing to hide behind).  Same results as prune_sharded; returns (pruned tensors, counts)."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    dev = weights[0].device if weights else torch.device('cpu')
+    cuda = dev.type == 'cuda'
+    pruned: List[Optional[torch.Tensor]] = [None] * len(weights)
+    counts_local = torch.zeros((len(weights), 4), dtype=torch.int64)
+    side = torch.cuda.Stream(device=dev) if cuda and world > 1 else None
+    main = torch.cuda.current_stream(dev) if cuda else None
+    for idx in layer_groups([int(w.numel()) for w in weights], n_groups):
+        layout = ShardLayout([weights[i].shape for i in idx], world)
+        flat = torch.zeros(world * layout.shard_elems, dtype=torch.float32, device=dev)
+        mine = layout.owned(rank)
+        if mine:
+            xs = [weights[idx[k]].contiguous() for k in mine]
+            outs = [layout.view(flat, k) for k in mine]
+            c = prune_fn(xs, outs, [int(levels[idx[k]]) for k in mine])
+            counts_local[[idx[k] for k in mine]] = torch.from_numpy(np.asarray(c, dtype=np.int64))
+        if world > 1:
+            my_shard = flat[rank * layout.shard_elems:(rank + 1) * layout.shard_elems]
+            if side is not None:
+                side.wait_stream(main)                 # this group's kernels are enqueued: its gather may start behind them
+                with torch.cuda.stream(side):
+                    dist.all_gather_into_tensor(flat, my_shard, group=group)
+                flat.record_stream(side)
+            else:
+                dist.all_gather_into_tensor(flat, my_shard.clone(), group=group)
+        for k, i in enumerate(idx):
+            pruned[i] = layout.view(flat, k)
+    if side is not None:
+        main.wait_stream(side)
+    counts = counts_local.to(dev)
+    if world > 1:
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
+    return pruned, counts.cpu().numpy()
 
 
 def prune_model_sharded(weights: List[torch.Tensor], wavelet: str, level: int, percentile: float, *,
