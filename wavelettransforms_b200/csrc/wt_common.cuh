@@ -176,7 +176,7 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
 // only re-points the scratch-relative fields (histograms, state, flags) at another zeroed block of the same layout
 void wt_select_rebind(WtSelArgs* a, void* scratch, int n_jobs);
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
-#define WT_SEL_SAMPLED_MIN_TILES 10240  // 40 Mi keys
+#define WT_SEL_SAMPLED_MIN_TILES 5500   // 22.5 M keys = 90 MB: beyond that the keys are not L2-resident between the radix path's two passes
 #ifndef WT_SEL_TAIL_MAX
 #define WT_SEL_TAIL_MAX 32768  // longest candidate list one CTA finishes alone (three L2-resident passes; measured
                                // against the grid-wide passes: wins at 20 K keys, loses at 50 K)

@@ -1307,10 +1307,12 @@ void wt_select_balance(const WtSelJob* jobs, int n_jobs, int n_tiles, int grid, 
     for (int c = used; c < grid; ++c) job_out[c] = n_jobs > 0 ? n_jobs - 1 : 0;
 }
 
-// Which path a launch over n_tiles tiles takes.  Measured on one B200 (tools/select_probe.py, tools/bank_probe.py): the
-// sampled path saves one of the two full passes but runs one or two more phases, each worth 6..8 us of barrier,
-// scan and flush latency whatever the size; it loses by 10 % at 31 M keys (ResNet-18 coefficients) and wins by 25 %
-// at 67 M.  WT_SELECT_PATH=radix|sampled (read at every launch) overrides.
+// Which path a launch over n_tiles tiles takes.  Measured on one B200 (tools/select_probe.py, tools/bank_probe.py,
+// tools/fused_probe.py): the sampled path saves one of the two full passes but runs one or two more phases, each worth
+// 6..8 us of barrier, scan and flush latency whatever the size.  What decides is whether the keys stay in the 126 MB L2
+// between the radix path's two passes: 79 MB of haar coefficients or 45 MB of raw weights do (radix wins: 138 vs 144 us,
+// 63 vs 81 us), 100 MB (ResNet-18 bior2.2 L3) and 124 MB (bior4.4 L5) do not (sampled wins: 152 vs 165 us, 205 vs 212 us,
+// long candidate lists included).  WT_SELECT_PATH=radix|sampled (read at every launch) overrides.
 int wt_select_path(int n_tiles, int short_lists) {
     const char* e = getenv("WT_SELECT_PATH");
     if (e && !strcmp(e, "radix")) return 1;
