@@ -150,7 +150,8 @@ int wt_plan_set_timing(WtPlan* plan, int enable);
 #define WT_ARITH_FMA_TAPORDER 1
 int wt_plan_set_arithmetic(WtPlan* plan, int arithmetic);
 /* which select the plan's percentile threshold runs through: 0 sampled (one full pass + short candidate lists),
- * 1 radix (three passes), 2 fused recompute kernels, -1 none (absolute threshold / empty plan).  Reporting aid. */
+ * 1 radix (three passes), 2 fused recompute kernels, 3 precompacted (the analysis kernels count and compact while they hold
+ * the coefficients, the select only finishes the candidate lists), -1 none (absolute threshold / empty plan).  Reporting aid. */
 int wt_plan_select_path(const WtPlan* plan);
 /* Layer-sharded runs (north star: layers dealt to the GPUs of a box, the pruned state reassembled on every rank).
  * Every rank's output tensors live in a flat buffer of ONE layout that is mapped into all peers (CUDA VMM /

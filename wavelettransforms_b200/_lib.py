@@ -212,7 +212,7 @@ class Plan:
 
     @property
     def select_path(self):
-        return {0: 'sampled', 1: 'radix', 2: 'fused', -1: None}[lib().wt_plan_select_path(self._h)]
+        return {0: 'sampled', 1: 'radix', 2: 'fused', 3: 'precompacted', -1: None}[lib().wt_plan_select_path(self._h)]
 
     @property
     def device_bytes(self):

@@ -219,6 +219,7 @@ struct WtPlan {
 
     std::vector<SmallClass> small;
     std::vector<FusedClass> fused;
+    bool precompact = false;  // percentile plans with small-plane layers: the analysis kernels do the select's streaming work
     int arithmetic = 0;  // 0: faithful (no FMA, the oracle's arithmetic), 1: fma_taporder (wt_plan_set_arithmetic)
     bool legacy_zero = false;  // some launch still accumulates into the zeroed block (generic path, legacy kernels)
     std::vector<WtGenericLayer> generic;
@@ -344,6 +345,10 @@ static int build_tables(WtPlan* P) {
             j.abs_threshold = (float)P->thr_value;
             j.use_abs = pct ? 0 : 1;
             j.peers = P->peers;
+            j.sel_job = pct ? (int)P->sel_jobs.size() : -1;   // the select job of this tensor is pushed below, in the same iteration
+            j.sample_shift = wt_select_sample_shift(P->ncoef[i]);
+            j.cand = P->d_cand[i];
+            j.cand_cap = P->cand_cap[i];
             cls->n_tiles += j.n_tiles;
             cls->jobs.push_back(j);
         } else if (P->path[i] == PATH_GENERIC) {
@@ -373,6 +378,7 @@ static int build_tables(WtPlan* P) {
             j.cand = P->d_cand[i];
             j.cand_cap = P->cand_cap[i];
             j.sample_shift = wt_select_sample_shift(j.n);
+            if (P->precompact && P->path[i] != PATH_SMALL) j.sample_shift = -1;   // not covered by the analysis kernels: radix passes
             if (l0) j.peers = P->peers;
             j.tile_begin = sel_tiles;
             const long long nt = (j.n + WT_SEL_TILE - 1) / WT_SEL_TILE;
@@ -387,6 +393,7 @@ static int build_tables(WtPlan* P) {
     P->sel_args.n_tiles = sel_tiles;
     P->sel_args.any_apply = any_apply ? 1 : 0;
     P->sel_args.short_lists = wt_select_predict_short(P->sel_jobs.data(), (int)P->sel_jobs.size());
+    P->sel_args.precompacted = P->precompact ? 1 : 0;
     return WT_OK;
 }
 
@@ -772,6 +779,14 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
         }
         if (!ok) { wt_set_error("creating the plan's auxiliary streams failed: %s", cudaGetErrorString(cudaGetLastError())); wt_plan_destroy(P); return WT_E_CUDA; }
     }
+    // WT_PRECOMPACT=1 (percentile plans with small-plane layers): sample pass + bracket + count / compact inside the analysis
+    // kernels, so that the select never streams the spilled coefficients.  Bit-exact, and opt-in because it measured
+    // slower than the select's own sampled pass at every model size tried: the ballots and the
+    // staging double the analysis kernel and the two extra launches sit on the critical path.
+    {
+        const char* pre = getenv("WT_PRECOMPACT");
+        P->precompact = threshold_kind == WT_THRESHOLD_PERCENTILE && !P->small.empty() && pre != nullptr && pre[0] != '\0' && pre[0] != '0';
+    }
     rc = build_tables(P);
     if (!rc) rc = upload_tables(P);
     if (!rc) {
@@ -953,12 +968,36 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         c.parity ^= 1;
         ++launches;
     }
+    const bool pre = P->precompact && !P->sel_jobs.empty();
+    if (pre) {
+        // the select's S0 on the analysis side: 12-bit histogram of one tile in 2^shift, per class; then ONE small kernel
+        // turns every job's sample histogram into its bracket (all classes' histograms are complete: join first)
+        for (size_t k = 0; k < P->small.size(); ++k) {
+            auto& c = P->small[k];
+            snprintf(label, sizeof(label), "small_sample_%dx%d", c.H, c.W);
+            mark(label);
+            rc = wt_small_sample_launch(c.H, c.W, P->bank, P->arithmetic, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->sel_args.hist1,
+                                        P->sel_args.hist1c, class_stream(k));
+            if (rc) return rc;
+            if (c.n_tiles) ++launches;
+        }
+        if ((rc = join())) return rc;
+        mark("select_bracket");
+        rc = wt_select_bracket_launch(P->sel_args, stream);
+        if (rc) return rc;
+        ++launches;
+        if ((rc = fork())) return rc;
+    }
     for (size_t k = 0; k < P->small.size(); ++k) {
         auto& c = P->small[k];
         snprintf(label, sizeof(label), "small_analysis_%dx%d", c.H, c.W);
         mark(label);
-        rc = wt_small_analysis_launch(c.H, c.W, P->bank, P->arithmetic, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev,
-                                      class_stream(k));
+        if (pre)
+            rc = wt_small_analysis_compact_launch(c.H, c.W, P->bank, P->arithmetic, c.jobs_dev, (int)c.jobs.size(), c.n_tiles,
+                                                  P->counts_dev, P->sel_args.state, class_stream(k));
+        else
+            rc = wt_small_analysis_launch(c.H, c.W, P->bank, P->arithmetic, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev,
+                                          class_stream(k));
         if (rc) return rc;
         if (c.n_tiles) ++launches;
     }
@@ -1045,6 +1084,7 @@ extern "C" int wt_plan_select_path(const WtPlan* P) {
     if (P->thr_kind != WT_THRESHOLD_PERCENTILE) return -1;
     for (const auto& c : P->fused) if (c.n_select > 0) return 2;
     if (P->sel_jobs.empty()) return -1;
+    if (P->precompact) return 3;
     return wt_select_path(P->sel_args.n_tiles, P->sel_args.short_lists);
 }
 

@@ -147,6 +147,9 @@ struct WtSelArgs {
     float* thresholds;          // [n_layers]
     long long* counts;          // [n_layers][4] {numel, nonzero, zeros, nonzero_before}
     int any_apply;              // at least one job has out != nullptr
+    int precompacted;           // 1: the small-plane analysis kernels have done S0 / S1 for the jobs with sample_shift >= 0 (sample
+                                // histogram -> wt_select_bracket_launch -> count + compact while the coefficients were in registers):
+                                // the select starts at the tail; jobs with sample_shift < 0 (level 0, generic path) take the radix passes
     char* zero_next;            // nullable: a block this launch zeroes for the NEXT run of the plan (two scratch blocks alternate,
     unsigned long long zero_next_bytes;  // so a step enqueues no memset); multiple of 16 bytes
 };
@@ -176,6 +179,9 @@ void wt_select_bind(WtSelArgs* a, void* scratch, int n_jobs);
 // only re-points the scratch-relative fields (histograms, state, flags) at another zeroed block of the same layout
 void wt_select_rebind(WtSelArgs* a, void* scratch, int n_jobs);
 int wt_select_launch(const WtSelArgs& args, cudaStream_t stream);
+// precompacted launches: one CTA per job turns the sample histogram (hist1 / hist1c) into the bracket of 12-bit bins the
+// analysis kernels compact (state.lo_bin / n_bins, 0 bins = none); jobs with sample_shift < 0 are handed to the radix passes
+int wt_select_bracket_launch(const WtSelArgs& args, cudaStream_t stream);
 #define WT_SEL_SAMPLED_MIN_TILES 5500   // 22.5 M keys = 90 MB: beyond that the keys are not L2-resident between the radix path's two passes
 #ifndef WT_SEL_TAIL_MAX
 #define WT_SEL_TAIL_MAX 32768  // longest candidate list one CTA finishes alone (three L2-resident passes; measured
@@ -299,6 +305,13 @@ struct WtSmallJob {
     int n_tiles;
     float abs_threshold;
     int use_abs;       // 1: compare against abs_threshold, 0: against thresholds[layer]
+    // precompacted select (percentile plans): the analysis kernel counts the keys below the job's bracket and appends the keys
+    // inside it to the select job's candidate list while they are in registers
+    int sel_job;       // index of the tensor's select job (-1: none)
+    int sample_shift;  // the sample pass analyses one tile out of every 2^shift
+    unsigned int* cand;
+    unsigned int cand_cap;
+    int pad;
     WtPeers peers;     // synthesis: the output tile is also stored at out + delta of every peer
 };
 
@@ -309,5 +322,11 @@ int wt_small_ncoef(int H, int W, int level);
 // fma: 0 faithful arithmetic (multiply, then add: the oracle's and the reference's), 1 fma_taporder (same tap order, fused)
 int wt_small_analysis_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
                              long long* counts, cudaStream_t stream);
+// precompacted select: (1) sample pass -- 12-bit histogram of |c| over one tile in 2^shift of every job, into the select's
+// hist1 / hist1c of the job; (2) after wt_select_bracket_launch: the analysis with count + compact against state[sel_job]
+int wt_small_sample_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                           unsigned long long* hist1, unsigned long long* hist1c, cudaStream_t stream);
+int wt_small_analysis_compact_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                                     long long* counts, WtSelState* state, cudaStream_t stream);
 int wt_small_synthesis_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
                               const float* thresholds, long long* counts, cudaStream_t stream);

@@ -549,7 +549,7 @@ __device__ __forceinline__ unsigned int cand_boundary(unsigned int n_c, int t, i
 
 // ================================ sampled path ===========================================================
 // true when job j runs (or has been handed to) the radix path
-__device__ __forceinline__ bool radix_job(const WtSelArgs& a, int j) { return a.path != 0 || __ldcg(&a.state[j].failed) != 0; }
+__device__ __forceinline__ bool radix_job(const WtSelArgs& a, int j) { return a.path == 1 || __ldcg(&a.state[j].failed) != 0; }
 
 // explicit-key ranks of the two order statistics: the implicit zeros sort first, so population rank k is
 // explicit rank k - zeros (clamped: a rank inside the zeros needs no explicit key at all, see final_keys)
@@ -1139,13 +1139,15 @@ __global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs 
         for (unsigned long long i = (unsigned long long)blockIdx.x * T + threadIdx.x; i < n16; i += (unsigned long long)gridDim.x * T)
             z[i] = make_int4(0, 0, 0, 0);
     }
-    if (a.path == 0) {
-        phase_s0_sample(a, sh, t_begin, t_end, acc);
-        acc.stamp(1);
-        grid.sync();
-        phase_s1_compact(a, sh, t_begin, t_end, acc);
-        acc.stamp(2);
-        grid.sync();
+    if (a.path != 1) {
+        if (a.path == 0) {   // path 2 (precompacted): the analysis kernels did S0 and S1 while they held the coefficients
+            phase_s0_sample(a, sh, t_begin, t_end, acc);
+            acc.stamp(1);
+            grid.sync();
+            phase_s1_compact(a, sh, t_begin, t_end, acc);
+            acc.stamp(2);
+            grid.sync();
+        }
         phase_tail(a, sh);
         acc.stamp(3);
         grid.sync();
@@ -1161,22 +1163,48 @@ __global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs 
             }
         }
     }
-    if (a.path != 0 || __ldcg(a.fail_flag) != 0) {  // grid-uniform: the flag was final before the last barrier
+    if (a.path == 1 || __ldcg(a.fail_flag) != 0) {  // grid-uniform: the flag was final before the last barrier
         acc.begin();
         phase1_hist(a, sh, t_begin, t_end, acc);
-        if (a.path != 0) acc.stamp(1);  // radix-only launches reuse the sampled path's boundary slots: arrival at the
+        if (a.path == 1) acc.stamp(1);  // radix-only launches reuse the sampled path's boundary slots: arrival at the
         grid.sync();                    // barrier after P1 / P2 / P3 (mean vs max over CTAs = imbalance)
         phase2_hist_compact(a, sh, t_begin, t_end, acc);
-        if (a.path != 0) acc.stamp(2);
+        if (a.path == 1) acc.stamp(2);
         grid.sync();
         phase3_hist_cand(a, sh, t_begin, t_end, acc);
-        if (a.path != 0) acc.stamp(3);
+        if (a.path == 1) acc.stamp(3);
         grid.sync();
         acc.end(15);
     }
     acc.stamp(5);
     phase4_apply(a, sh, t_begin, t_end, acc);
     acc.stamp(6);
+}
+
+// Precompacted launches: one CTA per job turns the job's SAMPLE histogram (written by the analysis kernels' sample pass)
+// into the bracket the analysis kernels then compact -- exactly what every CTA of phase_s1_compact works out for itself.
+// Jobs the analysis kernels do not cover (sample_shift < 0: level-0 tensors, generic-path layers) are handed to the radix
+// passes of the same select launch.
+__global__ void __launch_bounds__(WT_SEL_THREADS) wt_select_bracket_kernel(WtSelArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Shared& sh = *reinterpret_cast<Shared*>(smem_raw);
+    const int j = blockIdx.x;
+    const WtSelJob job = a.jobs[j];
+    WtSelState* st = &a.state[j];
+    if (job.sample_shift < 0 || job.cand == nullptr) {
+        if (threadIdx.x == 0) { st->failed = 1; st->n_bins = 0u; *a.fail_flag = 1; }
+        return;
+    }
+    unsigned long long e0, e1;
+    explicit_ranks(job, e0, e1);
+    const Found f = scan_find_two_level(a.hist1c + (size_t)j * WT_SEL_COARSE, global_hist<1>(a, j), 0ull, e0, e1, sh, job.n);
+    unsigned int n_bins = f.d1 - f.d0 + 1u;
+    if (f.d1 < f.d0) n_bins = 0u;
+    if (threadIdx.x == 0) {
+        st->lo_bin = f.d0;
+        st->n_bins = n_bins;
+        if (n_bins > 16u) *a.wide_flag = 1;
+    }
 }
 
 __global__ void __launch_bounds__(256) wt_apply_threshold_kernel(const float* __restrict__ x, float* __restrict__ out,
@@ -1351,7 +1379,7 @@ int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
     if (rc) return rc;
     const size_t smem = sizeof(Shared);
     WtSelArgs a = args;
-    a.path = wt_select_path(a.n_tiles, a.short_lists);
+    a.path = a.precompacted ? 2 : wt_select_path(a.n_tiles, a.short_lists);
     {
         const char* e = getenv("WT_SEL_TAIL_MAX");  // tuning aid, read at every launch
         a.tail_max = e ? (unsigned int)atoi(e) : (unsigned int)WT_SEL_TAIL_MAX;
@@ -1359,6 +1387,21 @@ int wt_select_launch(const WtSelArgs& args, cudaStream_t stream) {
     int do_apply = a.any_apply;  // jobs without `out` skip the apply loop inside P4
     void* params[] = {&a, &do_apply};
     WT_CUDA(cudaLaunchCooperativeKernel((const void*)wt_select_kernel, dim3(grid), dim3(WT_SEL_THREADS), params, smem, stream));
+    return WT_OK;
+}
+
+int wt_select_bracket_launch(const WtSelArgs& args, cudaStream_t stream) {
+    if (args.n_jobs <= 0) return WT_OK;
+    static bool attr_set[64] = {false};
+    WtDeviceInfo di;
+    int rc = wt_device_info(&di);
+    if (rc) return rc;
+    if (di.device >= 0 && di.device < 64 && !attr_set[di.device]) {
+        WT_CUDA(cudaFuncSetAttribute(wt_select_bracket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Shared)));
+        attr_set[di.device] = true;
+    }
+    wt_select_bracket_kernel<<<args.n_jobs, WT_SEL_THREADS, sizeof(Shared), stream>>>(args);
+    WT_CUDA(cudaGetLastError());
     return WT_OK;
 }
 

@@ -146,32 +146,73 @@ __device__ __noinline__ void mirror_tile(const float* s, float* out, const WtPee
 // ------------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------------
-template <int H, int W, int F, class Z>
+// MODE 0: wavedec2 of every plane, coefficients to the coefficient-major workspace.
+// MODE 1: the same, and -- for the precompacted select (wt_select.cu) -- every coefficient is held against the job's bracket
+//         while it is in a register: keys below it are counted, keys inside it are appended to the select job's candidate
+//         list (warp-private staging, one global atomic per ~224 keys), so the select never streams the coefficients.
+// MODE 2: the sample pass that precedes it: one tile out of every 2^shift of the job, 12-bit histogram of |c| (key bits
+//         30..19) into the select job's hist1 / hist1c; nothing else is written.
+constexpr int SM_WFLUSH = 224, SM_WSTAGE = SM_WFLUSH + 32;
+
+template <int H, int W, int F, class Z, int MODE>
 __global__ void __launch_bounds__(WT_SMALL_THREADS)
 wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __restrict__ jobs, int n_jobs,
-                         long long* __restrict__ counts) {
+                         long long* __restrict__ counts, WtSelState* state, unsigned long long* hist1, unsigned long long* hist1c) {
     constexpr int HW = H * W;
     __shared__ __align__(16) float s_in[WT_SMALL_THREADS * HW];
     __shared__ unsigned long long bar;
     __shared__ unsigned int s_cnt[WT_SMALL_THREADS / 32];
+    __shared__ unsigned int s_x[MODE == 2 ? WT_SEL_BINS1 : 1];
     const int tile = blockIdx.x;
     const int j = find_small_job(jobs, n_jobs, tile);
     const WtSmallJob job = jobs[j];
+    if (MODE == 2) {   // CTA-uniform early exits: jobs without a select, tiles outside the sample
+        const int s = job.sample_shift;
+        if (s < 0 || job.sel_job < 0) return;
+        if (s > 0) {
+            const int t = tile - job.tile_begin, g = t >> s;
+            int avail = job.n_tiles - (g << s);
+            if (avail > (1 << s)) avail = 1 << s;
+            if (t != (g << s) + (int)(((unsigned int)g * 5u + 3u) % (unsigned int)avail)) return;
+        }
+        for (int b = threadIdx.x; b < WT_SEL_BINS1; b += WT_SMALL_THREADS) s_x[b] = 0u;
+    }
     const long long p0 = (long long)(tile - job.tile_begin) * WT_SMALL_THREADS;
     const long long left = job.batch - p0;
     const int cnt = left < WT_SMALL_THREADS ? (int)left : WT_SMALL_THREADS;
     stage_in<HW>(s_in, job.in + p0 * HW, cnt, &bar);
+    const bool valid = (int)threadIdx.x < cnt;
     unsigned int nz = 0;
-    if ((int)threadIdx.x < cnt) {
-        float x[HW];
+    float x[HW];
 #pragma unroll
-        for (int i = 0; i < HW; ++i) {
-            x[i] = s_in[threadIdx.x * HW + i];
-            nz += (x[i] != 0.0f);
+    for (int i = 0; i < HW; ++i) {
+        x[i] = valid ? s_in[threadIdx.x * HW + i] : 0.0f;   // lanes without a plane run the transform on zeros: the warp votes below need them
+        nz += (x[i] != 0.0f);
+    }
+    if (MODE == 2) {
+        auto put = [&](int, float v) {
+            if (valid) atomicAdd(&s_x[(__float_as_uint(v) & 0x7fffffffu) >> 19], 1u);
+        };
+        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::analyze(x, job.level, bk, put);
+        __syncthreads();
+        unsigned long long* gh = hist1 + (size_t)job.sel_job * WT_SEL_BINS1;
+        unsigned long long* gc = hist1c + (size_t)job.sel_job * WT_SEL_COARSE;
+        for (int b = threadIdx.x; b < WT_SEL_BINS1; b += WT_SMALL_THREADS) {   // a warp covers 32 consecutive fine bins = one coarse bin
+            const unsigned int v = s_x[b];
+            if (v) atomicAdd(&gh[b], (unsigned long long)v);
+            unsigned int sum = v;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) sum += __shfl_down_sync(0xffffffffu, sum, d);
+            if ((threadIdx.x & 31) == 0 && sum) atomicAdd(&gc[b >> 5], (unsigned long long)sum);
         }
-        float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
-        const long long stride = job.batch;
-        auto put = [&](int idx, float v) { cbase[(long long)idx * stride] = v; };
+        return;
+    }
+    float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
+    const long long stride = job.batch;
+    {
+        auto put = [&](int idx, float v) {
+            if (valid) cbase[(long long)idx * stride] = v;
+        };
         SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::analyze(x, job.level, bk, put);
     }
     // nonzeros of the input (dwt_pruning_NoEntropy.py:58) and numel
@@ -185,6 +226,98 @@ wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __
         atomicAdd(reinterpret_cast<unsigned long long*>(counts + (size_t)job.layer * 4 + 3), t);
         if (tile == job.tile_begin) counts[(size_t)job.layer * 4] = job.batch * HW;
     }
+}
+
+// MODE 1 as a kernel of its own: a CTA walks SM_TPC consecutive tiles of the class and carries its warp-private staging and
+// its counters from tile to tile, so the job's global counters see one atomic per CTA and job instead of one per warp and
+// tile (measured: with one tile per CTA the returning atomics on s_count made the haar analysis 3.7x slower).
+constexpr int SM_TPC = 8;
+
+template <int H, int W, int F, class Z>
+__global__ void __launch_bounds__(WT_SMALL_THREADS)
+wt_small_analysis_compact_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __restrict__ jobs, int n_jobs, int n_tiles,
+                                 long long* __restrict__ counts, WtSelState* state) {
+    constexpr int HW = H * W;
+    __shared__ __align__(16) float s_in[WT_SMALL_THREADS * HW];
+    __shared__ unsigned long long bar;
+    __shared__ unsigned int s_cnt[WT_SMALL_THREADS / 32];
+    __shared__ unsigned int s_x[(WT_SMALL_THREADS / 32) * SM_WSTAGE];
+    const int tile0 = blockIdx.x * SM_TPC, tile1 = min(n_tiles, tile0 + SM_TPC);
+    const int lane = threadIdx.x & 31;
+    const unsigned int lt = (1u << lane) - 1u;
+    unsigned int* wbuf = s_x + (threadIdx.x >> 5) * SM_WSTAGE;
+    int j = find_small_job(jobs, n_jobs, tile0);
+    WtSmallJob job = jobs[j];
+    WtSelState* st = nullptr;
+    unsigned int lo = 0, width = 0, wc = 0, nb = 0, nz = 0;   // wc is warp-uniform
+    auto open_job = [&]() {
+        st = job.sel_job >= 0 ? state + job.sel_job : nullptr;
+        const unsigned int n_bins = st ? __ldcg(&st->n_bins) : 0u, lo_bin = st ? __ldcg(&st->lo_bin) : 0u;   // CTA-uniform
+        // a bracket that starts at bin 0 leaves the exact zeros out of the list (wt_select.cu, phase_s1_compact)
+        lo = (lo_bin << 19) | (lo_bin == 0u ? 1u : 0u);
+        width = n_bins ? ((lo_bin + n_bins) << 19) - lo : 0u;
+    };
+    auto flush = [&]() {
+        unsigned int gbase = 0;
+        if (lane == 0) gbase = atomicAdd(&st->s_count, wc);
+        gbase = __shfl_sync(0xffffffffu, gbase, 0);
+        __syncwarp();
+        for (unsigned int i = lane; i < wc; i += 32)
+            if (gbase + i < job.cand_cap) job.cand[gbase + i] = wbuf[i];
+        __syncwarp();
+        wc = 0;
+    };
+    auto close_job = [&]() {   // the CTA's share of the job: staged keys, keys below the bracket, nonzero inputs
+        if (width) {
+            if (wc) flush();
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) nb += __shfl_down_sync(0xffffffffu, nb, d);
+            if (lane == 0 && nb) atomicAdd(&st->below, (unsigned long long)nb);
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) nz += __shfl_down_sync(0xffffffffu, nz, d);
+        if (lane == 0 && nz) atomicAdd(reinterpret_cast<unsigned long long*>(counts + (size_t)job.layer * 4 + 3), (unsigned long long)nz);
+        nb = nz = 0;
+    };
+    open_job();
+    for (int tile = tile0; tile < tile1; ++tile) {
+        if (tile >= job.tile_begin + job.n_tiles) {
+            close_job();
+            job = jobs[++j];
+            open_job();
+        }
+        __syncthreads();   // every thread has its plane of the previous tile in registers: s_in and the mbarrier are free
+        const long long p0 = (long long)(tile - job.tile_begin) * WT_SMALL_THREADS;
+        const long long left = job.batch - p0;
+        const int cnt = left < WT_SMALL_THREADS ? (int)left : WT_SMALL_THREADS;
+        stage_in<HW>(s_in, job.in + p0 * HW, cnt, &bar);
+        const bool valid = (int)threadIdx.x < cnt;
+        float x[HW];
+#pragma unroll
+        for (int i = 0; i < HW; ++i) {
+            x[i] = valid ? s_in[threadIdx.x * HW + i] : 0.0f;   // lanes without a plane run the transform on zeros: the warp votes need them
+            nz += (x[i] != 0.0f);
+        }
+        float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
+        const long long stride = job.batch;
+        auto put = [&](int idx, float v) {
+            if (valid) cbase[(long long)idx * stride] = v;
+            if (width) {
+                const unsigned int key = __float_as_uint(v) & 0x7fffffffu;
+                nb += (valid && key < lo);
+                const bool hit = valid && (key - lo < width);
+                const unsigned int ballot = __ballot_sync(0xffffffffu, hit);
+                if (ballot) {
+                    if (hit) wbuf[wc + __popc(ballot & lt)] = key;
+                    wc += __popc(ballot);
+                    if (wc > SM_WFLUSH) flush();
+                }
+            }
+        };
+        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::analyze(x, job.level, bk, put);
+        if (tile == job.tile_begin && threadIdx.x == 0) counts[(size_t)job.layer * 4] = job.batch * HW;
+    }
+    close_job();
 }
 
 template <int H, int W, int F, class Z>
@@ -258,14 +391,18 @@ TapMasks tap_masks(const WtBank& b) {
     X(6, 0x23, 0x20, 0x20, 0x23)      \
     X(10, 0x203, 0x200, 0x200, 0x203)
 
-template <int H, int W>
-int launch_analysis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, int n_tiles, long long* counts,
-                       cudaStream_t stream) {
+template <int H, int W, int MODE>
+int launch_analysis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, int n_tiles, long long* counts, WtSelState* state,
+                       unsigned long long* hist1, unsigned long long* hist1c, cudaStream_t stream) {
     const TapMasks m = tap_masks(bank);
 #define WT_SPEC(FL, DL, DH, RL, RH)                                                                                       \
     if (bank.F == FL && m.dl == DL && m.dh == DH && m.rl == RL && m.rh == RH) {                                         \
-        wt_small_analysis_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH, kFma>>                                                     \
-            <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts);                                       \
+        if (MODE == 1)                                                                                                   \
+            wt_small_analysis_compact_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH, kFma>>                                   \
+                <<<(n_tiles + SM_TPC - 1) / SM_TPC, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, n_tiles, counts, state); \
+        else                                                                                                             \
+            wt_small_analysis_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH, kFma>, MODE == 1 ? 0 : MODE>                     \
+                <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts, state, hist1, hist1c);             \
         WT_CUDA(cudaGetLastError());                                                                                     \
         return WT_OK;                                                                                                    \
     }
@@ -273,7 +410,12 @@ int launch_analysis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, i
 #undef WT_SPEC
 #define WT_CASE(FL)                                                                                                       \
     case FL:                                                                                                              \
-        wt_small_analysis_kernel<H, W, FL, ZeroTaps<0, 0, 0, 0, kFma>><<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts); \
+        if (MODE == 1)                                                                                                    \
+            wt_small_analysis_compact_kernel<H, W, FL, ZeroTaps<0, 0, 0, 0, kFma>>                                        \
+                <<<(n_tiles + SM_TPC - 1) / SM_TPC, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, n_tiles, counts, state); \
+        else                                                                                                              \
+            wt_small_analysis_kernel<H, W, FL, ZeroTaps<0, 0, 0, 0, kFma>, MODE == 1 ? 0 : MODE>                          \
+                <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts, state, hist1, hist1c);              \
         break;
     switch (bank.F) {
         WT_CASE(2) WT_CASE(4) WT_CASE(6) WT_CASE(8) WT_CASE(10) WT_CASE(12) WT_CASE(18)
@@ -321,12 +463,14 @@ int launch_synthesis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, 
 #define WT_SMALL_ENTRY(name) name##_fma
 #else
 #define WT_SMALL_ENTRY(name) name##_faithful
-int wt_small_analysis_launch_faithful(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
-                                      long long* counts, cudaStream_t stream);
+int wt_small_analysis_mode_launch_faithful(int H, int W, int mode, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs,
+                                           int n_tiles, long long* counts, WtSelState* state, unsigned long long* hist1,
+                                           unsigned long long* hist1c, cudaStream_t stream);
+int wt_small_analysis_mode_launch_fma(int H, int W, int mode, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs,
+                                      int n_tiles, long long* counts, WtSelState* state, unsigned long long* hist1,
+                                      unsigned long long* hist1c, cudaStream_t stream);
 int wt_small_synthesis_launch_faithful(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
                                        const float* thresholds, long long* counts, cudaStream_t stream);
-int wt_small_analysis_launch_fma(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
-                                 long long* counts, cudaStream_t stream);
 int wt_small_synthesis_launch_fma(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
                                   const float* thresholds, long long* counts, cudaStream_t stream);
 
@@ -346,10 +490,23 @@ int wt_small_ncoef(int H, int W, int level) {
     return n + h * w;
 }
 
+static int analysis_mode(int H, int W, int mode, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                         long long* counts, WtSelState* state, unsigned long long* hist1, unsigned long long* hist1c,
+                         cudaStream_t stream) {
+    if (fma) return wt_small_analysis_mode_launch_fma(H, W, mode, bank, jobs_dev, n_jobs, n_tiles, counts, state, hist1, hist1c, stream);
+    return wt_small_analysis_mode_launch_faithful(H, W, mode, bank, jobs_dev, n_jobs, n_tiles, counts, state, hist1, hist1c, stream);
+}
 int wt_small_analysis_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
                              long long* counts, cudaStream_t stream) {
-    if (fma) return wt_small_analysis_launch_fma(H, W, bank, jobs_dev, n_jobs, n_tiles, counts, stream);
-    return wt_small_analysis_launch_faithful(H, W, bank, jobs_dev, n_jobs, n_tiles, counts, stream);
+    return analysis_mode(H, W, 0, bank, fma, jobs_dev, n_jobs, n_tiles, counts, nullptr, nullptr, nullptr, stream);
+}
+int wt_small_sample_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                           unsigned long long* hist1, unsigned long long* hist1c, cudaStream_t stream) {
+    return analysis_mode(H, W, 2, bank, fma, jobs_dev, n_jobs, n_tiles, nullptr, nullptr, hist1, hist1c, stream);
+}
+int wt_small_analysis_compact_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
+                                     long long* counts, WtSelState* state, cudaStream_t stream) {
+    return analysis_mode(H, W, 1, bank, fma, jobs_dev, n_jobs, n_tiles, counts, state, nullptr, nullptr, stream);
 }
 int wt_small_synthesis_launch(int H, int W, const WtBank& bank, int fma, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
                               const float* thresholds, long long* counts, cudaStream_t stream) {
@@ -358,13 +515,18 @@ int wt_small_synthesis_launch(int H, int W, const WtBank& bank, int fma, const W
 }
 #endif
 
-int WT_SMALL_ENTRY(wt_small_analysis_launch)(int H, int W, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs, int n_tiles,
-                                             long long* counts, cudaStream_t stream) {
+int WT_SMALL_ENTRY(wt_small_analysis_mode_launch)(int H, int W, int mode, const WtBank& bank, const WtSmallJob* jobs_dev, int n_jobs,
+                                                  int n_tiles, long long* counts, WtSelState* state, unsigned long long* hist1,
+                                                  unsigned long long* hist1c, cudaStream_t stream) {
     if (n_tiles <= 0) return WT_OK;
-    if (H == 1 && W == 1) return launch_analysis_hw<1, 1>(bank, jobs_dev, n_jobs, n_tiles, counts, stream);
-    if (H == 3 && W == 3) return launch_analysis_hw<3, 3>(bank, jobs_dev, n_jobs, n_tiles, counts, stream);
-    if (H == 5 && W == 5) return launch_analysis_hw<5, 5>(bank, jobs_dev, n_jobs, n_tiles, counts, stream);
-    if (H == 7 && W == 7) return launch_analysis_hw<7, 7>(bank, jobs_dev, n_jobs, n_tiles, counts, stream);
+#define WT_HW(h, w)                                                                                                            \
+    if (H == h && W == w) {                                                                                                    \
+        if (mode == 0) return launch_analysis_hw<h, w, 0>(bank, jobs_dev, n_jobs, n_tiles, counts, state, hist1, hist1c, stream); \
+        if (mode == 1) return launch_analysis_hw<h, w, 1>(bank, jobs_dev, n_jobs, n_tiles, counts, state, hist1, hist1c, stream); \
+        return launch_analysis_hw<h, w, 2>(bank, jobs_dev, n_jobs, n_tiles, counts, state, hist1, hist1c, stream);             \
+    }
+    WT_HW(1, 1) WT_HW(3, 3) WT_HW(5, 5) WT_HW(7, 7)
+#undef WT_HW
     wt_set_error("small-plane path: unsupported plane %dx%d", H, W);
     return WT_E_UNSUPPORTED;
 }
