@@ -139,6 +139,18 @@ int wt_plan_results(WtPlan* plan, void* stream, int64_t* counts, int64_t* nonzer
  * per-kernel durations; leave it off on the production path (each event costs ~1 us of stream time).
  */
 int wt_plan_set_timing(WtPlan* plan, int enable);
+/*
+ * CUDA graphs.  enable = 1: the first two calls of wt_plan_run (one per alternating scratch block) capture the plan's
+ * launch sequence -- every kernel of the run, the forks onto the plan's class streams and the joins back -- into a
+ * cudaGraph; later runs replay it with ONE cudaGraphLaunch on `stream`.  Results are those of the plain run, bit for bit.
+ * The reference has no counterpart (it calls PyWavelets / NumPy layer by layer: ResNet/dwt_pruning.py:67-77); this
+ * is for callers that run one plan many times (threshold sweeps re-create plans and gain nothing).  The graphs are
+ * dropped by anything that changes what a run launches (wt_plan_set_io / _set_peers / _set_multicast / _set_arithmetic)
+ * and bypassed while phase timing is on.  A stream that cannot be captured (the legacy default stream) makes the plan
+ * fall back to plain launches silently -- same results.  Device plans only run through it; a host-I/O plan forwards
+ * the switch to the device plans of its layer groups.  Default: off, or the value of WT_GRAPH when the plan is created.
+ */
+int wt_plan_set_graph(WtPlan* plan, int enable);
 /* Arithmetic of the DWT multiply-adds.  WT_ARITH_FAITHFUL (default): fp32 multiply, then fp32 add, no FMA,
  * the order of oracle/dwt_oracle.c -- the arithmetic every bit-exactness claim of this library refers to.
  * WT_ARITH_FMA_TAPORDER: the same taps in the same order with every multiply-add fused into one FFMA (one rounding
@@ -168,8 +180,14 @@ int wt_plan_set_peers(WtPlan* plan, int n_peers, const int64_t* byte_deltas);
 int wt_plan_set_multicast(WtPlan* plan, int64_t byte_delta);
 int wt_plan_phase_times(WtPlan* plan, int max_phases, float* ms, int* launches, char* names,
                         int name_stride);
-/* device address of the int64 [n_layers][4] result block {numel, nonzero, zeros, nonzero_before} */
+/* device address of the int64 [n_layers][4] result block of the LAST run: columns 1..3 = {nonzero, zeros,
+ * nonzero_before} (column 0 is scratch: numel is known on the host).  Percentile plans alternate between two blocks,
+ * so ask again after every wt_plan_run.  Valid in stream order after the run; nothing is synchronised. */
 int wt_plan_counts_device(WtPlan* plan, const int64_t** counts_dev);
+/* device address of the float32 [n_layers] thresholds the strict `<` compares against (percentile plans: written by
+ * the run; absolute plans: the constant).  With wt_plan_counts_device this lets a caller sweep thresholds or chain
+ * device-side logic without the stream synchronisation wt_plan_results implies. */
+int wt_plan_thresholds_device(WtPlan* plan, const float** thresholds_dev);
 
 /* one-shot convenience: create + run + results + destroy (device I/O). */
 int wt_dwt_prune_f32(const WtLayerDesc* layers, int n_layers, int wavelet_id, int mode,

@@ -26,8 +26,8 @@ class WtLayerDesc(ctypes.Structure):
 EXPORTS = [
     'wt_version', 'wt_last_error', 'wt_wavelet_lookup', 'wt_wavelet_filters', 'wt_dwt_max_level', 'wt_dwt_coeff_len',
     'wt_packed_shape', 'wt_percentile_plan', 'wt_plan_create', 'wt_plan_destroy', 'wt_plan_device_bytes',
-    'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device',
-    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path', 'wt_plan_set_arithmetic', 'wt_plan_set_multicast',
+    'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device', 'wt_plan_thresholds_device',
+    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path', 'wt_plan_set_arithmetic', 'wt_plan_set_multicast', 'wt_plan_set_graph',
     'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_select_abs_noalloc_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
     'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32',
 ]
@@ -63,7 +63,9 @@ def lib():
     L.wt_plan_run.argtypes = [vp, vp]
     L.wt_plan_results.argtypes = [vp, vp, P(i64), P(i64), P(fl)]
     L.wt_plan_counts_device.argtypes = [vp, P(vp)]
+    L.wt_plan_thresholds_device.argtypes = [vp, P(vp)]
     L.wt_plan_set_timing.argtypes = [vp, ci]
+    L.wt_plan_set_graph.argtypes = [vp, ci]
     L.wt_plan_select_path.argtypes = [vp]
     L.wt_plan_set_arithmetic.argtypes = [vp, ci]
     L.wt_plan_set_multicast.argtypes = [vp, i64]
@@ -180,6 +182,14 @@ class Plan:
         c = np.array(counts[:3 * self.n], dtype=np.int64).reshape(self.n, 3)
         return c, np.array(nzb[:self.n], dtype=np.int64), np.array(thr[:self.n], dtype=np.float32)
 
+    def device_result_pointers(self):
+        """(address of the int64 [n][4] block {scratch, nonzero, zeros, nonzero_before} of the last run, address of the
+        float32 [n] thresholds); valid in stream order after run(), nothing is synchronised"""
+        c, t = ctypes.c_void_p(), ctypes.c_void_p()
+        check(lib().wt_plan_counts_device(self._h, ctypes.byref(c)))
+        check(lib().wt_plan_thresholds_device(self._h, ctypes.byref(t)))
+        return int(c.value or 0), int(t.value or 0)
+
     def set_peers(self, byte_deltas):
         """mirror every output store at out + delta for each delta (peer mappings of the same flat buffer layout)"""
         d = [int(x) for x in byte_deltas]
@@ -195,6 +205,10 @@ class Plan:
         if name not in ARITHMETICS:
             raise ValueError(f"unknown arithmetic '{name}' (expected one of {sorted(ARITHMETICS)})")
         check(lib().wt_plan_set_arithmetic(self._h, ARITHMETICS[name]))
+
+    def set_graph(self, enable=True):
+        """replay the plan's launch sequence as a CUDA graph from the third run on (wtprune.h: wt_plan_set_graph)"""
+        check(lib().wt_plan_set_graph(self._h, 1 if enable else 0))
 
     def set_timing(self, enable=True):
         check(lib().wt_plan_set_timing(self._h, 1 if enable else 0))

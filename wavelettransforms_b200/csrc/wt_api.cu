@@ -180,6 +180,7 @@ struct FusedClass {
     char* scratch[2] = {nullptr, nullptr};
     size_t scratch_bytes = 0;
     int parity = 0;                // scratch block the next run uses (the run zeroes the other one for the run after)
+    int run_parity = 0;            // ... and the one the run being enqueued uses
     int total_items = 0, total_s_items = 0, n_select = 0;
     double share = 1.0;            // this class's part of the bytes of all fused classes of the plan
     unsigned long long* stamps_dev = nullptr;  // WT_FUSED_STAMPS tuning aid
@@ -253,6 +254,12 @@ struct WtPlan {
     std::vector<cudaEvent_t> ev_in, ev_k;
     cudaEvent_t ev_start = nullptr, ev_done = nullptr;
     int timing = 0;
+    // wt_plan_set_graph: the launch sequence of a run, captured once per scratch parity and replayed
+    int use_graph = 0;
+    unsigned long long run_count = 0;
+    cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};
+    int graph_launches[2] = {0, 0};
+    int graph_failed = 0;          // capture refused once (legacy default stream, ...): enqueue directly from then on
     std::vector<cudaEvent_t> events;
     std::vector<std::string> phase_names;
     std::vector<int> phase_launches;
@@ -433,6 +440,8 @@ static int upload_tables(WtPlan* P) {
     return WT_OK;
 }
 
+static void drop_graphs(WtPlan* P);
+
 extern "C" int wt_plan_destroy(WtPlan* P) {
     if (!P) return WT_OK;
     for (WtPlan* c : P->children) wt_plan_destroy(c);
@@ -442,6 +451,7 @@ extern "C" int wt_plan_destroy(WtPlan* P) {
     if (P->ev_done) cudaEventDestroy(P->ev_done);
     if (P->s_in) cudaStreamDestroy(P->s_in);
     if (P->s_out) cudaStreamDestroy(P->s_out);
+    for (int g = 0; g < 2; ++g) if (P->graph_exec[g]) cudaGraphExecDestroy(P->graph_exec[g]);
     for (cudaEvent_t e : P->events) cudaEventDestroy(e);
     for (cudaEvent_t e : P->ev_join) cudaEventDestroy(e);
     if (P->ev_fork) cudaEventDestroy(P->ev_fork);
@@ -784,14 +794,20 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     // slower than the select's own sampled pass at every model size tried: the ballots and the
     // staging double the analysis kernel and the two extra launches sit on the critical path.
     {
+        const char* gr = getenv("WT_GRAPH");
+        P->use_graph = gr != nullptr && gr[0] != '\0' && gr[0] != '0';
+    }
+    {
         const char* pre = getenv("WT_PRECOMPACT");
         P->precompact = threshold_kind == WT_THRESHOLD_PERCENTILE && !P->small.empty() && pre != nullptr && pre[0] != '\0' && pre[0] != '0';
     }
     rc = build_tables(P);
     if (!rc) rc = upload_tables(P);
     if (!rc) {
-        e = cudaMemset(P->thresholds_dev, 0, (size_t)std::max(n_layers, 1) * sizeof(float));
-        if (e != cudaSuccess) { wt_set_error("cudaMemset failed: %s", cudaGetErrorString(e)); rc = WT_E_CUDA; }
+        // percentile plans: the select writes the thresholds; absolute plans: the constant, for wt_plan_thresholds_device
+        std::vector<float> t0((size_t)std::max(n_layers, 1), threshold_kind == WT_THRESHOLD_ABSOLUTE ? (float)threshold_value : 0.0f);
+        e = cudaMemcpy(P->thresholds_dev, t0.data(), t0.size() * sizeof(float), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { wt_set_error("cudaMemcpy failed: %s", cudaGetErrorString(e)); rc = WT_E_CUDA; }
     }
     if (rc) { wt_plan_destroy(P); return rc; }
     *plan_out = P;
@@ -825,6 +841,7 @@ extern "C" int wt_plan_set_io(WtPlan* P, const WtLayerDesc* layers, int n_layers
         }
     }
     if (P->host_io) return WT_OK;
+    drop_graphs(P);
     int rc = build_tables(P);
     if (rc) return rc;
     return upload_tables(P);
@@ -849,6 +866,7 @@ extern "C" int wt_plan_set_peers(WtPlan* P, int n_peers, const int64_t* byte_del
     P->peers.n = n_peers;
     P->peers.mc = 0;
     for (int q = 0; q < n_peers; ++q) P->peers.delta[q] = (long long)byte_deltas[q];
+    drop_graphs(P);
     int rc = build_tables(P);
     if (rc) return rc;
     return upload_tables(P);
@@ -866,15 +884,41 @@ extern "C" int wt_plan_set_multicast(WtPlan* P, int64_t byte_delta) {
     P->peers.n = 1;
     P->peers.mc = 1;
     P->peers.delta[0] = (long long)byte_delta;
+    drop_graphs(P);
     int rc = build_tables(P);
     if (rc) return rc;
     return upload_tables(P);
 }
 
-extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
-    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    if (P->host_io) return run_host_pipeline(P, stream);
+// the captured graphs hold kernel parameters: anything that rebuilds the tables or changes what a run launches drops them
+static void drop_graphs(WtPlan* P) {
+    for (int g = 0; g < 2; ++g) {
+        if (P->graph_exec[g]) cudaGraphExecDestroy(P->graph_exec[g]);
+        P->graph_exec[g] = nullptr;
+    }
+    P->graph_failed = 0;
+}
+
+// which of the two alternating scratch blocks the run being enqueued uses (host state only: a replayed graph needs it too)
+static void advance_run_state(WtPlan* P) {
+    // Percentile plans with a select launch enqueue no memset: two blocks alternate and the select kernel of this run
+    // zeroes the block of the next one (every kernel that accumulates into the block runs in stream order after it).
+    if (P->thr_kind == WT_THRESHOLD_PERCENTILE && !P->sel_jobs.empty()) {
+        P->zero_block = P->zero_blocks[P->zpar];
+        P->counts_dev = reinterpret_cast<long long*>(P->zero_block + P->counts_off);
+        wt_select_rebind(&P->sel_args, P->zero_block, (int)P->sel_jobs.size());
+        P->sel_args.counts = P->counts_dev;
+        P->sel_args.zero_next = P->zero_blocks[P->zpar ^ 1];
+        P->sel_args.zero_next_bytes = P->zero_bytes;
+        P->zpar ^= 1;
+    }
+    for (auto& c : P->fused) {
+        c.run_parity = c.parity;
+        c.parity ^= 1;
+    }
+}
+
+static int plan_enqueue(WtPlan* P, cudaStream_t stream) {
     const int n = (int)P->layers.size();
     int launches = 0;
     P->n_phases = 0;
@@ -898,18 +942,8 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     char label[64];
     // counts / select scratch of the launches that accumulate with atomics (generic path, legacy kernels); the fused
     // classes zero their own scratch for the next run and store their counts, so a fused-only plan enqueues no memset
-    // Percentile plans with a select launch enqueue no memset either: two blocks alternate and the select kernel of
-    // this run zeroes the block of the next one (every kernel that accumulates into the block runs in stream order after it).
+    // (percentile plans with a select launch: advance_run_state)
     const bool self_zero = P->thr_kind == WT_THRESHOLD_PERCENTILE && !P->sel_jobs.empty();
-    if (self_zero) {
-        P->zero_block = P->zero_blocks[P->zpar];
-        P->counts_dev = reinterpret_cast<long long*>(P->zero_block + P->counts_off);
-        wt_select_rebind(&P->sel_args, P->zero_block, (int)P->sel_jobs.size());
-        P->sel_args.counts = P->counts_dev;
-        P->sel_args.zero_next = P->zero_blocks[P->zpar ^ 1];
-        P->sel_args.zero_next_bytes = P->zero_bytes;
-        P->zpar ^= 1;
-    }
     const size_t counts_off = P->counts_off;
     const bool split_zero = !self_zero && P->legacy_zero && !P->timing && !P->aux.empty() && counts_off > 0 && counts_off < P->zero_bytes;
     if (P->legacy_zero && !self_zero) {
@@ -952,7 +986,7 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         fa.jobs = c.jobs_dev;
         fa.n_jobs = (int)c.jobs.size(); fa.n_select = c.n_select;
         fa.total_items = c.total_items; fa.total_s_items = c.total_s_items;
-        fa.scratch = c.scratch[c.parity]; fa.scratch_next = c.scratch[c.parity ^ 1]; fa.scratch_bytes = c.scratch_bytes;
+        fa.scratch = c.scratch[c.run_parity]; fa.scratch_next = c.scratch[c.run_parity ^ 1]; fa.scratch_bytes = c.scratch_bytes;
         fa.thresholds = P->thresholds_dev; fa.counts = P->counts_dev;
         cudaStream_t cs = class_stream(P->small.size() + k);
         if (getenv("WT_FUSED_STAMPS")) {
@@ -965,7 +999,6 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
         rc = wt_fused_launch(c.H, c.W, P->bank, P->arithmetic, fa, reserve, k + 1 == P->fused.size() ? 1.0 : c.share, cs, &grid);
         if (rc) return rc;
         reserve += 2 * grid;
-        c.parity ^= 1;
         ++launches;
     }
     const bool pre = P->precompact && !P->sel_jobs.empty();
@@ -1058,6 +1091,60 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     return WT_OK;
 }
 
+extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (P->host_io) return run_host_pipeline(P, stream);
+    const int par = (int)(P->run_count & 1ull);   // both alternations flip once per run
+    advance_run_state(P);
+    ++P->run_count;
+    const bool graphable = P->use_graph && !P->graph_failed && !P->timing && P->stamps_dev == nullptr && getenv("WT_FUSED_STAMPS") == nullptr;
+    if (!graphable) return plan_enqueue(P, stream);
+    if (!P->graph_exec[par]) {
+        // capture this parity's launch sequence (the class streams fork from and join back into `stream`, so they are
+        // branches of the same graph); nothing runs during the capture, the replay below is the run
+        if (cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+            cudaGetLastError();   // e.g. the legacy default stream cannot be captured
+            P->graph_failed = 1;
+            return plan_enqueue(P, stream);
+        }
+        const int rc = plan_enqueue(P, stream);
+        cudaGraph_t g = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(stream, &g);
+        if (rc || e != cudaSuccess || g == nullptr) {
+            if (g) cudaGraphDestroy(g);
+            cudaGetLastError();
+            P->graph_failed = 1;
+            if (rc) return rc;
+            return plan_enqueue(P, stream);
+        }
+        cudaGraphExec_t x = nullptr;
+        const cudaError_t ei = cudaGraphInstantiate(&x, g, 0);
+        cudaGraphDestroy(g);
+        if (ei != cudaSuccess || x == nullptr) {
+            cudaGetLastError();
+            P->graph_failed = 1;
+            return plan_enqueue(P, stream);
+        }
+        P->graph_exec[par] = x;
+        P->graph_launches[par] = P->n_launches;
+    }
+    WT_CUDA(cudaGraphLaunch(P->graph_exec[par], stream));
+    P->n_launches = P->graph_launches[par];
+    return WT_OK;
+}
+
+extern "C" int wt_plan_set_graph(WtPlan* P, int enable) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    for (WtPlan* c : P->children) {
+        int rc = wt_plan_set_graph(c, enable);
+        if (rc) return rc;
+    }
+    P->use_graph = enable ? 1 : 0;
+    if (!enable) drop_graphs(P);
+    return WT_OK;
+}
+
 extern "C" int wt_plan_set_arithmetic(WtPlan* P, int arithmetic) {
     WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
     WT_CHECK(arithmetic == WT_ARITH_FAITHFUL || arithmetic == WT_ARITH_FMA_TAPORDER, WT_E_INVALID, "unknown arithmetic %d", arithmetic);
@@ -1075,6 +1162,7 @@ extern "C" int wt_plan_set_arithmetic(WtPlan* P, int arithmetic) {
         if (rc) return rc;
     }
     P->arithmetic = arithmetic;
+    drop_graphs(P);
     return WT_OK;
 }
 
@@ -1117,6 +1205,13 @@ extern "C" int wt_plan_counts_device(WtPlan* P, const int64_t** counts_dev) {
     WT_CHECK(P != nullptr && counts_dev != nullptr, WT_E_INVALID, "NULL argument");
     WT_CHECK(!P->host_io, WT_E_UNSUPPORTED, "host-I/O plans keep their counts per layer group: use wt_plan_results");
     *counts_dev = reinterpret_cast<const int64_t*>(P->counts_dev);
+    return WT_OK;
+}
+
+extern "C" int wt_plan_thresholds_device(WtPlan* P, const float** thresholds_dev) {
+    WT_CHECK(P != nullptr && thresholds_dev != nullptr, WT_E_INVALID, "NULL argument");
+    WT_CHECK(!P->host_io, WT_E_UNSUPPORTED, "host-I/O plans keep their thresholds per layer group: use wt_plan_results");
+    *thresholds_dev = P->thresholds_dev;
     return WT_OK;
 }
 

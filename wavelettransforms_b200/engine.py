@@ -56,12 +56,41 @@ class PruneResult:
         self.launches = launches
 
 
+class DevicePruneResult:
+    """prune_device_tensors(..., device_results=True): the same numbers as PruneResult, left on the GPU.  No D2H copy
+    has been made and the tensors are valid in stream order; .host() does the one D2H + sync when the caller wants it.
+    (Tearing the one-shot plan down still waits for the device inside cudaFree; a caller that must not block at all
+    keeps a _lib.Plan alive and reads Plan.device_result_pointers() after each run.)"""
+    __slots__ = ('outputs', 'numel', 'counts_dev', 'thresholds_dev', 'launches')
+
+    def __init__(self, outputs, numel, counts_dev, thresholds_dev, launches):
+        self.outputs = outputs                # list of device tensors
+        self.numel = numel                    # int64 [n] (host: known without running anything)
+        self.counts_dev = counts_dev          # int64 CUDA tensor [n, 3]: nonzero after, zeros after, nonzero before
+        self.thresholds_dev = thresholds_dev  # float32 CUDA tensor [n]
+        self.launches = launches
+
+    def host(self) -> PruneResult:
+        c = self.counts_dev.cpu().numpy()
+        counts = np.stack([self.numel, c[:, 0], c[:, 1]], axis=1) if len(self.numel) else np.zeros((0, 3), dtype=np.int64)
+        return PruneResult(self.outputs, counts, c[:, 2].copy(), self.thresholds_dev.cpu().numpy(), self.launches)
+
+
+class _DeviceBlock:
+    """a raw device address as a __cuda_array_interface__ object, so torch can view it without a copy"""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {'shape': tuple(shape), 'typestr': typestr, 'data': (int(ptr), False), 'version': 2}
+
+
 def prune_device_tensors(xs: List[torch.Tensor], levels: Sequence[int], wavelet: str, mode: str, threshold_kind: int,
                          threshold_value: float, numpy_semantics: Optional[str] = None,
                          outs: Optional[List[torch.Tensor]] = None,
-                         peer_deltas: Optional[Sequence[int]] = None, arithmetic: Optional[str] = None) -> PruneResult:
+                         peer_deltas: Optional[Sequence[int]] = None, arithmetic: Optional[str] = None,
+                         device_results: bool = False):
     """xs: contiguous float32 CUDA tensors.  One plan, one launch sequence for the whole group.  peer_deltas: the
-    kernels also store every output at out + delta (symmetric-memory mappings of the same buffer on the other ranks)."""
+    kernels also store every output at out + delta (symmetric-memory mappings of the same buffer on the other ranks).
+    device_results: return a DevicePruneResult (counts and thresholds stay on the GPU, no stream synchronisation)."""
     sem = numpy_semantics or config.numpy_semantics
     for lv in levels:
         if lv < 0:
@@ -85,8 +114,22 @@ def prune_device_tensors(xs: List[torch.Tensor], levels: Sequence[int], wavelet:
             plan.set_peers(peer_deltas)
         s = _stream_ptr()
         plan.run(s)
-        counts, nzb, thr = plan.results(s)
         launches = plan.num_launches
+        if device_results:
+            n = len(items)
+            numel = np.array([b * h * w for _, _, b, h, w, _ in items], dtype=np.int64)
+            if n == 0:
+                dev = cuda_device()
+                return DevicePruneResult(outs, numel, torch.zeros((0, 3), dtype=torch.int64, device=dev),
+                                         torch.zeros(0, dtype=torch.float32, device=dev), launches)
+            cp, tp = plan.device_result_pointers()
+            dev = xs[0].device
+            # copies on the current stream, enqueued before plan.close() frees the plan's block (cudaFree waits for them)
+            c4 = torch.as_tensor(_DeviceBlock(cp, (n, 4), '<i8'), device=dev)
+            counts_dev = c4[:, 1:].clone()
+            thresholds_dev = torch.as_tensor(_DeviceBlock(tp, (n,), '<f4'), device=dev).clone()
+            return DevicePruneResult(outs, numel, counts_dev, thresholds_dev, launches)
+        counts, nzb, thr = plan.results(s)
     finally:
         plan.close()
     return PruneResult(outs, counts, nzb, thr, launches)
