@@ -183,6 +183,26 @@ def test_generic_path_prune_flows(mods, mode):
         assert gp == wp
 
 
+@pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
+@pytest.mark.parametrize('wavelet,level', [('db4', 3), ('haar', 2), ('bior4.4', 2), ('coif3', 1)])
+def test_generic_large_plane_prune_flows(mods, wavelet, level, mode):
+    """whole prune flow (transform, select, threshold on load, inverse) on planes that take the fixed-geometry kernels:
+    aligned (16-byte staging, threshold swept as float4) and odd row strides (scalar staging), both threshold kinds"""
+    dp, ne, rf = mods['dp'], mods['ne'], mods['rf']
+    g = torch.Generator().manual_seed(23)
+    for shape in ((1, 1024, 1280), (2, 1030, 1101)):
+        w = torch.randn(shape, generator=g) * 0.02
+        got, gz = dp.multi_resolution_analysis([w], wavelet, level, 83.0, mode, clamp_level=False)
+        want, wz = rf.multi_resolution_analysis([w], wavelet, level, 83.0, mode=mode, numpy_semantics='legacy_1_22',
+                                                clamp_level=False)
+        assert_bit_equal(got[0], want[0], f'large pct {wavelet} {shape} {mode}')
+        assert gz == wz
+        got, gp = ne.multi_resolution_analysis([w], wavelet, level, 0.015, mode)
+        want, wp = rf.multi_resolution_analysis_absolute([w], wavelet, level, 0.015, mode)
+        assert_bit_equal(got[0], want[0], f'large abs {wavelet} {shape} {mode}')
+        assert gp == wp
+
+
 def test_golden_fixture(mods):
     dp = mods['dp']
     with open(os.path.join(ROOT, 'tests', 'golden', 'oracle_golden.json')) as f:

@@ -10,6 +10,9 @@
 // pass writes its intermediate to shared memory, the second pass writes the result.  Arithmetic and
 // accumulation order are those of oracle/dwt_oracle.c (fp32, no FMA).
 #include <cstdlib>
+#include <cstring>
+
+#include <cuda.h>   // CUtensorMap and the cuTensorMapEncodeTiled prototype only: the entry point is fetched at run time
 
 #include "wt_generic.cuh"
 
@@ -29,6 +32,40 @@ __device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
                  : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// ---- TMA tensor-map tile loads (cp.async.bulk.tensor, SASS UTMALDG) ------------------------------------------------
+// The fixed-geometry kernels stage a whole tile with ONE instruction: a 3-D box {columns, rows, 1 plane} of the strided
+// view, written densely into shared memory, out-of-bounds elements filled with zeros by the hardware.  Tiles that
+// touch the plane's border then overwrite the out-of-bounds part with the boundary extension (wrap / reflect) from
+// plain loads: the map cannot express it, and only ~9 % of the tiles of a 4096 x 4096 plane are border tiles.
+__device__ __forceinline__ unsigned int smem_u32(const void* p) { return (unsigned int)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect(unsigned long long* bar, unsigned int bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned int parity) {
+    unsigned int ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_box(float* smem_dst, const CUtensorMap* map, int col, int row, int plane, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(map), "r"(col), "r"(row), "r"(plane), "r"(smem_u32(bar))
+                 : "memory");
+}
 
 __device__ __forceinline__ int pmodi(int a, int m) {
     int r = a % m;
@@ -54,6 +91,7 @@ struct AnaParams {
     int h, w, h2, w2, mode;
     int t2r, t2c, tiles_r, tiles_c, pb, ir, ic;
     int ics;  // staged row width: ic + up to 3 columns so that the staged region starts 16-byte aligned, rounded to 4
+    int use_tma;  // fixed kernel: the tile comes in through the tensor map
 };
 
 constexpr int NWARP = GEN_THREADS / 32;
@@ -170,13 +208,14 @@ template <int F> struct FxGeom {
     static constexpr int IR = 2 * FX_T2R + F - 2, IC = 2 * FX_T2C + F - 2, ICS = (IC + 3 + 3) & ~3;
     static constexpr int SMEM_FLOATS_ = IR * ICS + 2 * FX_T2R * FX_LW;
     static_assert((IC + 1) / 2 <= FX_HALF, "tile wider than the de-interleaved row");
-    static_assert(SMEM_FLOATS_ <= SMEM_FLOATS, "fixed tile does not fit");
+    static_assert(SMEM_FLOATS_ + 4 <= SMEM_FLOATS, "fixed tile (+ its mbarrier) does not fit");
 };
 
 template <int F, int MODE>
 __global__ void __launch_bounds__(GEN_THREADS)
-wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ AnaParams P) {
-    extern __shared__ float smem[];
+wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ AnaParams P,
+                                 const __grid_constant__ CUtensorMap tmap) {
+    extern __shared__ __align__(128) float smem[];
     using G = FxGeom<F>;
     constexpr int IR = G::IR, IC = G::IC, ICS = G::ICS;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -194,7 +233,25 @@ wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid
     const int rows_valid = min(FX_T2R, P.h2 - o0), cols_valid = min(FX_T2C, P.w2 - c0);
     const bool vec = c_al >= 0 && c_al + ICS <= P.w && (P.in.rstride & 3) == 0 && (P.in.pstride & 3) == 0 &&
                      (reinterpret_cast<uintptr_t>(P.in.p) & 15u) == 0;
-    {
+    if (P.use_tma) {
+        unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + G::SMEM_FLOATS_);   // past the tile buffers
+        if (threadIdx.x == 0) {
+            mbar_init(bar, 1);
+            mbar_expect(bar, IR * ICS * (unsigned)sizeof(float));
+            tma_load_box(s_in, &tmap, c_al, r_start, (int)pl, bar);
+        }
+        __syncthreads();   // the barrier is initialised for everybody
+        mbar_wait(bar, 0);
+        if (r_start < 0 || r_start + IR > P.h || c_al < 0 || c_al + ICS > P.w) {   // border tile: the zero fill becomes the extension
+            const float* __restrict__ plane = P.in.p + pl * P.in.pstride;
+            for (int i = threadIdx.x; i < IR * ICS; i += GEN_THREADS) {
+                const int rr = i / ICS, cc = i - rr * ICS;
+                const int r = r_start + rr, c = c_al + cc;
+                if ((unsigned)r >= (unsigned)P.h || (unsigned)c >= (unsigned)P.w)
+                    s_in[i] = plane[(long long)ext_index<MODE>(r, P.h) * P.in.rstride + ext_index<MODE>(c, P.w)];
+            }
+        }
+    } else {
         const float* __restrict__ plane = P.in.p + pl * P.in.pstride;
         for (int rr = warp; rr < IR; rr += NWARP) {
             const float* __restrict__ row = plane + (long long)ext_index<MODE>(r_start + rr, P.h) * P.in.rstride;
@@ -205,8 +262,8 @@ wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid
                 for (int cc = lane; cc < ICS; cc += 32) cp_async4(dst + cc, row + ext_index<MODE>(c_al + cc, P.w));
             }
         }
+        cp_async_wait_all();
     }
-    cp_async_wait_all();
     __syncthreads();
     // axis -2: output rows ol and ol + 1 of column cc from staged rows 2*ol .. 2*ol + F + 1
     // (row pair, column) items dealt flat over the CTA: IC is not a multiple of 32
@@ -299,6 +356,7 @@ struct SynParams {
     float thr_host;
     int use_thr, thr_a;
     long long* counts4;
+    int use_tma;  // fixed kernel: the four sub-band tiles come in through the tensor maps
 };
 
 // virtual coefficient index and tap parity that produce output sample o
@@ -408,7 +466,7 @@ wt_generic_synthesis_kernel(const __grid_constant__ WtBank bk, const __grid_cons
         }
     }
     cp_async_wait_all();
-    if (thr) {  // np.where(|c| < t, 0, c): every thread sweeps exactly the elements it copied
+    if (thr) {  // np.where(|c| < t, 0, c): every thread sweeps exactly the elements it copied (TMA: visible to everybody)
         for (int p = 0; p < np; ++p) {
             for (int r2 = warp; r2 < cr; r2 += NWARP) {
                 const size_t off = ((size_t)p * cr + r2) * cc;
@@ -480,10 +538,11 @@ constexpr int FS_TW = 2 * FS_HALF;
 template <int F, int TR> struct FsGeom {
     static constexpr int hf = F / 2;
     static constexpr int CR = TR / 2 + hf + 2, CC = FS_TC / 2 + hf + 2, CCS = (CC + 3 + 3) & ~3;
-    static constexpr int SMEM_FLOATS_ = 4 * CR * CCS + 2 * CR * FS_TW;
+    static constexpr int BAND = (CR * CCS + 31) & ~31;   // every sub-band tile starts 128-byte aligned (TMA destination)
+    static constexpr int SMEM_FLOATS_ = 4 * BAND + 2 * CR * FS_TW;
 };
 // tile height of the fixed kernel for filter length F: 64 rows when the tile fits shared memory, else 32
-template <int F> constexpr int fs_tr() { return (WT_FS_TR_MAX >= 64 && FsGeom<F, 64>::SMEM_FLOATS_ <= SMEM_FLOATS) ? 64 : 32; }
+template <int F> constexpr int fs_tr() { return (WT_FS_TR_MAX >= 64 && FsGeom<F, 64>::SMEM_FLOATS_ + 4 <= SMEM_FLOATS) ? 64 : 32; }  // + the mbarrier
 
 // the two outputs (tap parity 0, 1) fed by coefficients a[0], a[-stride], ..., a[-(hf-1)*stride] and the same of d
 template <int F, int MODE, int STRIDE>
@@ -522,10 +581,46 @@ __device__ __forceinline__ void syn_pair(const float* a, const float* d, const W
     }
 }
 
+// syn_pair on values already in registers: va[j] / vd[j] = the coefficients paired with taps 2j, 2j + 1 (same order of operations)
+template <int F, int MODE>
+__device__ __forceinline__ void syn_pair_regs(const float (&va)[F / 2], const float (&vd)[F / 2], const WtBank& bk, float& o0, float& o1) {
+    constexpr int hf = F / 2;
+    if (MODE == WT_MODE_PERIODIZATION) {
+        float e = 0.0f, o = 0.0f;
+#pragma unroll
+        for (int j = 0; j < hf; ++j) {
+            e = __fadd_rn(e, __fmul_rn(bk.rec_lo[2 * j], va[j]));
+            o = __fadd_rn(o, __fmul_rn(bk.rec_lo[2 * j + 1], va[j]));
+        }
+#pragma unroll
+        for (int j = 0; j < hf; ++j) {
+            e = __fadd_rn(e, __fmul_rn(bk.rec_hi[2 * j], vd[j]));
+            o = __fadd_rn(o, __fmul_rn(bk.rec_hi[2 * j + 1], vd[j]));
+        }
+        o0 = e; o1 = o;
+    } else {
+        float le = 0.0f, lo = 0.0f, he = 0.0f, ho = 0.0f;
+#pragma unroll
+        for (int j = 0; j < hf; ++j) {
+            le = __fadd_rn(le, __fmul_rn(bk.rec_lo[2 * j], va[j]));
+            lo = __fadd_rn(lo, __fmul_rn(bk.rec_lo[2 * j + 1], va[j]));
+        }
+#pragma unroll
+        for (int j = 0; j < hf; ++j) {
+            he = __fadd_rn(he, __fmul_rn(bk.rec_hi[2 * j], vd[j]));
+            ho = __fadd_rn(ho, __fmul_rn(bk.rec_hi[2 * j + 1], vd[j]));
+        }
+        o0 = __fadd_rn(__fadd_rn(0.0f, le), he);
+        o1 = __fadd_rn(__fadd_rn(0.0f, lo), ho);
+    }
+}
+
 template <int F, int MODE, int TR>
 __global__ void __launch_bounds__(GEN_THREADS)
-wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ SynParams P) {
-    extern __shared__ float smem[];
+wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid_constant__ SynParams P,
+                                  const __grid_constant__ CUtensorMap map_aa, const __grid_constant__ CUtensorMap map_da,
+                                  const __grid_constant__ CUtensorMap map_ad, const __grid_constant__ CUtensorMap map_dd) {
+    extern __shared__ __align__(128) float smem[];
     using G = FsGeom<F, TR>;
     constexpr int hf = F / 2, CR = G::CR, CCS = G::CCS;
     // q = o - SH is the index whose parity picks the taps (syn_index)
@@ -542,7 +637,7 @@ wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __gri
     const int col_lo0 = iv0 - (hf - 1);
     const int col_lo = (col_lo0 >> 2) << 2;
     const int d0 = col_lo0 - col_lo;
-    constexpr int band = CR * CCS;
+    constexpr int band = G::BAND;
     float* s_aa = smem;
     float* s_da = s_aa + band;
     float* s_ad = s_da + band;
@@ -558,40 +653,85 @@ wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __gri
     };
     const bool vec = col_lo >= 0 && col_lo + CCS <= P.w2 && aligned_view(P.aa) && aligned_view(P.da) && aligned_view(P.ad) &&
                      aligned_view(P.dd);
-    for (int r2 = warp; r2 < CR; r2 += NWARP) {
-        const long long sr = syn_map<MODE>(row_lo + r2, P.h2);
-        const float* __restrict__ raa = P.aa.p + pl * P.aa.pstride + sr * P.aa.rstride;
-        const float* __restrict__ rda = P.da.p + pl * P.da.pstride + sr * P.da.rstride;
-        const float* __restrict__ rad = P.ad.p + pl * P.ad.pstride + sr * P.ad.rstride;
-        const float* __restrict__ rdd = P.dd.p + pl * P.dd.pstride + sr * P.dd.rstride;
-        const int off = r2 * CCS;
-        if (vec) {
-            for (int v = lane; v < CCS / 4; v += 32) {
-                cp_async16(s_aa + off + 4 * v, raa + col_lo + 4 * v);
-                cp_async16(s_da + off + 4 * v, rda + col_lo + 4 * v);
-                cp_async16(s_ad + off + 4 * v, rad + col_lo + 4 * v);
-                cp_async16(s_dd + off + 4 * v, rdd + col_lo + 4 * v);
+    const bool tma = P.use_tma != 0;
+    if (tma) {
+        unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + G::SMEM_FLOATS_);   // past the tile buffers
+        if (threadIdx.x == 0) {
+            mbar_init(bar, 1);
+            mbar_expect(bar, 4u * CR * CCS * (unsigned)sizeof(float));
+            tma_load_box(s_aa, &map_aa, col_lo, row_lo, (int)pl, bar);
+            tma_load_box(s_da, &map_da, col_lo, row_lo, (int)pl, bar);
+            tma_load_box(s_ad, &map_ad, col_lo, row_lo, (int)pl, bar);
+            tma_load_box(s_dd, &map_dd, col_lo, row_lo, (int)pl, bar);
+        }
+        __syncthreads();   // the barrier is initialised for everybody
+        mbar_wait(bar, 0);
+        if (row_lo < 0 || row_lo + CR > P.h2 || col_lo < 0 || col_lo + CCS > P.w2) {   // border tile: zero fill -> extension
+            for (int i = threadIdx.x; i < CR * CCS; i += GEN_THREADS) {
+                const int r2 = i / CCS, c2 = i - r2 * CCS;
+                const int r = row_lo + r2, c = col_lo + c2;
+                if ((unsigned)r >= (unsigned)P.h2 || (unsigned)c >= (unsigned)P.w2) {
+                    const long long sr = syn_map<MODE>(r, P.h2);
+                    const int sc = syn_map<MODE>(c, P.w2);
+                    s_aa[i] = P.aa.p[pl * P.aa.pstride + sr * P.aa.rstride + sc];
+                    s_da[i] = P.da.p[pl * P.da.pstride + sr * P.da.rstride + sc];
+                    s_ad[i] = P.ad.p[pl * P.ad.pstride + sr * P.ad.rstride + sc];
+                    s_dd[i] = P.dd.p[pl * P.dd.pstride + sr * P.dd.rstride + sc];
+                }
             }
-        } else {
-            for (int c2 = lane; c2 < CCS; c2 += 32) {
-                const int sc = syn_map<MODE>(col_lo + c2, P.w2);
-                cp_async4(s_aa + off + c2, raa + sc);
-                cp_async4(s_da + off + c2, rda + sc);
-                cp_async4(s_ad + off + c2, rad + sc);
-                cp_async4(s_dd + off + c2, rdd + sc);
+            __syncthreads();   // the threshold sweep below reads what other threads patched
+        }
+    } else {
+        for (int r2 = warp; r2 < CR; r2 += NWARP) {
+            const long long sr = syn_map<MODE>(row_lo + r2, P.h2);
+            const float* __restrict__ raa = P.aa.p + pl * P.aa.pstride + sr * P.aa.rstride;
+            const float* __restrict__ rda = P.da.p + pl * P.da.pstride + sr * P.da.rstride;
+            const float* __restrict__ rad = P.ad.p + pl * P.ad.pstride + sr * P.ad.rstride;
+            const float* __restrict__ rdd = P.dd.p + pl * P.dd.pstride + sr * P.dd.rstride;
+            const int off = r2 * CCS;
+            if (vec) {
+                for (int v = lane; v < CCS / 4; v += 32) {
+                    cp_async16(s_aa + off + 4 * v, raa + col_lo + 4 * v);
+                    cp_async16(s_da + off + 4 * v, rda + col_lo + 4 * v);
+                    cp_async16(s_ad + off + 4 * v, rad + col_lo + 4 * v);
+                    cp_async16(s_dd + off + 4 * v, rdd + col_lo + 4 * v);
+                }
+            } else {
+                for (int c2 = lane; c2 < CCS; c2 += 32) {
+                    const int sc = syn_map<MODE>(col_lo + c2, P.w2);
+                    cp_async4(s_aa + off + c2, raa + sc);
+                    cp_async4(s_da + off + c2, rda + sc);
+                    cp_async4(s_ad + off + c2, rad + sc);
+                    cp_async4(s_dd + off + c2, rdd + sc);
+                }
             }
         }
+    
+        cp_async_wait_all();
     }
-    cp_async_wait_all();
     if (thr) {  // np.where(|c| < t, 0, c): every thread sweeps exactly the elements it copied
+        auto cut = [t](float v) { return fabsf(v) < t ? 0.0f : v; };
+        auto cut4 = [&](float* p) {   // 16-byte shared accesses: a lane's four floats in one conflict-free wavefront
+            float4 v = *reinterpret_cast<float4*>(p);
+            v.x = cut(v.x); v.y = cut(v.y); v.z = cut(v.z); v.w = cut(v.w);
+            *reinterpret_cast<float4*>(p) = v;
+        };
         for (int r2 = warp; r2 < CR; r2 += NWARP) {
             const int off = r2 * CCS;
-            for (int i = lane; i < (vec ? CCS / 4 : CCS); i += 32)
-            for (int c2 = vec ? 4 * i : i; c2 < (vec ? 4 * i + 4 : i + 1); ++c2) {
-                if (thr_a && fabsf(s_aa[off + c2]) < t) s_aa[off + c2] = 0.0f;
-                if (fabsf(s_da[off + c2]) < t) s_da[off + c2] = 0.0f;
-                if (fabsf(s_ad[off + c2]) < t) s_ad[off + c2] = 0.0f;
-                if (fabsf(s_dd[off + c2]) < t) s_dd[off + c2] = 0.0f;
+            if (vec || tma) {
+                for (int i = lane; i < CCS / 4; i += 32) {
+                    if (thr_a) cut4(s_aa + off + 4 * i);
+                    cut4(s_da + off + 4 * i);
+                    cut4(s_ad + off + 4 * i);
+                    cut4(s_dd + off + 4 * i);
+                }
+            } else {
+                for (int c2 = lane; c2 < CCS; c2 += 32) {
+                    if (thr_a) s_aa[off + c2] = cut(s_aa[off + c2]);
+                    s_da[off + c2] = cut(s_da[off + c2]);
+                    s_ad[off + c2] = cut(s_ad[off + c2]);
+                    s_dd[off + c2] = cut(s_dd[off + c2]);
+                }
             }
         }
     }
@@ -617,21 +757,43 @@ wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __gri
         }
     }
     __syncthreads();
-    // axis -2: row pair tp (tile rows 2*tp - SH, 2*tp - SH + 1) of column cl reads intermediate rows tp + hf-1 - j
+    // axis -2: row pair tp (tile rows 2*tp - SH, 2*tp - SH + 1) of column cl reads intermediate rows tp + hf-1 - j.
+    // A thread walks DOWN its column: consecutive row pairs share hf - 1 of their hf intermediate rows, so the window lives
+    // in registers and a step costs two shared loads (one new row of s_lo, one of s_hi) and two stores at a running pointer
+    // (ncu, round 2: the flat (pair, column) loop spent 86 instructions per pair on 31 flops -- eight loads, the address
+    // arithmetic of both stores and the row checks, every pair from scratch).
     unsigned int zc = 0, wr = 0;
     constexpr int NPAIR_R = TR / 2 + SH;
-    float* __restrict__ plane = P.out.p + pl * P.out.pstride + C0;
-    for (int it = threadIdx.x; it < NPAIR_R * FS_TC; it += GEN_THREADS) {  // a warp: 32 columns of one row pair
-        const int tp = it / FS_TC, cl = it % FS_TC;
-        const int rl0 = 2 * tp - SH;
-        const bool ok0 = rl0 >= 0 && rl0 < rows_valid, ok1 = rl0 + 1 < rows_valid;
-        if (!ok0 && !ok1) continue;
-        if (cl < cols_valid) {
+    constexpr int COL_GROUPS = GEN_THREADS / FS_TC;                 // threads per column
+    constexpr int PAIRS_PER = (NPAIR_R + COL_GROUPS - 1) / COL_GROUPS;
+    static_assert(GEN_THREADS % FS_TC == 0, "whole columns per thread group");
+    {
+        const int cl = threadIdx.x % FS_TC, grp = threadIdx.x / FS_TC;
+        const int tp0 = grp * PAIRS_PER, tp1 = min(NPAIR_R, tp0 + PAIRS_PER);
+        if (cl < cols_valid && tp0 < tp1) {
             const int idx = ((cl + SH) & 1) * FS_HALF + ((cl + SH) >> 1);
-            float v0, v1;
-            syn_pair<F, MODE, FS_TW>(s_lo + (tp + hf - 1) * FS_TW + idx, s_hi + (tp + hf - 1) * FS_TW + idx, bk, v0, v1);
-            if (ok0) { plane[(long long)(R0 + rl0) * P.out.rstride + cl] = v0; zc += (v0 == 0.0f); ++wr; }
-            if (ok1) { plane[(long long)(R0 + rl0 + 1) * P.out.rstride + cl] = v1; zc += (v1 == 0.0f); ++wr; }
+            const float* lo = s_lo + idx;
+            const float* hi = s_hi + idx;
+            float wl[hf], wh[hf];   // w[j] = intermediate row tp + hf-1 - j
+#pragma unroll
+            for (int j = 1; j < hf; ++j) {
+                wl[j - 1] = lo[(tp0 + hf - 1 - j) * FS_TW];
+                wh[j - 1] = hi[(tp0 + hf - 1 - j) * FS_TW];
+            }
+            float* __restrict__ o = P.out.p + pl * P.out.pstride + C0 + (long long)(R0 + 2 * tp0 - SH) * P.out.rstride + cl;
+            const long long rs = P.out.rstride;
+            for (int tp = tp0; tp < tp1; ++tp) {
+#pragma unroll
+                for (int j = hf - 1; j > 0; --j) { wl[j] = wl[j - 1]; wh[j] = wh[j - 1]; }
+                wl[0] = lo[(tp + hf - 1) * FS_TW];
+                wh[0] = hi[(tp + hf - 1) * FS_TW];
+                float v0, v1;
+                syn_pair_regs<F, MODE>(wl, wh, bk, v0, v1);
+                const int rl0 = 2 * tp - SH;
+                if (rl0 >= 0 && rl0 < rows_valid) { o[0] = v0; zc += (v0 == 0.0f); ++wr; }
+                if (rl0 + 1 < rows_valid) { o[rs] = v1; zc += (v1 == 0.0f); ++wr; }
+                o += 2 * rs;
+            }
         }
     }
     if (P.counts4) {
@@ -851,6 +1013,43 @@ float* wt_generic_scratch(float* tmp, long long batch, int H, int W, int F, int 
     return mode > WT_MODE_SYMMETRIC ? tmp + batch * tmp_pingpong_elems(H, W, F, mode, level) : nullptr;
 }
 
+// ---- tensor maps for the fixed-geometry kernels ----------------------------------------------------------------
+// cuTensorMapEncodeTiled lives in the driver library; the entry point comes from the runtime, so libwtprune.so keeps
+// linking against cudart alone.
+typedef CUresult (*WtEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static WtEncodeTiled encode_tiled_entry() {
+    static WtEncodeTiled fn = []() -> WtEncodeTiled {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return reinterpret_cast<WtEncodeTiled>(p);
+    }();
+    return fn;
+}
+
+// map of the view as a 3-D tensor {w, h, batch} with a box of box_rows x box_cols floats of one plane; false when the
+// view cannot be described (unaligned base / strides): the kernels then stage with cp.async as before
+static bool make_plane_map(CUtensorMap* m, const WtView& v, long long batch, int h, int w, int box_rows, int box_cols) {
+    memset(m, 0, sizeof(*m));
+    static const bool off = getenv("WT_GENERIC_NO_TMA") != nullptr;
+    WtEncodeTiled fn = off ? nullptr : encode_tiled_entry();
+    if (!fn) return false;
+    if ((reinterpret_cast<uintptr_t>(v.p) & 15u) != 0 || (v.rstride & 3) != 0 || (batch > 1 && (v.pstride & 3) != 0)) return false;
+    if (box_cols > 256 || box_rows > 256 || (box_cols & 3) != 0 || h <= 0 || w <= 0 || batch <= 0 || batch > 2147483647LL) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)batch};
+    const cuuint64_t pstride_b = (cuuint64_t)(batch > 1 ? v.pstride : (long long)v.rstride * h) * sizeof(float);
+    const cuuint64_t strides[2] = {(cuuint64_t)v.rstride * sizeof(float), (pstride_b + 15) / 16 * 16};
+    const cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, v.p, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
                               WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream) {
     if (mode > WT_MODE_SYMMETRIC) {
@@ -872,7 +1071,7 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     }
     AnaParams P;
     P.in = in; P.aa = aa; P.da = da; P.ad = ad; P.dd = dd;
-    P.batch = batch; P.h = h; P.w = w; P.mode = mode;
+    P.batch = batch; P.h = h; P.w = w; P.mode = mode; P.use_tma = 0;
     P.h2 = wt_dwt_coeff_len(h, bank.F, mode);
     P.w2 = wt_dwt_coeff_len(w, bank.F, mode);
     P.t2r = std::min(P.h2, 32);
@@ -908,7 +1107,9 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     if (fixed) {                                                                                                  \
         auto kern = wt_generic_analysis_fixed_kernel<FL, MD>;                                                     \
         WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
-        kern<<<(unsigned)(ftiles * batch), GEN_THREADS, FxGeom<FL>::SMEM_FLOATS_ * sizeof(float), stream>>>(bank, P); \
+        CUtensorMap tm;                                                                                           \
+        P.use_tma = make_plane_map(&tm, in, batch, h, w, FxGeom<FL>::IR, FxGeom<FL>::ICS) ? 1 : 0;                \
+        kern<<<(unsigned)(ftiles * batch), GEN_THREADS, (FxGeom<FL>::SMEM_FLOATS_ + 4) * sizeof(float), stream>>>(bank, P, tm); \
     } else {                                                                                                      \
         auto kern = wt_generic_analysis_kernel<FL, MD>;                                                           \
         WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
@@ -946,7 +1147,7 @@ int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView d
     while (geometry() > SMEM_FLOATS && (P.tr > 8 || P.tc > 32)) {
         if (P.tr > 8) P.tr /= 2; else P.tc /= 2;
     }
-    P.thr_dev = thr_dev; P.thr_host = thr_host; P.use_thr = use_thr; P.thr_a = thr_a; P.counts4 = counts4;
+    P.thr_dev = thr_dev; P.thr_host = thr_host; P.use_thr = use_thr; P.thr_a = thr_a; P.counts4 = counts4; P.use_tma = 0;
     const long long per_plane = 4LL * P.cr * P.ccs + 2LL * P.cr * P.tc;
     long long pb = SMEM_FLOATS / per_plane;
     WT_CHECK(pb >= 1, WT_E_UNSUPPORTED, "generic synthesis tile does not fit shared memory");
@@ -968,7 +1169,14 @@ int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView d
             geometry();                                                                                           \
             auto kern = wt_generic_synthesis_fixed_kernel<FL, MD, FTR>;                                           \
             WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));    \
-            kern<<<(unsigned)(ftiles * batch), GEN_THREADS, FsGeom<FL, FTR>::SMEM_FLOATS_ * sizeof(float), stream>>>(bank, P); \
+            using G_ = FsGeom<FL, FTR>;                                                                           \
+            CUtensorMap m0, m1, m2, m3;                                                                           \
+            const bool t0 = make_plane_map(&m0, aa, batch, h2, w2, G_::CR, G_::CCS);                              \
+            const bool t1 = make_plane_map(&m1, da, batch, h2, w2, G_::CR, G_::CCS);                              \
+            const bool t2 = make_plane_map(&m2, ad, batch, h2, w2, G_::CR, G_::CCS);                              \
+            const bool t3 = make_plane_map(&m3, dd, batch, h2, w2, G_::CR, G_::CCS);                              \
+            P.use_tma = (t0 && t1 && t2 && t3) ? 1 : 0;                                                           \
+            kern<<<(unsigned)(ftiles * batch), GEN_THREADS, (G_::SMEM_FLOATS_ + 4) * sizeof(float), stream>>>(bank, P, m0, m1, m2, m3); \
         } else {                                                                                                  \
             auto kern = wt_generic_synthesis_kernel<FL, MD>;                                                      \
             WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));    \
