@@ -92,6 +92,7 @@ struct AnaParams {
     int t2r, t2c, tiles_r, tiles_c, pb, ir, ic;
     int ics;  // staged row width: ic + up to 3 columns so that the staged region starts 16-byte aligned, rounded to 4
     int use_tma;  // fixed kernel: the tile comes in through the tensor map
+    long long* nz_counts4;  // fixed kernel, level 1: counts4[3] += nonzero inputs, counts4[0] = numel (else nullptr)
 };
 
 constexpr int NWARP = GEN_THREADS / 32;
@@ -188,18 +189,21 @@ wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_const
     }
 }
 
-// ---- large-plane fast path: fixed 32 x 64 output tile, one plane per CTA ----------------------------------------
+// ---- large-plane fast path: fixed FX_T2R x 64 output tile, one plane per CTA ----------------------------------------
 // Same arithmetic and accumulation order as wt_generic_analysis_kernel; what changes is the instruction count (ncu:
 // the runtime-geometry kernel issues ~119 thread-instructions per input element against ~32 no-FMA flops):
 // every shared-memory stride is a compile-time constant (LDS with immediate offsets instead of an IMAD + LEA per
 // tap), the axis -2 pass computes two output rows per thread from one column of F + 2 staged values (they share
 // F - 2 of them), the axis -1 pass computes two adjacent output columns per thread from 64-bit shared loads and
 // stores float2s.
+// tile heights: measured on 4096 x 4096 db4 (round 2, TMA staging): analysis 32 / 16 / 8 rows -> 115 / 103 / 105 us per
+// plane over five levels, synthesis 64 / 32 rows -> 123 / 116.5 us.  The smaller tiles load more halo (38 staged rows for 32
+// useful ones) but five CTAs fit an SM instead of two, and the other CTAs' arithmetic covers a CTA's wait for its tile.
 #ifndef WT_FX_T2R
-#define WT_FX_T2R 32
+#define WT_FX_T2R 16
 #endif
 #ifndef WT_FS_TR_MAX
-#define WT_FS_TR_MAX 64
+#define WT_FS_TR_MAX 32
 #endif
 constexpr int FX_T2R = WT_FX_T2R, FX_T2C = 64;
 constexpr int FX_HALF = 80;          // even (8-byte aligned odd half) and = 16 mod 32 (de-interleaving stores conflict-free)
@@ -208,7 +212,8 @@ template <int F> struct FxGeom {
     static constexpr int IR = 2 * FX_T2R + F - 2, IC = 2 * FX_T2C + F - 2, ICS = (IC + 3 + 3) & ~3;
     static constexpr int SMEM_FLOATS_ = IR * ICS + 2 * FX_T2R * FX_LW;
     static_assert((IC + 1) / 2 <= FX_HALF, "tile wider than the de-interleaved row");
-    static_assert(SMEM_FLOATS_ + 4 <= SMEM_FLOATS, "fixed tile (+ its mbarrier) does not fit");
+    static constexpr int EXTRA = 16;   // floats past the tile buffers: the mbarrier, then one nonzero counter per warp
+    static_assert(SMEM_FLOATS_ + EXTRA <= SMEM_FLOATS, "fixed tile (+ its mbarrier and counters) does not fit");
 };
 
 template <int F, int MODE>
@@ -265,6 +270,20 @@ wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid
         cp_async_wait_all();
     }
     __syncthreads();
+    unsigned int* s_nz = reinterpret_cast<unsigned int*>(smem + G::SMEM_FLOATS_ + 2);   // [NWARP], past the mbarrier
+    if (P.nz_counts4) {
+        // nonzeros of the input (dwt_pruning_NoEntropy.py:58) while the tile is in shared memory: input rows 2*o0 .. and
+        // columns 2*c0 .. of this tile -- every input element belongs to exactly one tile -- instead of a pass of its own
+        constexpr int OFF = (F - 1) - base;   // staged row / logical column of the tile's first own input row / column
+        unsigned int nz = 0;
+        const int j = threadIdx.x % (2 * FX_T2C);
+        if (2 * c0 + j < P.w)
+            for (int i = threadIdx.x / (2 * FX_T2C); i < 2 * FX_T2R && 2 * o0 + i < P.h; i += GEN_THREADS / (2 * FX_T2C))
+                nz += (s_in[(i + OFF) * ICS + j + OFF + shift] != 0.0f);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) nz += __shfl_down_sync(0xffffffffu, nz, d);
+        if (lane == 0) s_nz[warp] = nz;
+    }
     // axis -2: output rows ol and ol + 1 of column cc from staged rows 2*ol .. 2*ol + F + 1
     // (row pair, column) items dealt flat over the CTA: IC is not a multiple of 32
     for (int it = threadIdx.x; it < (FX_T2R / 2) * IC; it += GEN_THREADS) {
@@ -290,6 +309,13 @@ wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid
         }
     }
     __syncthreads();
+    if (P.nz_counts4 && threadIdx.x == 0) {
+        unsigned int nz = 0;
+#pragma unroll
+        for (int q = 0; q < NWARP; ++q) nz += s_nz[q];
+        if (nz) atomicAdd(reinterpret_cast<unsigned long long*>(P.nz_counts4 + 3), (unsigned long long)nz);
+        if (blockIdx.x == 0) P.nz_counts4[0] = P.batch * P.h * P.w;
+    }
     // axis -1: output columns cl = 2*lane and cl + 1.  Tile column m = 2*c + F-1-j of output column c lives at
     // [(m & 1) * HALF + (m >> 1)] = [parity_j * HALF + c + ((F-1-j) >> 1)]: both outputs read E[0 .. F/2], O[0 .. F/2]
     constexpr int NV2 = (F / 2 + 2) / 2;  // float2 loads per half row
@@ -766,6 +792,7 @@ wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __gri
     constexpr int NPAIR_R = TR / 2 + SH;
     constexpr int COL_GROUPS = GEN_THREADS / FS_TC;                 // threads per column
     constexpr int PAIRS_PER = (NPAIR_R + COL_GROUPS - 1) / COL_GROUPS;
+    static_assert(GEN_THREADS % (2 * FX_T2C) == 0, "whole input columns per thread group");
     static_assert(GEN_THREADS % FS_TC == 0, "whole columns per thread group");
     {
         const int cl = threadIdx.x % FS_TC, grp = threadIdx.x / FS_TC;
@@ -1051,7 +1078,9 @@ static bool make_plane_map(CUtensorMap* m, const WtView& v, long long batch, int
 }
 
 int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
-                              WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream) {
+                              WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream, long long* nz_counts4,
+                              int* nz_counted) {
+    if (nz_counted) *nz_counted = 0;
     if (mode > WT_MODE_SYMMETRIC) {
         WT_CHECK(scratch != nullptr, WT_E_INVALID, "generic analysis: mode %d needs the sweep scratch", mode);
         AxisParams A;
@@ -1071,7 +1100,7 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     }
     AnaParams P;
     P.in = in; P.aa = aa; P.da = da; P.ad = ad; P.dd = dd;
-    P.batch = batch; P.h = h; P.w = w; P.mode = mode; P.use_tma = 0;
+    P.batch = batch; P.h = h; P.w = w; P.mode = mode; P.use_tma = 0; P.nz_counts4 = nullptr;
     P.h2 = wt_dwt_coeff_len(h, bank.F, mode);
     P.w2 = wt_dwt_coeff_len(w, bank.F, mode);
     P.t2r = std::min(P.h2, 32);
@@ -1099,6 +1128,10 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     const long long ftiles = (long long)((P.h2 + FX_T2R - 1) / FX_T2R) * ((P.w2 + FX_T2C - 1) / FX_T2C);
     const bool fixed = P.h2 >= FX_T2R && P.w2 >= FX_T2C && ftiles * batch >= 296 && !getenv("WT_GENERIC_NO_FIXED");
     if (fixed) {
+        if (nz_counts4 && nz_counted && in.rstride == w && in.pstride == (long long)h * w) {   // contiguous input: count it on the way
+            P.nz_counts4 = nz_counts4;
+            *nz_counted = 1;
+        }
         P.t2r = FX_T2R; P.t2c = FX_T2C; P.pb = 1;
         P.tiles_r = (P.h2 + FX_T2R - 1) / FX_T2R;
         P.tiles_c = (P.w2 + FX_T2C - 1) / FX_T2C;
@@ -1109,7 +1142,7 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
         WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
         CUtensorMap tm;                                                                                           \
         P.use_tma = make_plane_map(&tm, in, batch, h, w, FxGeom<FL>::IR, FxGeom<FL>::ICS) ? 1 : 0;                \
-        kern<<<(unsigned)(ftiles * batch), GEN_THREADS, (FxGeom<FL>::SMEM_FLOATS_ + 4) * sizeof(float), stream>>>(bank, P, tm); \
+        kern<<<(unsigned)(ftiles * batch), GEN_THREADS, (FxGeom<FL>::SMEM_FLOATS_ + FxGeom<FL>::EXTRA) * sizeof(float), stream>>>(bank, P, tm); \
     } else {                                                                                                      \
         auto kern = wt_generic_analysis_kernel<FL, MD>;                                                           \
         WT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_FLOATS * 4));        \
@@ -1221,9 +1254,12 @@ int wt_generic_analysis(const WtBank& bank, int mode, const WtGenericLayer& L, l
     int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
     long long off[(WT_MAX_LEVEL + 1) * 3], off_a;
     band_offsets(L, bank.F, mode, hs, ws, off, &off_a);
-    int rc = wt_count_nonzero_launch(L.in, L.batch * L.H * L.W, counts + (size_t)L.layer * 4, stream);
-    if (rc) return rc;
-    ++*launches;
+    int rc = WT_OK;
+    if (L.level < 1) {
+        rc = wt_count_nonzero_launch(L.in, L.batch * L.H * L.W, counts + (size_t)L.layer * 4, stream);
+        if (rc) return rc;
+        ++*launches;
+    }
     WtView cur = wt_view(const_cast<float*>(L.in), L.H, L.W);
     for (int l = 1; l <= L.level; ++l) {
         float* dst = (l == L.level) ? L.coef + off_a : ((l & 1) ? L.tmp0 : L.tmp1);
@@ -1233,9 +1269,18 @@ int wt_generic_analysis(const WtBank& bank, int mode, const WtGenericLayer& L, l
         WtView dd = wt_view(L.coef + off[l * 3 + 2], hs[l], ws[l]);
         // the scratch of the two-sweep modes sits behind the ping-pong part of the buffer `cur` is NOT in
         float* scratch = wt_generic_scratch((l & 1) ? L.tmp0 : L.tmp1, L.batch, L.H, L.W, bank.F, mode, L.level);
-        rc = wt_generic_analysis_level(bank, mode, cur, L.batch, hs[l - 1], ws[l - 1], aa, da, ad, dd, scratch, stream);
+        // level 1 reads the whole input anyway: the fixed-geometry kernel counts its nonzeros (counts[3], dwt_pruning_NoEntropy.py:58)
+        // from the staged tiles; when another kernel takes the level, the count is a pass of its own
+        int counted = 0;
+        rc = wt_generic_analysis_level(bank, mode, cur, L.batch, hs[l - 1], ws[l - 1], aa, da, ad, dd, scratch, stream,
+                                       l == 1 ? counts + (size_t)L.layer * 4 : nullptr, l == 1 ? &counted : nullptr);
         if (rc) return rc;
         *launches += (mode > WT_MODE_SYMMETRIC) ? 2 : 1;
+        if (l == 1 && !counted) {
+            rc = wt_count_nonzero_launch(L.in, L.batch * L.H * L.W, counts + (size_t)L.layer * 4, stream);
+            if (rc) return rc;
+            ++*launches;
+        }
         cur = aa;
     }
     return WT_OK;

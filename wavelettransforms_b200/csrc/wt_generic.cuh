@@ -37,8 +37,11 @@ long long wt_generic_tmp_elems(int H, int W, int F, int mode, int level);
 float* wt_generic_scratch(float* tmp, long long batch, int H, int W, int F, int mode, int level);
 
 // one decomposition level: in (h x w) -> aa, da, ad, dd (h2 x w2); scratch: see wt_generic_scratch
+// nz_counts4 / nz_counted (optional): when the kernel that takes the level can count the nonzeros of `in` on the way it adds
+// them to nz_counts4[3], sets nz_counts4[0] = numel and *nz_counted = 1; otherwise *nz_counted = 0 and the caller counts
 int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
-                              WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream);
+                              WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream,
+                              long long* nz_counts4 = nullptr, int* nz_counted = nullptr);
 // one reconstruction level: bands (h2 x w2) -> out (oh x ow, cropped).  thr: device threshold
 // (nullable) or thr_host when use_host; thr_a: also threshold the approximation band (deepest
 // level only); counts4 != nullptr: add zero / nonzero counts of `out` (final level).
