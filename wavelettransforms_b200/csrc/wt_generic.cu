@@ -765,8 +765,10 @@ wt_generic_synthesis_fixed_kernel(const __grid_constant__ WtBank bk, const __gri
     // axis -1 first (idwt2).  Pair tp: q = 2*(tp - SH), q + 1, i.e. tile columns 2*tp - SH and 2*tp - SH + 1; both read
     // the staged coefficients [tp + hf-1 + d0 - j], j < hf
     constexpr int NPAIR_C = FS_TC / 2 + SH;
-    // (row, pair) items dealt flat over the CTA: neither CR nor NPAIR_C is a multiple of the warp geometry
-    for (int it = threadIdx.x; it < CR * NPAIR_C; it += GEN_THREADS) {
+    constexpr int ROWS_USED = (TR / 2 + SH) + hf - 1;   // intermediate rows the axis -2 pass reads (CR keeps two spare)
+    static_assert(ROWS_USED <= CR, "staged rows");
+    // (row, pair) items dealt flat over the CTA: neither ROWS_USED nor NPAIR_C is a multiple of the warp geometry
+    for (int it = threadIdx.x; it < ROWS_USED * NPAIR_C; it += GEN_THREADS) {
         const int r2 = it / NPAIR_C, tp = it % NPAIR_C;
         const float* aa = s_aa + r2 * CCS + (hf - 1) + d0;
         const float* ad = s_ad + r2 * CCS + (hf - 1) + d0;
