@@ -127,7 +127,7 @@ def test_generic_packed_coefficients_bitwise(mods, wavelet, mode):
 @pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
 @pytest.mark.parametrize('wavelet', ['haar', 'db4', 'bior4.4', 'coif3'])
 def test_generic_large_planes_bitwise(mods, wavelet, mode):
-    """planes large enough for the fixed-geometry analysis kernel (full 32 x 64 tiles, >= 296 CTAs): partial edge
+    """planes large enough for the fixed-geometry kernels (full 16 x 64 analysis tiles, >= 296 CTAs; TMA staging): partial edge
     tiles, row strides that allow / forbid the 16-byte staging and the float2 stores, two levels"""
     eng, o = mods['eng'], mods['o']
     rng = np.random.default_rng(5)
