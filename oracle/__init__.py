@@ -22,7 +22,8 @@ MODES = {'periodization': 0, 'symmetric': 1, 'zero': 2, 'constant': 3, 'reflect'
 def build(force=False):
     so = os.path.join(_HERE, 'liboracle.so')
     src = os.path.join(_HERE, 'dwt_oracle.c')
-    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+    newest = max(os.path.getmtime(src), os.path.getmtime(os.path.join(_HERE, 'wavelet_tables.h')))
+    if force or not os.path.exists(so) or os.path.getmtime(so) < newest:
         subprocess.check_call(['make', '-C', _HERE, '-s'])
     return so
 

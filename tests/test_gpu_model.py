@@ -206,3 +206,32 @@ def test_synthetic_logits_and_sparsity_parity(mods, wavelet, level, p, clamp):
             nz += torch.sum(torch.abs(prm) < 1e-6).item()
     assert eval_model.calculate_sparsity(ours) == nz / tot
     assert eval_model.calculate_sparsity(ours.cpu()) == nz / tot
+
+
+def test_background_save_of_a_cuda_model_overlaps_the_next_method(tmp_path, monkeypatch):
+    """save_model(async) on a model that lives on the GPU snapshots it through pinned host memory, returns,
+    and the serialisation runs while the next pruning method already works on (and changes) the same weights"""
+    import os
+
+    from wavelettransforms_b200 import config, engine, utils
+    dev = torch.device('cuda', 0)
+    g = torch.Generator().manual_seed(5)
+    m = torch.nn.Sequential(torch.nn.Conv2d(8, 16, 3, bias=False), torch.nn.Conv2d(16, 16, 1, bias=False))
+    with torch.no_grad():
+        for p in m.parameters():
+            p.copy_(torch.randn(p.shape, generator=g) * 0.05)
+    m.to(dev)
+    want = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    monkeypatch.setattr(config, 'async_save', True)
+    fut = utils.save_model(m, str(tmp_path / 'bg'))
+    # the caller moves on: the next masker prunes the live weights in place while the save is (or may be) still writing
+    ws = [p.data for p in m.parameters()]
+    nz = engine.min_weight_prune_(ws, [w.numel() // 2 for w in ws])
+    torch.cuda.synchronize()
+    utils.wait_for_saves()
+    assert fut.done() and fut.exception() is None
+    sd = torch.load(os.path.join(tmp_path, 'bg', 'pytorch_model.bin'))
+    for k in want:
+        assert not sd[k].is_cuda and torch.equal(sd[k], want[k]), k      # the snapshot, not the pruned weights
+    for w, n in zip(ws, nz):
+        assert int(torch.count_nonzero(w)) == n == w.numel() - w.numel() // 2

@@ -12,7 +12,9 @@ pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WAVELETS = ['haar', 'db1', 'db2', 'db4', 'db6', 'coif1', 'coif2', 'coif3', 'bior1.3', 'bior2.2', 'bior4.4',
-            'rbio1.3', 'rbio2.2', 'rbio4.4', 'sym2', 'sym4', 'sym6']
+            'rbio1.3', 'rbio2.2', 'rbio4.4', 'sym2', 'sym4', 'sym6',
+            # round 2: beyond the reference's flag enum (wavelet is an open string in dwt_pruning.py:35)
+            'db3', 'db5', 'db7', 'db8', 'db9', 'sym3', 'bior1.1', 'rbio1.1', 'bior3.1', 'rbio3.1']
 
 
 @pytest.fixture(scope='module')
@@ -109,7 +111,7 @@ def test_small_planes_absolute(mods, wavelet):
 
 
 @pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
-@pytest.mark.parametrize('wavelet', ['haar', 'db2', 'db4', 'coif3', 'bior1.3', 'bior4.4', 'rbio2.2', 'sym6'])
+@pytest.mark.parametrize('wavelet', ['haar', 'db2', 'db4', 'coif3', 'bior1.3', 'bior4.4', 'rbio2.2', 'sym6', 'db7', 'db8', 'db9', 'rbio3.1'])
 def test_generic_packed_coefficients_bitwise(mods, wavelet, mode):
     eng, o = mods['eng'], mods['o']
     rng = np.random.default_rng(3)
@@ -125,7 +127,7 @@ def test_generic_packed_coefficients_bitwise(mods, wavelet, mode):
 
 
 @pytest.mark.parametrize('mode', ['periodization', 'symmetric'])
-@pytest.mark.parametrize('wavelet', ['haar', 'db4', 'bior4.4', 'coif3'])
+@pytest.mark.parametrize('wavelet', ['haar', 'db4', 'bior4.4', 'coif3', 'db7', 'db8', 'bior3.1'])
 def test_generic_large_planes_bitwise(mods, wavelet, mode):
     """planes large enough for the fixed-geometry kernels (full 16 x 64 analysis tiles, >= 296 CTAs; TMA staging): partial edge
     tiles, row strides that allow / forbid the 16-byte staging and the float2 stores, two levels"""

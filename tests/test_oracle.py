@@ -13,7 +13,9 @@ from oracle import reference_flow as rf
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WAVELETS = ['haar', 'db1', 'db2', 'db4', 'db6', 'coif1', 'coif2', 'coif3', 'bior1.3', 'bior2.2', 'bior4.4',
-            'rbio1.3', 'rbio2.2', 'rbio4.4', 'sym2', 'sym4', 'sym6']
+            'rbio1.3', 'rbio2.2', 'rbio4.4', 'sym2', 'sym4', 'sym6',
+            # round 2: beyond the reference's flag enum (wavelet is an open string in dwt_pruning.py:35)
+            'db3', 'db5', 'db7', 'db8', 'db9', 'sym3', 'bior1.1', 'rbio1.1', 'bior3.1', 'rbio3.1']
 S = np.float32(np.sqrt(2.0))
 
 
@@ -102,7 +104,11 @@ def test_perfect_reconstruction(wavelet, mode):
             r = o.waverec2_packed(o.wavedec2_packed(x, wavelet, L, mode), x.shape, wavelet, L, mode)
             assert r.shape[-2] in (H, H + 1) and r.shape[-1] in (W, W + 1)
             # smooth / antireflect extrapolate: on N < F planes the extended values (and the rounding error) grow per level
-            np.testing.assert_allclose(r[:, :H, :W], x, atol=2e-3 if mode in ('smooth', 'antireflect') else 2e-5)
+            # bior3.1 / rbio3.1 are the ill-conditioned spline pair (|taps| sum to 2.83 per axis and level): fp32 rounding grows
+            # (with the extrapolating modes the error of rbio3.1 goes 2e-6, 7e-6, 1e-4, 1e-2 over levels 1, 2, 3, 5: conditioning)
+            ill = wavelet in ('bior3.1', 'rbio3.1')
+            atol = (1e-1 if ill and L > 1 else 2e-3) if mode in ('smooth', 'antireflect') else (5e-4 if ill else 2e-5)
+            np.testing.assert_allclose(r[:, :H, :W], x, atol=atol)
 
 
 def test_packing_rule_padding():
@@ -178,3 +184,49 @@ def test_golden_fixture_matches_oracle():
                                                   clamp_level=c['clamp_level'])
         assert out[0].numpy().tobytes().hex() == c['pruned_hex'], c['name']
         assert zeros == c['zeros'], c['name']
+
+
+def test_round2_wavelets_from_their_defining_properties():
+    """The ten wavelets added in round 2 are re-derived, not copied (tools/gen_wavelets.py); pin them independently:
+    db3 / sym3 against Daubechies' closed form, bior3.1 / bior1.1 against the spline pairs' closed forms, db5..db9 against
+    the conditions that define a Daubechies filter (sum sqrt 2, orthonormal to its double shifts, N vanishing moments,
+    minimum phase), and every new bank against perfect reconstruction through the oracle's own dwt / idwt."""
+    s10, s2 = np.sqrt(10.0), np.sqrt(2.0)
+    t = np.sqrt(5.0 + 2.0 * s10)
+    db3 = np.array([1 + s10 + t, 5 + s10 + 3 * t, 10 - 2 * s10 + 2 * t, 10 - 2 * s10 - 2 * t, 5 + s10 - 3 * t, 1 + s10 - t]) / (16 * s2)
+    for name in ('db3', 'sym3'):
+        dec_lo, dec_hi, rec_lo, rec_hi = o.filters(name)
+        np.testing.assert_allclose(rec_lo, db3, rtol=0, atol=2e-15)
+        np.testing.assert_allclose(dec_lo, db3[::-1], rtol=0, atol=2e-15)
+        np.testing.assert_allclose(rec_hi, [(-1) ** i * db3[5 - i] for i in range(6)], rtol=0, atol=2e-15)
+    dec_lo, dec_hi, rec_lo, rec_hi = o.filters('bior3.1')
+    np.testing.assert_allclose(dec_lo, np.array([-1, 3, 3, -1]) * s2 / 4, atol=1e-15)
+    np.testing.assert_allclose(rec_lo, np.array([1, 3, 3, 1]) * s2 / 8, atol=1e-15)
+    np.testing.assert_allclose(dec_hi, np.array([-1, 3, -3, 1]) * s2 / 8, atol=1e-15)
+    np.testing.assert_allclose(rec_hi, np.array([-1, -3, 3, 1]) * s2 / 4, atol=1e-15)
+    for a, b in zip(o.filters('bior1.1'), o.filters('haar')):
+        assert np.array_equal(a, b)
+    for a, b in zip(o.filters('rbio3.1'), o.filters('bior3.1')[2:] + o.filters('bior3.1')[:2]):
+        np.testing.assert_allclose(a, np.asarray(b)[::-1], atol=0)
+    for n in (5, 7, 8, 9):
+        dec_lo, dec_hi, rec_lo, rec_hi = (np.asarray(f) for f in o.filters(f'db{n}'))
+        F = 2 * n
+        assert len(rec_lo) == F == o.dec_len(f'db{n}')
+        assert abs(rec_lo.sum() - s2) < 1e-14
+        for k in range(n):   # orthonormal to its even shifts
+            dot = float(np.dot(rec_lo[2 * k:], rec_lo[:F - 2 * k]))
+            assert abs(dot - (1.0 if k == 0 else 0.0)) < 1e-14, (n, k)
+        idx = np.arange(F, dtype=np.float64)
+        for m in range(n):   # N vanishing moments of the high-pass
+            assert abs(float(np.dot(idx ** m, rec_hi))) < 1e-7 * max(1.0, float(F) ** m), (n, m)
+        roots = np.roots(rec_lo[::-1])   # rec_lo in ascending powers of z: (1 + z)^N times the minimum-phase factor
+        away = roots[np.abs(roots + 1.0) > 0.2]   # the N-fold zero at -1 comes back as a small circle of computed roots
+        assert len(away) == n - 1 and np.all(np.abs(away) > 1.0), n   # energy at the front = zeros outside in this orientation
+        np.testing.assert_array_equal(dec_lo, rec_lo[::-1])
+    rng = np.random.default_rng(9)
+    for name in ('db3', 'db5', 'db7', 'db8', 'db9', 'sym3', 'bior1.1', 'rbio1.1', 'bior3.1', 'rbio3.1'):
+        for mode in ('periodization', 'symmetric'):
+            x = rng.standard_normal(64).astype(np.float32)
+            ca, cd = o.dwt(x, name, mode)
+            back = o.idwt(ca, cd, name, mode)
+            np.testing.assert_allclose(back[:64], x, atol=5e-6, err_msg=f'{name} {mode}')

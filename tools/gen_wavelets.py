@@ -229,11 +229,28 @@ def all_banks():
     banks['coif2'] = orth_bank(coiflet(2, COIF2_DEC_LO)[::-1])
     banks['coif3'] = orth_bank(coiflet(3, COIF3_DEC_LO)[::-1])
     banks.update(bior_banks())
+    # round 2 (`wavelet` is an open string in dwt_pruning.py:35): the Daubechies filters up to 18 taps need
+    # nothing beyond the spectral factorisation above; sym3 is db3 (below N = 4 the least-asymmetric choice is the only one);
+    # bior1.1 is haar; bior3.1 is the 4/4-tap spline pair in closed form.  The other symlets / coiflets / spline pairs need
+    # a table to pick their root selection or alignment from and stay out until PyWavelets can be held against them.
+    for n in (3, 5, 7, 8, 9):
+        banks[f'db{n}'] = orth_bank(daubechies(n))
+    banks['sym3'] = banks['db3']
+    banks['bior1.1'] = banks['haar']
+    banks['rbio1.1'] = tuple(f[::-1] for f in (banks['haar'][2], banks['haar'][3], banks['haar'][0], banks['haar'][1]))
+    q4, q8 = SQ2 / 4, SQ2 / 8
+    b31_dec_lo = [-q4, 3 * q4, 3 * q4, -q4]
+    b31_rec_lo = [q8, 3 * q8, 3 * q8, q8]
+    b31 = (b31_dec_lo, [(-1) ** (i + 1) * b31_rec_lo[i] for i in range(4)], b31_rec_lo, [(-1) ** i * b31_dec_lo[i] for i in range(4)])
+    banks['bior3.1'] = b31
+    banks['rbio3.1'] = (b31[2][::-1], b31[3][::-1], b31[0][::-1], b31[1][::-1])
     return banks
 
 
 ORDER = ['haar', 'db1', 'db2', 'db4', 'db6', 'coif1', 'coif2', 'coif3', 'bior1.3', 'bior2.2', 'bior4.4',
-         'rbio1.3', 'rbio2.2', 'rbio4.4', 'sym2', 'sym4', 'sym6']
+         'rbio1.3', 'rbio2.2', 'rbio4.4', 'sym2', 'sym4', 'sym6',
+         # round 2, appended so that the ids of the 17 flag names stay what they were
+         'db3', 'db5', 'db7', 'db8', 'db9', 'sym3', 'bior1.1', 'rbio1.1', 'bior3.1', 'rbio3.1']
 MAXF = 18
 
 

@@ -995,7 +995,7 @@ wt_generic_axis1_kernel(const __grid_constant__ WtBank bk, const __grid_constant
     {                                                                                          \
         const int mode_ = (mode__);                                                            \
         switch (F_) {                                                                          \
-            WT_GEN_CASE(2) WT_GEN_CASE(4) WT_GEN_CASE(6) WT_GEN_CASE(8) WT_GEN_CASE(10) WT_GEN_CASE(12) WT_GEN_CASE(18) \
+            WT_GEN_CASE(2) WT_GEN_CASE(4) WT_GEN_CASE(6) WT_GEN_CASE(8) WT_GEN_CASE(10) WT_GEN_CASE(12) WT_GEN_CASE(14) WT_GEN_CASE(16) WT_GEN_CASE(18) \
             default:                                                                           \
                 wt_set_error("generic path: unsupported filter length %d", (int)(F_));         \
                 return WT_E_UNSUPPORTED;                                                       \
