@@ -75,8 +75,9 @@ typedef struct WtPlan WtPlan;
 int wt_version(void);
 const char* wt_last_error(void);
 
-/* pywt.Wavelet(name): id for the other calls and dec_len.  Names = the --wavelet enum of
- * ResNet/main_pruning.py:89-96.  Unknown name -> WT_E_INVALID (pywt raises ValueError). */
+/* pywt.Wavelet(name): id for the other calls and dec_len.  Names = the 17 of the --wavelet enum of
+ * ResNet/main_pruning.py:89-96 (haar, db1/2/4/6, sym2/4/6, coif1/2/3, bior and rbio 1.3/2.2/4.4) plus db3/5/7/8/9, sym3,
+ * bior1.1/3.1, rbio1.1/3.1 (dwt_pruning.py:35 takes any name).  Unknown name -> WT_E_INVALID (pywt raises ValueError). */
 int wt_wavelet_lookup(const char* name, int* id, int* dec_len);
 /* copies the four float64 filters (dec_lo, dec_hi, rec_lo, rec_hi), each `dec_len` long (HOST) */
 int wt_wavelet_filters(int wavelet_id, double* dec_lo, double* dec_hi, double* rec_lo, double* rec_hi);
@@ -148,7 +149,9 @@ int wt_plan_set_timing(WtPlan* plan, int enable);
  * dropped by anything that changes what a run launches (wt_plan_set_io / _set_peers / _set_multicast / _set_arithmetic)
  * and bypassed while phase timing is on.  A stream that cannot be captured (the legacy default stream) makes the plan
  * fall back to plain launches silently -- same results.  Device plans only run through it; a host-I/O plan forwards
- * the switch to the device plans of its layer groups.  Default: off, or the value of WT_GRAPH when the plan is created.
+ * the switch to the device plans of its layer groups.  Default (neither this call nor WT_GRAPH=0|1 in the environment when
+ * the plan is created): automatic -- plans with layers on the large-plane kernels (a dozen short dependent launches per
+ * plane) replay from their second run on, conv-weight plans launch plainly (measured gain 1 %, single-launch plans lose 1 %).
  */
 int wt_plan_set_graph(WtPlan* plan, int enable);
 /* Arithmetic of the DWT multiply-adds.  WT_ARITH_FAITHFUL (default): fp32 multiply, then fp32 add, no FMA,

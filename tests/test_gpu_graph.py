@@ -26,8 +26,8 @@ def _run(xs, levels, wavelet, kind, value, graph, runs, arithmetic=None):
     s = torch.cuda.Stream()
     res = []
     try:
-        if graph:
-            plan.set_graph(True)
+        if graph is not None:
+            plan.set_graph(graph)   # None: the library's default (automatic for large-plane plans)
         with torch.cuda.stream(s):
             for r in range(runs):
                 if arithmetic and r == runs - 2:
@@ -120,3 +120,18 @@ def test_device_results_match_host_results(kind, value):
     assert np.array_equal(back.thresholds.view(np.uint32), host.thresholds.view(np.uint32))
     for a, b in zip(devr.outputs, host.outputs):
         assert np.array_equal(_bits(a), _bits(b))
+
+
+def test_large_plane_plans_replay_by_default():
+    """no switch touched: a plan with layers on the large-plane kernels captures its launch sequence on runs 2 and 3 and
+    replays it afterwards; every run gives the bits, counts and thresholds of the first (plain) one"""
+    from wavelettransforms_b200 import _lib
+    dev = torch.device('cuda', 0)
+    g = torch.Generator().manual_seed(8)
+    xs = [(torch.randn(1, 600, 520, generator=g) * 0.05).to(dev), (torch.randn(64, 32, 3, 3, generator=g) * 0.05).to(dev)]
+    res, launches = _run(xs, (4, 1), 'db4', _lib.THRESHOLD_PERCENTILE, 75.0, None, 6)
+    assert launches >= 8
+    for r, (bits, counts, nzb, thr) in enumerate(res[1:], 1):
+        for a, b in zip(bits, res[0][0]):
+            assert np.array_equal(a, b), r
+        assert np.array_equal(counts, res[0][1]) and np.array_equal(nzb, res[0][2]) and np.array_equal(thr, res[0][3]), r

@@ -255,7 +255,7 @@ struct WtPlan {
     cudaEvent_t ev_start = nullptr, ev_done = nullptr;
     int timing = 0;
     // wt_plan_set_graph: the launch sequence of a run, captured once per scratch parity and replayed
-    int use_graph = 0;
+    int use_graph = -1;            // -1: automatic (plans with large-plane layers, from the second run on), 0: never, 1: always
     unsigned long long run_count = 0;
     cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};
     int graph_launches[2] = {0, 0};
@@ -795,7 +795,7 @@ extern "C" int wt_plan_create(const WtLayerDesc* layers, int n_layers, int wavel
     // staging double the analysis kernel and the two extra launches sit on the critical path.
     {
         const char* gr = getenv("WT_GRAPH");
-        P->use_graph = gr != nullptr && gr[0] != '\0' && gr[0] != '0';
+        P->use_graph = (gr == nullptr || gr[0] == '\0') ? -1 : (gr[0] != '0' ? 1 : 0);
     }
     {
         const char* pre = getenv("WT_PRECOMPACT");
@@ -1098,7 +1098,11 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     const int par = (int)(P->run_count & 1ull);   // both alternations flip once per run
     advance_run_state(P);
     ++P->run_count;
-    const bool graphable = P->use_graph && !P->graph_failed && !P->timing && P->stamps_dev == nullptr && getenv("WT_FUSED_STAMPS") == nullptr;
+    // automatic: a plan with large-plane layers is a dozen dependent launches per plane, several of them a few microseconds long
+    // (the deep levels): replaying them as a graph measured 2-7 %; conv-weight plans gain 1 % and
+    // single-launch plans lose 1 %, so they stay on plain launches unless asked
+    const bool want_graph = P->use_graph > 0 || (P->use_graph < 0 && !P->generic.empty() && P->n_launches >= 8);
+    const bool graphable = want_graph && !P->graph_failed && !P->timing && P->stamps_dev == nullptr && getenv("WT_FUSED_STAMPS") == nullptr;
     if (!graphable) return plan_enqueue(P, stream);
     if (!P->graph_exec[par]) {
         // capture this parity's launch sequence (the class streams fork from and join back into `stream`, so they are
