@@ -160,7 +160,7 @@ int wt_plan_set_graph(WtPlan* plan, int enable);
  * instead of two).  A NAMED FAST MODE for the fp32-issue-bound decompositions (long filters on 3x3 planes), never chosen
  * silently: bit-exact against the oracle's twin (orc_set_arithmetic(1)), within 1e-5 relative / 1e-6 absolute of the
  * faithful weights, but exact zeros of a round trip are not preserved, so masks and zero counts can differ
- * from the reference's.  Small-plane layers only (WT_E_UNSUPPORTED for plans with layers on the generic tiled path). */
+ * from the reference's.  Covers the small-plane kernels and the tiled / large-plane kernels (every boundary mode). */
 #define WT_ARITH_FAITHFUL 0
 #define WT_ARITH_FMA_TAPORDER 1
 int wt_plan_set_arithmetic(WtPlan* plan, int arithmetic);

@@ -58,15 +58,43 @@ def test_fma_taporder_absolute_flow_and_default_stays_faithful(oracle_lib):
     assert gp == wp and all(np.array_equal(_bits(a), _bits(b)) for a, b in zip(got, want))
 
 
-def test_fma_taporder_is_refused_where_it_does_not_exist():
+def test_unknown_arithmetic_is_refused_and_generic_plans_take_the_fast_mode():
     from wavelettransforms_b200 import _lib, engine
     dev = torch.device('cuda', 0)
     x = torch.randn(2, 64, 64, device=dev)
     o = torch.empty_like(x)
     plan = _lib.Plan([(x.data_ptr(), o.data_ptr()) + engine.plane_geometry(x.shape) + (2,)], 'db4', 'periodization',
                      _lib.THRESHOLD_PERCENTILE, 50.0, 'legacy_1_22')
-    with pytest.raises(NotImplementedError, match='generic tiled path'):
-        plan.set_arithmetic('fma_taporder')
+    plan.set_arithmetic('fma_taporder')      # round 2: the tiled kernels exist in both arithmetics (wt_generic_fma.cu)
     with pytest.raises(ValueError):
         plan.set_arithmetic('fast')
     plan.close()
+
+
+@pytest.mark.parametrize('mode', ['periodization', 'symmetric', 'reflect'])
+@pytest.mark.parametrize('wavelet,level', [('db4', 3), ('bior4.4', 2), ('haar', 2), ('db8', 1)])
+def test_fma_taporder_on_the_large_plane_and_generic_kernels(oracle_lib, wavelet, level, mode):
+    """the tiled kernels (wt_generic_fma.cu): TMA-staged fixed-geometry kernels on the big planes, runtime-geometry kernels on
+    the odd one, two-sweep kernels for the extra mode -- both threshold kinds, bit for bit against the oracle's twin"""
+    from oracle import reference_flow as rf
+    from wavelettransforms_b200 import dwt_pruning, dwt_pruning_NoEntropy as ne
+    g = torch.Generator().manual_seed(31)
+    ws = [torch.randn(1, 1024, 1280, generator=g) * 0.02, torch.randn(2, 530, 517, generator=g) * 0.02, torch.randn(3, 2, 9, 12, generator=g) * 0.02]
+    got, gz = dwt_pruning.multi_resolution_analysis(ws, wavelet, level, 83.0, mode, clamp_level=False, arithmetic='fma_taporder')
+    with oracle_lib.arithmetic('fma_taporder'):
+        want, wz = rf.multi_resolution_analysis(ws, wavelet, level, 83.0, mode=mode, numpy_semantics='legacy_1_22', clamp_level=False)
+    assert gz == wz
+    for a, b in zip(got, want):
+        assert np.array_equal(_bits(a), _bits(b))
+    got, gp = ne.multi_resolution_analysis(ws, wavelet, level, 0.015, mode, arithmetic='fma_taporder')
+    with oracle_lib.arithmetic('fma_taporder'):
+        want, wp = rf.multi_resolution_analysis_absolute(ws, wavelet, level, 0.015, mode)
+    assert gp == wp
+    for a, b in zip(got, want):
+        assert np.array_equal(_bits(a), _bits(b))
+    # the two arithmetics do differ on these inputs (a silent fall-back to the faithful kernels would pass the checks above
+    # only if the oracle twin were broken too, but make it explicit)
+    slow, _ = ne.multi_resolution_analysis(ws, wavelet, level, 0.015, mode)
+    assert any(not np.array_equal(_bits(a), _bits(b)) for a, b in zip(got, slow)) or wavelet == 'haar'
+    for a, b in zip(got, slow):
+        np.testing.assert_allclose(a.numpy(), b.numpy(), rtol=1e-5, atol=1e-6)

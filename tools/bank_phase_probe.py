@@ -19,6 +19,8 @@ if __name__ == '__main__':
     outs = [torch.empty_like(x) for x in xs]
     items = [(x.data_ptr(), o.data_ptr()) + engine.plane_geometry(x.shape) + (level,) for x, o in zip(xs, outs)]
     plan = _lib.Plan(items, wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, 50.0, 'legacy_1_22')
+    if os.environ.get('WT_PROBE_ARITH'):
+        plan.set_arithmetic(os.environ['WT_PROBE_ARITH'])
     s = torch.cuda.Stream()
     with torch.cuda.stream(s):
         st = int(s.cuda_stream)

@@ -17,7 +17,7 @@ OBJDIR = os.path.join(HERE, 'build')
 LIB = os.path.join(LIBDIR, 'libwtprune.so')
 
 SOURCES = ['wt_fused_s7.cu', 'wt_fused_s5.cu', 'wt_fused_s3.cu', 'wt_fused_s1.cu', 'wt_small.cu', 'wt_small_fma.cu', 'wt_fused_flat.cu', 'wt_api.cu',
-           'wt_select.cu', 'wt_generic.cu', 'wt_maskers.cu', 'wt_blocks.cu', 'wt_noalloc.cu']  # heaviest first
+           'wt_select.cu', 'wt_generic.cu', 'wt_generic_fma.cu', 'wt_maskers.cu', 'wt_blocks.cu', 'wt_noalloc.cu']  # heaviest first
 # the fma_taporder instantiations of the fused kernels (wt_fused_s<N>f.cu) double the build time: WT_BUILD_FMA=1 adds them
 if os.environ.get('WT_BUILD_FMA'):
     SOURCES = ['wt_fused_s7f.cu', 'wt_fused_s5f.cu', 'wt_fused_s3f.cu', 'wt_fused_s1f.cu'] + SOURCES

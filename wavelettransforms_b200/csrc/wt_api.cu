@@ -1038,7 +1038,8 @@ static int plan_enqueue(WtPlan* P, cudaStream_t stream) {
     for (auto& g : P->generic) {
         snprintf(label, sizeof(label), "generic_analysis_layer%d", g.layer);
         mark(label);
-        rc = wt_generic_analysis(P->bank, P->mode, g, P->counts_dev, class_stream((size_t)(gi++ % P->gen_lanes)), &launches);
+        rc = (P->arithmetic ? wt_generic_analysis_fma : wt_generic_analysis)(P->bank, P->mode, g, P->counts_dev,
+                                                                             class_stream((size_t)(gi++ % P->gen_lanes)), &launches);
         if (rc) return rc;
     }
     if ((rc = join())) return rc;
@@ -1074,7 +1075,7 @@ static int plan_enqueue(WtPlan* P, cudaStream_t stream) {
     for (auto& g : P->generic) {
         snprintf(label, sizeof(label), "generic_synthesis_layer%d", g.layer);
         mark(label);
-        rc = wt_generic_synthesis(P->bank, P->mode, g, P->thresholds_dev, P->counts_dev, class_stream((size_t)(gi++ % P->gen_lanes)),
+        rc = (P->arithmetic ? wt_generic_synthesis_fma : wt_generic_synthesis)(P->bank, P->mode, g, P->thresholds_dev, P->counts_dev, class_stream((size_t)(gi++ % P->gen_lanes)),
                                   &launches);
         if (rc) return rc;
     }
@@ -1153,8 +1154,6 @@ extern "C" int wt_plan_set_arithmetic(WtPlan* P, int arithmetic) {
     WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
     WT_CHECK(arithmetic == WT_ARITH_FAITHFUL || arithmetic == WT_ARITH_FMA_TAPORDER, WT_E_INVALID, "unknown arithmetic %d", arithmetic);
     if (arithmetic == WT_ARITH_FMA_TAPORDER) {
-        WT_CHECK(P->generic.empty(), WT_E_UNSUPPORTED,
-                 "fma_taporder: not available for layers on the generic tiled path (large or odd planes, non-periodization modes)");
 #ifndef WT_WITH_FMA_KERNELS
         for (const auto& c : P->fused)
             WT_CHECK(c.H == 0, WT_E_UNSUPPORTED, "fma_taporder: this build has no fused small-plane kernels in that arithmetic "

@@ -16,6 +16,18 @@
 
 #include "wt_generic.cuh"
 
+// This file is compiled twice (wt_generic_fma.cu defines WT_GENERIC_FMA and includes it): the faithful arithmetic -- multiply,
+// then add, like PyWavelets' C loops without contraction -- and the named fast mode fma_taporder (include/wtprune.h), one
+// FMA per tap in the same tap order (oracle twin: orc_set_arithmetic(1)).  Boundary extrapolation (smooth / antireflect
+// modes) is not a tap and stays multiply-then-add in both.
+#ifdef WT_GENERIC_FMA
+#define WT_MAC(acc, tap, v) __fmaf_rn((tap), (v), (acc))
+#define WT_GEN_FN(name) name##_fma
+#else
+#define WT_MAC(acc, tap, v) __fadd_rn((acc), __fmul_rn((tap), (v)))
+#define WT_GEN_FN(name) name
+#endif
+
 namespace {
 
 constexpr int GEN_THREADS = 256;
@@ -151,8 +163,8 @@ wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_const
 #pragma unroll
                 for (int j = 0; j < F; ++j) {
                     const float v = top[cc - j * ics];
-                    sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
-                    sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+                    sl = WT_MAC(sl, bk.dec_lo[j], v);
+                    sh = WT_MAC(sh, bk.dec_hi[j], v);
                 }
                 const int d = (cc & 1) * half + (cc >> 1);
                 lo[d] = sl;
@@ -174,10 +186,10 @@ wt_generic_analysis_kernel(const __grid_constant__ WtBank bk, const __grid_const
                 for (int j = 0; j < F; ++j) {
                     const int idx = ((F - 1 - j) & 1) * half + cl + ((F - 1 - j) >> 1);
                     const float vl = rl[idx], vh = rh[idx];
-                    saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
-                    sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
-                    sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
-                    sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
+                    saa = WT_MAC(saa, bk.dec_lo[j], vl);
+                    sad = WT_MAC(sad, bk.dec_hi[j], vl);
+                    sda = WT_MAC(sda, bk.dec_lo[j], vh);
+                    sdd = WT_MAC(sdd, bk.dec_hi[j], vh);
                 }
                 const int c = c0 + cl;
                 P.aa.p[pl * P.aa.pstride + o * P.aa.rstride + c] = saa;
@@ -296,10 +308,10 @@ wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid
             float sl0 = 0.0f, sh0 = 0.0f, sl1 = 0.0f, sh1 = 0.0f;
 #pragma unroll
             for (int j = 0; j < F; ++j) {  // tap j of output row ol + q reads staged row 2*(ol + q) + F-1-j
-                sl0 = __fadd_rn(sl0, __fmul_rn(bk.dec_lo[j], v[F - 1 - j]));
-                sh0 = __fadd_rn(sh0, __fmul_rn(bk.dec_hi[j], v[F - 1 - j]));
-                sl1 = __fadd_rn(sl1, __fmul_rn(bk.dec_lo[j], v[F + 1 - j]));
-                sh1 = __fadd_rn(sh1, __fmul_rn(bk.dec_hi[j], v[F + 1 - j]));
+                sl0 = WT_MAC(sl0, bk.dec_lo[j], v[F - 1 - j]);
+                sh0 = WT_MAC(sh0, bk.dec_hi[j], v[F - 1 - j]);
+                sl1 = WT_MAC(sl1, bk.dec_lo[j], v[F + 1 - j]);
+                sh1 = WT_MAC(sh1, bk.dec_hi[j], v[F + 1 - j]);
             }
             const int d = (cc & 1) * FX_HALF + (cc >> 1);
             s_lo[ol * FX_LW + d] = sl0;
@@ -346,10 +358,10 @@ wt_generic_analysis_fixed_kernel(const __grid_constant__ WtBank bk, const __grid
             for (int q = 0; q < 2; ++q) {
                 const float vl = par ? lo_[q + sft] : le[q + sft];
                 const float vh = par ? ho[q + sft] : he[q + sft];
-                saa[q] = __fadd_rn(saa[q], __fmul_rn(bk.dec_lo[j], vl));
-                sad[q] = __fadd_rn(sad[q], __fmul_rn(bk.dec_hi[j], vl));
-                sda[q] = __fadd_rn(sda[q], __fmul_rn(bk.dec_lo[j], vh));
-                sdd[q] = __fadd_rn(sdd[q], __fmul_rn(bk.dec_hi[j], vh));
+                saa[q] = WT_MAC(saa[q], bk.dec_lo[j], vl);
+                sad[q] = WT_MAC(sad[q], bk.dec_hi[j], vl);
+                sda[q] = WT_MAC(sda[q], bk.dec_lo[j], vh);
+                sdd[q] = WT_MAC(sdd[q], bk.dec_hi[j], vh);
             }
         }
         const long long o = o0 + ol;
@@ -414,17 +426,17 @@ __device__ __forceinline__ float syn_sample(const float* a, const float* d, int 
         float acc = 0.0f;
 #pragma unroll
         for (int j = 0; j < hf; ++j)
-            acc = __fadd_rn(acc, __fmul_rn(par ? bk.rec_lo[2 * j + 1] : bk.rec_lo[2 * j], a[top - j * stride]));
+            acc = WT_MAC(acc, par ? bk.rec_lo[2 * j + 1] : bk.rec_lo[2 * j], a[top - j * stride]);
 #pragma unroll
         for (int j = 0; j < hf; ++j)
-            acc = __fadd_rn(acc, __fmul_rn(par ? bk.rec_hi[2 * j + 1] : bk.rec_hi[2 * j], d[top - j * stride]));
+            acc = WT_MAC(acc, par ? bk.rec_hi[2 * j + 1] : bk.rec_hi[2 * j], d[top - j * stride]);
         return acc;
     }
     float sl = 0.0f, sh = 0.0f;
 #pragma unroll
-    for (int j = 0; j < hf; ++j) sl = __fadd_rn(sl, __fmul_rn(par ? bk.rec_lo[2 * j + 1] : bk.rec_lo[2 * j], a[top - j * stride]));
+    for (int j = 0; j < hf; ++j) sl = WT_MAC(sl, par ? bk.rec_lo[2 * j + 1] : bk.rec_lo[2 * j], a[top - j * stride]);
 #pragma unroll
-    for (int j = 0; j < hf; ++j) sh = __fadd_rn(sh, __fmul_rn(par ? bk.rec_hi[2 * j + 1] : bk.rec_hi[2 * j], d[top - j * stride]));
+    for (int j = 0; j < hf; ++j) sh = WT_MAC(sh, par ? bk.rec_hi[2 * j + 1] : bk.rec_hi[2 * j], d[top - j * stride]);
     return __fadd_rn(__fadd_rn(0.0f, sl), sh);
 }
 
@@ -581,26 +593,26 @@ __device__ __forceinline__ void syn_pair(const float* a, const float* d, const W
         float e = 0.0f, o = 0.0f;
 #pragma unroll
         for (int j = 0; j < hf; ++j) {
-            e = __fadd_rn(e, __fmul_rn(bk.rec_lo[2 * j], va[j]));
-            o = __fadd_rn(o, __fmul_rn(bk.rec_lo[2 * j + 1], va[j]));
+            e = WT_MAC(e, bk.rec_lo[2 * j], va[j]);
+            o = WT_MAC(o, bk.rec_lo[2 * j + 1], va[j]);
         }
 #pragma unroll
         for (int j = 0; j < hf; ++j) {
-            e = __fadd_rn(e, __fmul_rn(bk.rec_hi[2 * j], vd[j]));
-            o = __fadd_rn(o, __fmul_rn(bk.rec_hi[2 * j + 1], vd[j]));
+            e = WT_MAC(e, bk.rec_hi[2 * j], vd[j]);
+            o = WT_MAC(o, bk.rec_hi[2 * j + 1], vd[j]);
         }
         o0 = e; o1 = o;
     } else {
         float le = 0.0f, lo = 0.0f, he = 0.0f, ho = 0.0f;
 #pragma unroll
         for (int j = 0; j < hf; ++j) {
-            le = __fadd_rn(le, __fmul_rn(bk.rec_lo[2 * j], va[j]));
-            lo = __fadd_rn(lo, __fmul_rn(bk.rec_lo[2 * j + 1], va[j]));
+            le = WT_MAC(le, bk.rec_lo[2 * j], va[j]);
+            lo = WT_MAC(lo, bk.rec_lo[2 * j + 1], va[j]);
         }
 #pragma unroll
         for (int j = 0; j < hf; ++j) {
-            he = __fadd_rn(he, __fmul_rn(bk.rec_hi[2 * j], vd[j]));
-            ho = __fadd_rn(ho, __fmul_rn(bk.rec_hi[2 * j + 1], vd[j]));
+            he = WT_MAC(he, bk.rec_hi[2 * j], vd[j]);
+            ho = WT_MAC(ho, bk.rec_hi[2 * j + 1], vd[j]);
         }
         o0 = __fadd_rn(__fadd_rn(0.0f, le), he);
         o1 = __fadd_rn(__fadd_rn(0.0f, lo), ho);
@@ -615,26 +627,26 @@ __device__ __forceinline__ void syn_pair_regs(const float (&va)[F / 2], const fl
         float e = 0.0f, o = 0.0f;
 #pragma unroll
         for (int j = 0; j < hf; ++j) {
-            e = __fadd_rn(e, __fmul_rn(bk.rec_lo[2 * j], va[j]));
-            o = __fadd_rn(o, __fmul_rn(bk.rec_lo[2 * j + 1], va[j]));
+            e = WT_MAC(e, bk.rec_lo[2 * j], va[j]);
+            o = WT_MAC(o, bk.rec_lo[2 * j + 1], va[j]);
         }
 #pragma unroll
         for (int j = 0; j < hf; ++j) {
-            e = __fadd_rn(e, __fmul_rn(bk.rec_hi[2 * j], vd[j]));
-            o = __fadd_rn(o, __fmul_rn(bk.rec_hi[2 * j + 1], vd[j]));
+            e = WT_MAC(e, bk.rec_hi[2 * j], vd[j]);
+            o = WT_MAC(o, bk.rec_hi[2 * j + 1], vd[j]);
         }
         o0 = e; o1 = o;
     } else {
         float le = 0.0f, lo = 0.0f, he = 0.0f, ho = 0.0f;
 #pragma unroll
         for (int j = 0; j < hf; ++j) {
-            le = __fadd_rn(le, __fmul_rn(bk.rec_lo[2 * j], va[j]));
-            lo = __fadd_rn(lo, __fmul_rn(bk.rec_lo[2 * j + 1], va[j]));
+            le = WT_MAC(le, bk.rec_lo[2 * j], va[j]);
+            lo = WT_MAC(lo, bk.rec_lo[2 * j + 1], va[j]);
         }
 #pragma unroll
         for (int j = 0; j < hf; ++j) {
-            he = __fadd_rn(he, __fmul_rn(bk.rec_hi[2 * j], vd[j]));
-            ho = __fadd_rn(ho, __fmul_rn(bk.rec_hi[2 * j + 1], vd[j]));
+            he = WT_MAC(he, bk.rec_hi[2 * j], vd[j]);
+            ho = WT_MAC(ho, bk.rec_hi[2 * j + 1], vd[j]);
         }
         o0 = __fadd_rn(__fadd_rn(0.0f, le), he);
         o1 = __fadd_rn(__fadd_rn(0.0f, lo), ho);
@@ -948,8 +960,8 @@ wt_generic_axis0_kernel(const __grid_constant__ WtBank bk, const __grid_constant
         float sl = 0.0f, sh = 0.0f;
         for (int j = 0; j < P.F; ++j) {
             const float v = ext_value(col, P.h, P.in.rstride, 1 + 2 * o - j, P.mode);
-            sl = __fadd_rn(sl, __fmul_rn(bk.dec_lo[j], v));
-            sh = __fadd_rn(sh, __fmul_rn(bk.dec_hi[j], v));
+            sl = WT_MAC(sl, bk.dec_lo[j], v);
+            sh = WT_MAC(sh, bk.dec_hi[j], v);
         }
         P.lo[i] = sl;
         P.hi[i] = sh;
@@ -971,10 +983,10 @@ wt_generic_axis1_kernel(const __grid_constant__ WtBank bk, const __grid_constant
         for (int j = 0; j < P.F; ++j) {
             const float vl = ext_value(rl, P.w, 1, 1 + 2 * c - j, P.mode);
             const float vh = ext_value(rh, P.w, 1, 1 + 2 * c - j, P.mode);
-            saa = __fadd_rn(saa, __fmul_rn(bk.dec_lo[j], vl));
-            sad = __fadd_rn(sad, __fmul_rn(bk.dec_hi[j], vl));
-            sda = __fadd_rn(sda, __fmul_rn(bk.dec_lo[j], vh));
-            sdd = __fadd_rn(sdd, __fmul_rn(bk.dec_hi[j], vh));
+            saa = WT_MAC(saa, bk.dec_lo[j], vl);
+            sad = WT_MAC(sad, bk.dec_hi[j], vl);
+            sda = WT_MAC(sda, bk.dec_lo[j], vh);
+            sdd = WT_MAC(sdd, bk.dec_hi[j], vh);
         }
         P.aa.p[p * P.aa.pstride + (long long)o * P.aa.rstride + c] = saa;
         P.ad.p[p * P.ad.pstride + (long long)o * P.ad.rstride + c] = sad;
@@ -1003,6 +1015,7 @@ wt_generic_axis1_kernel(const __grid_constant__ WtBank bk, const __grid_constant
     }
 
 // ---- host side -----------------------------------------------------------------------------------------
+#ifndef WT_GENERIC_FMA
 long long wt_generic_ncoef(int H, int W, int F, int mode, int level) {
     int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
     wt_level_sizes(H, F, mode, level, hs);
@@ -1042,6 +1055,8 @@ float* wt_generic_scratch(float* tmp, long long batch, int H, int W, int F, int 
     return mode > WT_MODE_SYMMETRIC ? tmp + batch * tmp_pingpong_elems(H, W, F, mode, level) : nullptr;
 }
 
+#endif  // !WT_GENERIC_FMA
+
 // ---- tensor maps for the fixed-geometry kernels ----------------------------------------------------------------
 // cuTensorMapEncodeTiled lives in the driver library; the entry point comes from the runtime, so libwtprune.so keeps
 // linking against cudart alone.
@@ -1079,7 +1094,7 @@ static bool make_plane_map(CUtensorMap* m, const WtView& v, long long batch, int
               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
+int WT_GEN_FN(wt_generic_analysis_level)(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
                               WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream, long long* nz_counts4,
                               int* nz_counted) {
     if (nz_counted) *nz_counted = 0;
@@ -1156,7 +1171,7 @@ int wt_generic_analysis_level(const WtBank& bank, int mode, WtView in, long long
     return WT_OK;
 }
 
-int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView da, WtView ad, WtView dd,
+int WT_GEN_FN(wt_generic_synthesis_level)(const WtBank& bank, int mode, WtView aa, WtView da, WtView ad, WtView dd,
                                long long batch, int h2, int w2, WtView out, int oh, int ow, const float* thr_dev,
                                float thr_host, int use_thr, int thr_a, long long* counts4, cudaStream_t stream) {
     SynParams P;
@@ -1224,6 +1239,7 @@ int wt_generic_synthesis_level(const WtBank& bank, int mode, WtView aa, WtView d
     return WT_OK;
 }
 
+#ifndef WT_GENERIC_FMA
 int wt_count_nonzero_launch(const float* x, long long n, long long* counts4, cudaStream_t stream) {
     if (n <= 0) return WT_OK;
     WtDeviceInfo di;
@@ -1236,6 +1252,8 @@ int wt_count_nonzero_launch(const float* x, long long n, long long* counts4, cud
 }
 
 // flat coefficient layout: [cA_L | L: da, ad, dd | ... | 1: da, ad, dd]
+#endif  // !WT_GENERIC_FMA
+
 static void band_offsets(const WtGenericLayer& L, int F, int mode, int* hs, int* ws, long long* off /*[level+1][3]*/,
                          long long* off_a) {
     wt_level_sizes(L.H, F, mode, L.level, hs);
@@ -1251,7 +1269,7 @@ static void band_offsets(const WtGenericLayer& L, int F, int mode, int* hs, int*
     }
 }
 
-int wt_generic_analysis(const WtBank& bank, int mode, const WtGenericLayer& L, long long* counts, cudaStream_t stream,
+int WT_GEN_FN(wt_generic_analysis)(const WtBank& bank, int mode, const WtGenericLayer& L, long long* counts, cudaStream_t stream,
                         int* launches) {
     int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
     long long off[(WT_MAX_LEVEL + 1) * 3], off_a;
@@ -1274,7 +1292,7 @@ int wt_generic_analysis(const WtBank& bank, int mode, const WtGenericLayer& L, l
         // level 1 reads the whole input anyway: the fixed-geometry kernel counts its nonzeros (counts[3], dwt_pruning_NoEntropy.py:58)
         // from the staged tiles; when another kernel takes the level, the count is a pass of its own
         int counted = 0;
-        rc = wt_generic_analysis_level(bank, mode, cur, L.batch, hs[l - 1], ws[l - 1], aa, da, ad, dd, scratch, stream,
+        rc = WT_GEN_FN(wt_generic_analysis_level)(bank, mode, cur, L.batch, hs[l - 1], ws[l - 1], aa, da, ad, dd, scratch, stream,
                                        l == 1 ? counts + (size_t)L.layer * 4 : nullptr, l == 1 ? &counted : nullptr);
         if (rc) return rc;
         *launches += (mode > WT_MODE_SYMMETRIC) ? 2 : 1;
@@ -1288,7 +1306,7 @@ int wt_generic_analysis(const WtBank& bank, int mode, const WtGenericLayer& L, l
     return WT_OK;
 }
 
-int wt_generic_synthesis(const WtBank& bank, int mode, const WtGenericLayer& L, const float* thresholds,
+int WT_GEN_FN(wt_generic_synthesis)(const WtBank& bank, int mode, const WtGenericLayer& L, const float* thresholds,
                          long long* counts, cudaStream_t stream, int* launches) {
     int hs[WT_MAX_LEVEL + 1], ws[WT_MAX_LEVEL + 1];
     long long off[(WT_MAX_LEVEL + 1) * 3], off_a;
@@ -1303,7 +1321,7 @@ int wt_generic_synthesis(const WtBank& bank, int mode, const WtGenericLayer& L, 
         WtView da = wt_view(L.coef + off[l * 3 + 0], hs[l], ws[l]);
         WtView ad = wt_view(L.coef + off[l * 3 + 1], hs[l], ws[l]);
         WtView dd = wt_view(L.coef + off[l * 3 + 2], hs[l], ws[l]);
-        int rc = wt_generic_synthesis_level(bank, mode, cur, da, ad, dd, L.batch, hs[l], ws[l], out, oh, ow, thr_dev,
+        int rc = WT_GEN_FN(wt_generic_synthesis_level)(bank, mode, cur, da, ad, dd, L.batch, hs[l], ws[l], out, oh, ow, thr_dev,
                                             L.abs_threshold, 1, l == L.level, l == 1 ? counts + (size_t)L.layer * 4 : nullptr,
                                             stream);
         if (rc) return rc;

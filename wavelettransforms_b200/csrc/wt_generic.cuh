@@ -55,5 +55,17 @@ int wt_generic_analysis(const WtBank& bank, int mode, const WtGenericLayer& L, l
 int wt_generic_synthesis(const WtBank& bank, int mode, const WtGenericLayer& L, const float* thresholds,
                          long long* counts, cudaStream_t stream, int* launches);
 
+// the same four in the named fast mode fma_taporder (wt_generic_fma.cu: one FMA per tap, same tap order)
+int wt_generic_analysis_level_fma(const WtBank& bank, int mode, WtView in, long long batch, int h, int w, WtView aa,
+                                  WtView da, WtView ad, WtView dd, float* scratch, cudaStream_t stream,
+                                  long long* nz_counts4 = nullptr, int* nz_counted = nullptr);
+int wt_generic_synthesis_level_fma(const WtBank& bank, int mode, WtView aa, WtView da, WtView ad, WtView dd,
+                                   long long batch, int h2, int w2, WtView out, int oh, int ow, const float* thr_dev,
+                                   float thr_host, int use_thr, int thr_a, long long* counts4, cudaStream_t stream);
+int wt_generic_analysis_fma(const WtBank& bank, int mode, const WtGenericLayer& L, long long* counts, cudaStream_t stream,
+                            int* launches);
+int wt_generic_synthesis_fma(const WtBank& bank, int mode, const WtGenericLayer& L, const float* thresholds,
+                             long long* counts, cudaStream_t stream, int* launches);
+
 // counts4[3] += count(x != 0); counts4[0] = n
 int wt_count_nonzero_launch(const float* x, long long n, long long* counts4, cudaStream_t stream);
