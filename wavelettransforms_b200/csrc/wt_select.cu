@@ -797,8 +797,8 @@ __device__ void phase_tail(const WtSelArgs& a, Shared& sh) {
 __device__ void phase_c1_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
         WtSelState* st = &a.state[j];
-        if (__ldcg(&st->tail_done) || __ldcg(&st->failed)) return;  // settled by the one-CTA tail
         const unsigned int n_bins = __ldcg(&st->n_bins), n_c = __ldcg(&st->s_count);
+        if (n_c <= a.tail_max) return;  // the one-CTA tail's job (it runs in this same phase: its flags are not read here)
         const unsigned long long below = __ldcg(&st->below);
         unsigned long long e0, e1;
         explicit_ranks(job, e0, e1);
@@ -1148,12 +1148,14 @@ __global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs 
             acc.stamp(2);
             grid.sync();
         }
+        // one phase: the short lists are finished by one CTA each (tail), the long ones (s_count > tail_max, final since the
+        // last barrier) get their first-digit histogram from everybody (C1) meanwhile -- round 1 ran the tail, a barrier, then
+        // C1: at p = 90 the headline's three 146 k-key lists made every step pay both, one after the other
         phase_tail(a, sh);
         acc.stamp(3);
+        phase_c1_cand(a, sh, t_begin, t_end, acc);
         grid.sync();
         if (__ldcg(a.big_flag) != 0) {  // grid-uniform (final before the last barrier): some list is too long for one CTA
-            phase_c1_cand(a, sh, t_begin, t_end, acc);
-            grid.sync();
             phase_c2_cand(a, sh, t_begin, t_end, acc);
             acc.stamp(4);
             grid.sync();
