@@ -49,6 +49,12 @@
 
 namespace cg = cooperative_groups;
 
+// longest candidate list the one-CTA tail takes when some other list needs the grid passes anyway (see wt_select_kernel;
+// WT_SEL_TAIL_MAX in wt_common.cuh is the limit when none does).  Sweep 2048 .. 32768 on the headline: 8192 is the minimum.
+#ifndef WT_SEL_TAIL_SHORT
+#define WT_SEL_TAIL_SHORT 8192u
+#endif
+
 namespace {
 
 constexpr int T = WT_SEL_THREADS;
@@ -728,7 +734,7 @@ __device__ void phase_s1_compact(const WtSelArgs& a, Shared& sh, int t_begin, in
 // over the job's candidate list, which is short (5 sigma of the sampling error: ~1e4 keys) and L2-resident.  CTA-local
 // barriers only -- the grid-wide candidate passes C1..C3 cost a grid barrier, a flush and 296 redundant scans each
 // and are kept for the lists this CTA would take too long over (big_flag).
-__device__ void phase_tail(const WtSelArgs& a, Shared& sh) {
+__device__ void phase_tail(const WtSelArgs& a, Shared& sh, unsigned int tail_max) {
     for (int j = blockIdx.x; j < a.n_jobs; j += gridDim.x) {
         const WtSelJob job = a.jobs[j];
         WtSelState* st = &a.state[j];
@@ -747,7 +753,7 @@ __device__ void phase_tail(const WtSelArgs& a, Shared& sh) {
             if (threadIdx.x == 0) { st->failed = 1; *a.fail_flag = 1; }
             continue;
         }
-        if (n_c > a.tail_max) {
+        if (n_c > tail_max) {
             if (threadIdx.x == 0) *a.big_flag = 1;
             continue;
         }
@@ -794,11 +800,11 @@ __device__ void phase_tail(const WtSelArgs& a, Shared& sh) {
 }
 
 // ---- C1: verify the bracket; histogram of the top 12 bits of key - lo_key over the candidate list -> hist2 ------
-__device__ void phase_c1_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc) {
+__device__ void phase_c1_cand(const WtSelArgs& a, Shared& sh, int t_begin, int t_end, Acc& acc, unsigned int tail_max) {
     for_each_segment(a, t_begin, t_end, [&](int j, const WtSelJob& job, long long base, long long len, int tiles) {
         WtSelState* st = &a.state[j];
         const unsigned int n_bins = __ldcg(&st->n_bins), n_c = __ldcg(&st->s_count);
-        if (n_c <= a.tail_max) return;  // the one-CTA tail's job (it runs in this same phase: its flags are not read here)
+        if (n_c <= tail_max) return;  // the one-CTA tail's job (it runs in this same phase: its flags are not read here)
         const unsigned long long below = __ldcg(&st->below);
         unsigned long long e0, e1;
         explicit_ranks(job, e0, e1);
@@ -1151,9 +1157,19 @@ __global__ void __launch_bounds__(WT_SEL_THREADS, 2) wt_select_kernel(WtSelArgs 
         // one phase: the short lists are finished by one CTA each (tail), the long ones (s_count > tail_max, final since the
         // last barrier) get their first-digit histogram from everybody (C1) meanwhile -- round 1 ran the tail, a barrier, then
         // C1: at p = 90 the headline's three 146 k-key lists made every step pay both, one after the other
-        phase_tail(a, sh);
+        // How long a list the tail takes depends on whether the grid passes run anyway: when no list exceeds tail_max, every
+        // job ends in its tail and C2 / C3 never start (p = 50: 179 us against 200); when one does, C2 will run, and lists
+        // over WT_SEL_TAIL_SHORT go with it rather than keep one CTA busy for three passes (p = 90: 195 us against 201).
+        // The counts are final since the last barrier, so every CTA takes the same decision.
+        unsigned int tail_max = a.tail_max;
+        {
+            bool big = false;
+            for (int j = threadIdx.x; j < a.n_jobs; j += T) big |= __ldcg(&a.state[j].s_count) > a.tail_max;
+            if (__syncthreads_or(big) && tail_max > WT_SEL_TAIL_SHORT) tail_max = WT_SEL_TAIL_SHORT;
+        }
+        phase_tail(a, sh, tail_max);
         acc.stamp(3);
-        phase_c1_cand(a, sh, t_begin, t_end, acc);
+        phase_c1_cand(a, sh, t_begin, t_end, acc, tail_max);
         grid.sync();
         if (__ldcg(a.big_flag) != 0) {  // grid-uniform (final before the last barrier): some list is too long for one CTA
             phase_c2_cand(a, sh, t_begin, t_end, acc);
