@@ -150,8 +150,8 @@ int wt_plan_set_timing(WtPlan* plan, int enable);
  * and bypassed while phase timing is on.  A stream that cannot be captured (the legacy default stream) makes the plan
  * fall back to plain launches silently -- same results.  Device plans only run through it; a host-I/O plan forwards
  * the switch to the device plans of its layer groups.  Default (neither this call nor WT_GRAPH=0|1 in the environment when
- * the plan is created): automatic -- plans with layers on the large-plane kernels (a dozen short dependent launches per
- * plane) replay from their second run on, conv-weight plans launch plainly (measured gain 1 %, single-launch plans lose 1 %).
+ * the plan is created): automatic -- plans of four or more launches per run replay from their second run on (measured:
+ * 1.5-2 % on conv-weight plans, 2-7 % on large-plane plans); single-launch plans (the level-0 flows) launch plainly.
  */
 int wt_plan_set_graph(WtPlan* plan, int enable);
 /* Arithmetic of the DWT multiply-adds.  WT_ARITH_FAITHFUL (default): fp32 multiply, then fp32 add, no FMA,

@@ -441,6 +441,7 @@ static int upload_tables(WtPlan* P) {
 }
 
 static void drop_graphs(WtPlan* P);
+#define WT_GRAPH_AUTO_MIN_LAUNCHES 4
 
 extern "C" int wt_plan_destroy(WtPlan* P) {
     if (!P) return WT_OK;
@@ -1099,10 +1100,10 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     const int par = (int)(P->run_count & 1ull);   // both alternations flip once per run
     advance_run_state(P);
     ++P->run_count;
-    // automatic: a plan with large-plane layers is a dozen dependent launches per plane, several of them a few microseconds long
-    // (the deep levels): replaying them as a graph measured 2-7 %; conv-weight plans gain 1 % and
-    // single-launch plans lose 1 %, so they stay on plain launches unless asked
-    const bool want_graph = P->use_graph > 0 || (P->use_graph < 0 && !P->generic.empty() && P->n_launches >= 8);
+    // automatic: from its second run on, a plan of several dependent launches (with the forks onto the class streams and the
+    // joins in between) replays them as a graph: 1.5-2 % on the conv-weight plans (7 launches), 2-7 % on large-plane plans
+    // (a dozen short launches per plane); single-launch plans (the level-0 flows) gain nothing and stay on plain launches
+    const bool want_graph = P->use_graph > 0 || (P->use_graph < 0 && P->n_launches >= WT_GRAPH_AUTO_MIN_LAUNCHES);
     const bool graphable = want_graph && !P->graph_failed && !P->timing && P->stamps_dev == nullptr && getenv("WT_FUSED_STAMPS") == nullptr;
     if (!graphable) return plan_enqueue(P, stream);
     if (!P->graph_exec[par]) {
