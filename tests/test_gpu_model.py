@@ -235,3 +235,42 @@ def test_background_save_of_a_cuda_model_overlaps_the_next_method(tmp_path, monk
         assert not sd[k].is_cuda and torch.equal(sd[k], want[k]), k      # the snapshot, not the pruned weights
     for w, n in zip(ws, nz):
         assert int(torch.count_nonzero(w)) == n == w.numel() - w.numel() // 2
+
+
+def test_three_methods_on_three_streams_equal_the_three_walkers_arithmetic():
+    """three_streams.prune_three_ways (one upload, DWT on the caller's stream, the two comparison maskers
+    forked onto two more streams) against the same three steps done one after the other on one stream"""
+    from wavelettransforms_b200 import dwt_pruning, engine, three_streams
+    dev = torch.device('cuda', 0)
+    g = torch.Generator().manual_seed(12)
+    ws = [torch.randn(64, 3, 7, 7, generator=g) * 0.05, torch.randn(128, 64, 3, 3, generator=g) * 0.02,
+          torch.randn(256, 128, 1, 1, generator=g) * 0.02, torch.randn(96, 96, 3, 3, generator=g) * 0.03]
+    keep = [w.clone() for w in ws]
+    torch.manual_seed(77)
+    got = three_streams.prune_three_ways(ws, 'haar', 5, 60.0)
+    torch.cuda.synchronize()
+    for w, k in zip(ws, keep):
+        assert torch.equal(w, k)                                                     # inputs untouched
+    # selective: the drop-in's own function
+    want, _ = dwt_pruning.multi_resolution_analysis(ws, 'haar', 5, 60.0)
+    sel, sel_counts = got['selective']
+    for a, b in zip(sel, want):
+        assert np.array_equal(a.cpu().numpy().view(np.uint32), b.cpu().numpy().view(np.uint32))
+    numel = np.array([w.numel() for w in ws])
+    pruned = numel - sel_counts[:, 1]
+    assert np.array_equal(sel_counts[:, 0], numel) and pruned.sum() > 0
+    # min-weight: the DWT's overall fraction, grouped call, one stream
+    pct = float(pruned.sum()) / float(numel.sum())
+    mn = [w.to(dev).clone() for w in ws]
+    nz = engine.min_weight_prune_(mn, [int(m.numel() * pct) for m in mn])
+    for a, b in zip(got['min'][0], mn):
+        assert torch.equal(a, b)
+    assert list(got['min'][1][:, 1]) == nz
+    # random: the DWT's per-layer counts, torch.randperm drawn in layer order from the same seed
+    torch.manual_seed(77)
+    for w, k, a, row in zip(ws, pruned, got['random'][0], got['random'][1]):
+        r = w.to(dev).clone().view(-1)
+        idx = torch.randperm(r.numel(), device=dev)[:int(k)]
+        r[idx] = 0
+        assert torch.equal(a.view(-1), r)
+        assert row[1] == int(torch.count_nonzero(r)) and row[2] == row[0] - row[1]

@@ -226,6 +226,22 @@ def scatter_zero_group_(ws: List[torch.Tensor], idxs: List[torch.Tensor]) -> Lis
     return [int(v) for v in counts.cpu().tolist()]
 
 
+def scatter_zero_group_async_(ws: List[torch.Tensor], idxs: List[torch.Tensor]) -> torch.Tensor:
+    """scatter_zero_group_ without the host synchronisation: returns the int64 CUDA tensor of nonzero counts, valid in
+    stream order (the caller reads it when it needs the numbers)"""
+    dev = ws[0].device if ws else cuda_device()
+    counts = torch.empty(len(ws), dtype=torch.int64, device=dev)
+    L, s = _lib.lib(), _stream_ptr()
+    for i, (w, idx) in enumerate(zip(ws, idxs)):
+        _check_fp32(w)
+        if not w.is_contiguous():
+            raise ValueError('scatter_zero_group_async_ needs contiguous tensors')
+        idx = idx.to(device=dev, dtype=torch.int64).contiguous()
+        idx.record_stream(torch.cuda.current_stream())
+        _lib.check(L.wt_scatter_zero_f32(w.data_ptr(), w.numel(), idx.data_ptr(), idx.numel(), counts[i:].data_ptr(), s))
+    return counts
+
+
 def count_nonzero_and_below(x: torch.Tensor, eps: float = 1e-6) -> Tuple[int, int]:
     """(torch.count_nonzero(x), (|x| < eps).sum())  -- calculate_sparsity, testing_suite/eval_model.py:7-20"""
     _check_fp32(x)
