@@ -198,6 +198,13 @@ int wt_dwt_prune_f32(const WtLayerDesc* layers, int n_layers, int wavelet_id, in
                      int64_t* counts, int64_t* nonzero_before, float* thresholds);
 
 /* ---- building blocks (exposed for tests and for callers that keep coefficients) ------------- */
+/* One radix pass of a DISTRIBUTED exact select (intra-layer multi-GPU split; the reference has no
+ * counterpart: np.percentile sees one array, dwt_pruning.py:27).  hist[d] += number of elements of x whose key (the bit
+ * pattern of |x|, 31 bits) has `prefix` in its top prefix_bits bits and d in the next digit_bits (<= 12) bits.  The caller
+ * zeroes hist, sums it over the ranks (all-reduce) and descends: 12 + 10 + 9 bits give the exact k-th smallest |x| of the
+ * union (wavelettransforms_b200/sharded.py: prune_tensor_split).  Device pointers; nothing is synchronised. */
+int wt_key_hist_f32(const float* x, int64_t n, uint32_t prefix, int prefix_bits, int digit_bits, uint64_t* hist, void* stream);
+
 
 /* Exact order statistics of |x| over a population of n explicit values plus `implicit_zeros`
  * zeros: ab_out[0] = sorted[k0], ab_out[1] = sorted[k1] (device float[2]).  Replaces the

@@ -76,3 +76,28 @@ def test_sharded_gpu_peer_store_equals_allgather(wtlib, oracle_lib, pg):
         for i, w in enumerate(host):
             want, _ = rf.multi_resolution_analysis([w], wavelet, level, 50.0, numpy_semantics='legacy_1_22', clamp_level=clamp)
             assert np.array_equal(b[i].cpu().numpy().view(np.uint32), want[0].numpy().view(np.uint32)), census[i][0]
+
+
+@pytest.mark.parametrize('wavelet,level,shape,pct', [('bior2.2', 2, (37, 8, 3, 3), 70.0), ('haar', 1, (64, 16, 3, 3), 50.0),
+                                                     ('db4', 3, (5, 200, 264), 83.0), ('bior4.4', 0, (300, 7, 1, 1), 35.0),
+                                                     ('db2', 2, (1, 130, 130), 61.8), ('haar', 0, (513,), 90.0)])
+def test_intra_layer_split_equals_the_single_gpu_plan(pg, wavelet, level, shape, pct):
+    """one tensor's planes over the ranks, threshold agreed by the distributed radix select (wt_key_hist_f32 +
+    all-reduce): the gathered result, the threshold and the zero count equal the single-GPU percentile plan, bit for bit.
+    World size 1 under plain pytest; `torchrun --nproc-per-node N -m pytest tests/test_gpu_sharded.py` runs it on N GPUs."""
+    from wavelettransforms_b200 import _lib, dwt_pruning, engine, sharded
+    g = torch.Generator().manual_seed(21)
+    w = torch.randn(shape, generator=g) * 0.05
+    w.view(-1)[::11] = 0.0
+    got, t, zeros = sharded.prune_tensor_split(w, wavelet, level, pct)
+    want, wz = dwt_pruning.multi_resolution_analysis([w], wavelet, level, pct, clamp_level=False)
+    assert zeros == wz
+    assert np.array_equal(got.cpu().numpy().view(np.uint32), want[0].cpu().numpy().view(np.uint32))
+    dev = torch.device('cuda', torch.cuda.current_device())
+    ref = engine.prune_device_tensors([w.to(dev)], [level if w.ndim >= 2 else 0], wavelet, 'periodization', _lib.THRESHOLD_PERCENTILE, pct)
+    assert np.float32(t).view(np.uint32) == np.float32(ref.thresholds[0]).view(np.uint32)
+    # without the gather every rank holds its own planes
+    part, _, _ = sharded.prune_tensor_split(w, wavelet, level, pct, gather=False)
+    b, H, W = engine.plane_geometry(w.shape)
+    lo, hi = sharded.plane_slice(b, dist.get_rank(), dist.get_world_size())
+    assert np.array_equal(part.cpu().numpy().view(np.uint32), want[0].reshape(b, H, W)[lo:hi].cpu().numpy().view(np.uint32))

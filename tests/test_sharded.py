@@ -173,3 +173,68 @@ def test_peer_store_falls_back_on_all_ranks_together(oracle_lib):
         assert barriers == 1                   # the entry barrier of a reused buffer only: no peer-store barrier after the fallback
         for got, exp in zip(pruned, want):
             assert np.array_equal(got.view(np.uint32), exp.view(np.uint32))
+
+
+# ---- intra-layer split: the distributed exact select (host logic on CPU, numpy standing in for wt_key_hist_f32) ----------
+def _kth_worker(rank, world, port, out_q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from wavelettransforms_b200 import sharded
+        rng = np.random.default_rng(100)
+        full = (rng.standard_normal(20011) * 0.05).astype(np.float32)
+        full[::7] = 0.0                       # a massive tie at zero
+        full[5::97] = full[3]                 # and ties elsewhere
+        lo, hi = sharded.plane_slice(len(full), rank, world)
+        keys = full[lo:hi].view(np.uint32) & np.uint32(0x7fffffff)
+
+        def local_hist(prefix, prefix_bits, digit_bits):
+            sel = keys if prefix_bits == 0 else keys[(keys >> np.uint32(31 - prefix_bits)) == np.uint32(prefix)]
+            digit = (sel >> np.uint32(31 - prefix_bits - digit_bits)) & np.uint32((1 << digit_bits) - 1)
+            return np.bincount(digit.astype(np.int64), minlength=1 << digit_bits)
+
+        got = [sharded.global_kth_key(k, local_hist) for k in (0, 1, 2858, 2859, 10005, 20010)]
+        out_q.put((rank, got))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world', [2, 3])
+def test_distributed_kth_key_is_exact(world):
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_kth_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    rng = np.random.default_rng(100)
+    full = (rng.standard_normal(20011) * 0.05).astype(np.float32)
+    full[::7] = 0.0
+    full[5::97] = full[3]
+    s = np.sort(np.abs(full))
+    want = [int(np.float32(s[k]).view(np.uint32)) for k in (0, 1, 2858, 2859, 10005, 20010)]
+    for rank, got in results:
+        assert got == want, rank
+
+
+def test_plane_slice_and_percentile_lerp_match_the_oracle(oracle_lib):
+    from wavelettransforms_b200 import sharded
+    for batch in (0, 1, 5, 8, 17):
+        for world in (1, 2, 3, 8):
+            cuts = [sharded.plane_slice(batch, r, world) for r in range(world)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == batch
+            assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))
+            assert max(h - l for l, h in cuts) - min(h - l for l, h in cuts) <= 1
+    rng = np.random.default_rng(3)
+    for _ in range(2000):
+        a, b = np.sort(np.abs(rng.standard_normal(2).astype(np.float32) * np.float32(10.0 ** rng.integers(-20, 3))))
+        g = float(rng.random()) if rng.random() < 0.9 else float(rng.integers(0, 2))
+        for sem, idx in (('legacy_1_22', 0), ('nep50_2x', 1)):
+            got = sharded.percentile_lerp(a, b, g, sem)
+            want = oracle_lib.percentile_lerp(a, b, g, idx)
+            assert np.float32(got).view(np.uint32) == np.float32(want).view(np.uint32), (a, b, g, sem)

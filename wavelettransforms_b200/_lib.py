@@ -29,7 +29,7 @@ EXPORTS = [
     'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device', 'wt_plan_thresholds_device',
     'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path', 'wt_plan_set_arithmetic', 'wt_plan_set_multicast', 'wt_plan_set_graph',
     'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_select_abs_noalloc_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
-    'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32',
+    'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32', 'wt_key_hist_f32',
 ]
 
 _LIB = None
@@ -79,6 +79,7 @@ def lib():
     L.wt_min_weight_prune_f32.argtypes = [P(vp), P(i64), P(i64), ci, vp, P(i64)]
     L.wt_scatter_zero_f32.argtypes = [vp, i64, vp, i64, vp, vp]
     L.wt_count_f32.argtypes = [vp, i64, fl, vp, vp]
+    L.wt_key_hist_f32.argtypes = [vp, i64, ctypes.c_uint32, ci, ci, vp, vp]
     _LIB = L
     return L
 

@@ -171,3 +171,50 @@ extern "C" int wt_waverec2_packed_f32(const float* packed, int64_t batch, int H,
     }
     return rc;
 }
+
+// ---- wt_key_hist_f32: one radix pass of a DISTRIBUTED order-statistic select --------------------------------------
+// A tensor whose planes are split over several GPUs (intra-layer split) needs np.percentile over the union
+// of every rank's coefficients.  Each rank histograms one digit of its own keys (bit pattern of |x|, 31 bits) under a
+// prefix, the caller sums the histograms over the ranks (NCCL all-reduce of digit_bits <= 12 -> at most 32 KB) and walks
+// down: three passes (12 + 10 + 9 bits) give the exact k-th smallest of the union.  hist is ACCUMULATED into (the caller
+// zeroes it), so several tensors can share one histogram.
+namespace {
+constexpr int KH_THREADS = 512;
+__global__ void __launch_bounds__(KH_THREADS) wt_key_hist_kernel(const float* __restrict__ x, long long n, unsigned int prefix,
+                                                                 int prefix_bits, int digit_bits, unsigned long long* hist) {
+    __shared__ unsigned int sh[4096];
+    const int nb = 1 << digit_bits;
+    for (int b = threadIdx.x; b < nb; b += KH_THREADS) sh[b] = 0u;
+    __syncthreads();
+    const int below = 31 - prefix_bits - digit_bits;          // key bits under the digit
+    const unsigned int mask = (unsigned int)nb - 1u;
+    const long long stride = (long long)gridDim.x * KH_THREADS;
+    for (long long i = (long long)blockIdx.x * KH_THREADS + threadIdx.x; i < n; i += stride) {
+        const unsigned int key = __float_as_uint(__ldcg(&x[i])) & 0x7fffffffu;
+        if (prefix_bits == 0 || (key >> (31 - prefix_bits)) == prefix) atomicAdd(&sh[(key >> below) & mask], 1u);
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < nb; b += KH_THREADS) {
+        const unsigned int v = sh[b];
+        if (v) atomicAdd(&hist[b], (unsigned long long)v);
+    }
+}
+}  // namespace
+
+extern "C" int wt_key_hist_f32(const float* x, int64_t n, uint32_t prefix, int prefix_bits, int digit_bits, uint64_t* hist,
+                               void* stream_) {
+    WT_CHECK(n >= 0 && hist != nullptr && (n == 0 || x != nullptr), WT_E_INVALID, "bad argument");
+    WT_CHECK(prefix_bits >= 0 && digit_bits >= 1 && digit_bits <= 12 && prefix_bits + digit_bits <= 31, WT_E_INVALID,
+             "wt_key_hist_f32: prefix_bits + digit_bits must stay within the 31 key bits, digit_bits within 1..12");
+    WT_CHECK(prefix_bits == 0 || prefix_bits == 31 || (prefix >> prefix_bits) == 0u, WT_E_INVALID, "prefix wider than prefix_bits");
+    if (n == 0) return WT_OK;
+    WtDeviceInfo di;
+    int rc = wt_device_info(&di);
+    if (rc) return rc;
+    const long long want = (n + KH_THREADS * 8 - 1) / (KH_THREADS * 8);
+    const int grid = (int)std::max<long long>(1, std::min<long long>(want, (long long)di.sm_count * 4));
+    wt_key_hist_kernel<<<grid, KH_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(x, (long long)n, prefix, prefix_bits, digit_bits,
+                                                                                     reinterpret_cast<unsigned long long*>(hist));
+    WT_CUDA(cudaGetLastError());
+    return WT_OK;
+}

@@ -235,3 +235,114 @@ def prune_model_sharded(weights: List[torch.Tensor], wavelet: str, level: int, p
             levels.append(min(level, _lib.dwt_max_level(min(w.shape[-2:]), F)) if clamp_level else level)
     fn = _gpu_prune_fn(wavelet, mode, _lib.THRESHOLD_PERCENTILE, float(percentile), numpy_semantics or config.numpy_semantics)
     return prune_sharded(weights, levels, fn, group=group, gather=gather)
+
+
+# ---- intra-layer split: ONE tensor's planes over the ranks -----------------------------------------
+# The planes of a tensor transform independently, but its percentile is ONE order statistic over every plane's
+# coefficients (dwt_pruning.py:27 on the packed array of the whole tensor).  Each rank transforms its planes, the ranks
+# agree on the threshold by an exact distributed radix select -- per pass a digit histogram of the local keys, summed by an
+# all-reduce of at most 32 KB -- and every rank then thresholds and reconstructs its own planes.  This is the one place on
+# the path with a real exchange step; layer sharding above needs none.
+
+HistFn = Callable[[int, int, int], np.ndarray]    # (prefix, prefix_bits, digit_bits) -> local int64 histogram [2**digit_bits]
+KEY_BITS = 31
+RADIX_DIGITS = (12, 10, 9)
+
+
+def global_kth_key(k: int, local_hist: HistFn, group=None) -> int:
+    """the k-th smallest (0-based) 31-bit key of the union of every rank's keys: three passes, one all-reduce each"""
+    prefix, prefix_bits = 0, 0
+    for digit_bits in RADIX_DIGITS:
+        h = torch.as_tensor(np.asarray(local_hist(prefix, prefix_bits, digit_bits), dtype=np.int64))
+        if dist.is_initialized() and dist.get_world_size(group) > 1:
+            dev_h = h.cuda() if dist.get_backend(group) == 'nccl' else h
+            dist.all_reduce(dev_h, op=dist.ReduceOp.SUM, group=group)
+            h = dev_h.cpu()
+        c = np.cumsum(h.numpy())
+        d = int(np.searchsorted(c, k, side='right'))
+        if d >= len(c):
+            raise ValueError(f'rank {k} beyond the {int(c[-1])} keys under prefix {prefix:#x}')
+        k -= int(c[d - 1]) if d else 0
+        prefix, prefix_bits = (prefix << digit_bits) | d, prefix_bits + digit_bits
+    return prefix
+
+
+def percentile_lerp(a: np.float32, b: np.float32, gamma: float, numpy_semantics: str) -> np.float32:
+    """the interpolation step of np.percentile exactly as libwtprune's kernels do it (csrc/wt_select.cu: lerp_threshold):
+    'legacy_1_22' = (b - a) in float32, the rest in float64, result demoted; 'nep50_2x' = all float32"""
+    a, b = np.float32(a), np.float32(b)
+    if numpy_semantics == 'legacy_1_22':
+        d = np.float64(np.float32(b - a))
+        g = np.float64(gamma)
+        t = np.float64(b) - d * (np.float64(1.0) - g) if g >= 0.5 else np.float64(a) + d * g
+        return np.float32(t)
+    g = np.float32(gamma)
+    d = np.float32(b - a)
+    return np.float32(b - np.float32(d * np.float32(np.float32(1.0) - g))) if g >= np.float32(0.5) else np.float32(a + np.float32(d * g))
+
+
+def plane_slice(batch: int, rank: int, world: int) -> Tuple[int, int]:
+    """contiguous share of `batch` planes for `rank` (the first batch % world ranks take one more)"""
+    q, r = divmod(batch, world)
+    lo = rank * q + min(rank, r)
+    return lo, lo + q + (1 if rank < r else 0)
+
+
+def prune_tensor_split(w: torch.Tensor, wavelet: str, level: int, percentile: float, *, mode: str = 'periodization',
+                       numpy_semantics: Optional[str] = None, group=None, gather: bool = True):
+    """multi_resolution_analysis([w], ...) (dwt_pruning.py:35-95, no level clamp applied here: pass the level you want) with
+    the planes of `w` split over the ranks of `group`.  Every rank passes the same full tensor (host or device; only its own
+    planes are uploaded).  Returns (pruned, threshold, zeros): the whole pruned tensor on every rank when gather=True, else
+    this rank's planes [lo:hi] of the flattened batch; zeros = count over the whole tensor.  Bit-identical to the
+    single-GPU plan: same kernels, same order statistics, same interpolation."""
+    from . import _lib, config, engine
+    sem = numpy_semantics or config.numpy_semantics
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    dev = engine.cuda_device()
+    batch, H, W = engine.plane_geometry(w.shape)
+    if w.ndim < 2:
+        level = 0
+    lo, hi = plane_slice(batch, rank, world)
+    planes = w.reshape(batch, H, W)[lo:hi]
+    x = engine.to_device_f32(planes, dev) if hi > lo else torch.empty((0, H, W), dtype=torch.float32, device=dev)
+    sh, sw, _ = _lib.packed_shape(H, W, wavelet, level, mode)
+    n_total = batch * sh * sw                                  # what np.percentile sees: the packed array, padding zeros included
+    k0, k1, gamma = _lib.percentile_plan(n_total, float(percentile), sem)
+    packed = engine.wavedec2_packed(x, wavelet, level, mode) if hi > lo else x
+    hist = torch.zeros(1 << max(RADIX_DIGITS), dtype=torch.int64, device=dev)
+    L, s = _lib.lib(), int(torch.cuda.current_stream().cuda_stream)
+
+    def local_hist(prefix, prefix_bits, digit_bits):
+        hist.zero_()
+        if packed.numel():
+            _lib.check(L.wt_key_hist_f32(packed.data_ptr(), packed.numel(), prefix, prefix_bits, digit_bits, hist.data_ptr(), s))
+        return hist[:1 << digit_bits].cpu().numpy()
+
+    ka = global_kth_key(k0, local_hist, group)
+    kb = ka if k1 == k0 else global_kth_key(k1, local_hist, group)
+    a, b = np.array([ka, kb], dtype=np.uint32).view(np.float32)
+    t = percentile_lerp(a, b, gamma, sem)
+    del packed
+    if hi > lo:
+        res = engine.prune_device_tensors([x], [level], wavelet, mode, _lib.THRESHOLD_ABSOLUTE, float(t), sem)
+        out, zeros = res.outputs[0], int(res.counts[0, 2])
+    else:
+        out, zeros = x, 0
+    zt = torch.tensor([zeros], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(zt, op=dist.ReduceOp.SUM, group=group)
+    if not gather:
+        return out, np.float32(t), int(zt.item())
+    if world == 1:
+        return out.reshape(w.shape), np.float32(t), int(zt.item())
+    q = (batch + world - 1) // world                          # padded equal shares for all_gather_into_tensor
+    send = torch.zeros((q, H, W), dtype=torch.float32, device=dev)
+    send[:hi - lo] = out
+    recv = torch.empty((world * q, H, W), dtype=torch.float32, device=dev)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    parts = []
+    for r in range(world):
+        a0, a1 = plane_slice(batch, r, world)
+        parts.append(recv[r * q:r * q + (a1 - a0)])
+    return torch.cat(parts, 0).reshape(w.shape), np.float32(t), int(zt.item())
