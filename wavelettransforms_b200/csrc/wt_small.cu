@@ -228,6 +228,88 @@ wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __
     }
 }
 
+// MODE 0 with the next tile's copy in flight: a CTA takes SM_PAIR consecutive tiles, issues the TMA loads of all of them up
+// front (one mbarrier each) and transforms them one after the other, so only the first load's latency is exposed (ncu,
+// round 2: the one-tile kernel issues 75 % of the time; its four warps all wait for the tile before any of them computes).
+#ifndef WT_SMALL_PAIR
+#define WT_SMALL_PAIR 2
+#endif
+constexpr int SM_PAIR = WT_SMALL_PAIR;
+// tiles per CTA for H x W planes: as many as fit 40 KB of static shared memory (7 x 7 planes: one)
+template <int H, int W> struct PairTiles { static constexpr int value = (H * W * WT_SMALL_THREADS * 4 * SM_PAIR <= 40960) ? SM_PAIR : 1; };
+
+template <int H, int W, int F, class Z>
+__global__ void __launch_bounds__(WT_SMALL_THREADS)
+wt_small_analysis_pair_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __restrict__ jobs, int n_jobs, int n_tiles,
+                              long long* __restrict__ counts) {
+    constexpr int HW = H * W, NP = PairTiles<H, W>::value;
+    __shared__ __align__(16) float s_in[NP][WT_SMALL_THREADS * HW];
+    __shared__ unsigned long long bar[NP];
+    __shared__ unsigned int s_cnt[WT_SMALL_THREADS / 32];
+    __shared__ int s_job[NP], s_planes[NP], s_tma[NP];
+    __shared__ long long s_p0[NP];
+    const int tile0 = blockIdx.x * NP;
+    if (threadIdx.x < NP) {
+        const int k = threadIdx.x, tile = tile0 + k;
+        s_planes[k] = 0;
+        if (tile < n_tiles) {
+            const int j = find_small_job(jobs, n_jobs, tile);
+            const long long batch = jobs[j].batch, p0 = (long long)(tile - jobs[j].tile_begin) * WT_SMALL_THREADS;
+            const long long left = batch - p0;
+            const int cnt = left < WT_SMALL_THREADS ? (int)left : WT_SMALL_THREADS;
+            const float* src = jobs[j].in + p0 * HW;
+            const unsigned int bytes = (unsigned int)cnt * HW * 4u;
+            const bool tma_ok = ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) && ((bytes & 15u) == 0);
+            s_job[k] = j; s_planes[k] = cnt; s_p0[k] = p0; s_tma[k] = tma_ok ? 1 : 0;
+            if (tma_ok) {
+                mbar_init(&bar[k], 1);
+                bulk_load(s_in[k], src, bytes, &bar[k]);
+            }
+        }
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int k = 0; k < NP; ++k) {
+        const int cnt = s_planes[k];
+        if (cnt == 0) break;   // CTA-uniform: past the last tile of the class
+        const WtSmallJob job = jobs[s_job[k]];
+        const long long p0 = s_p0[k];
+        if (s_tma[k]) {
+            mbar_wait(&bar[k], 0);
+        } else {
+            const float* __restrict__ g = job.in + p0 * HW;
+            for (int i = threadIdx.x; i < cnt * HW; i += WT_SMALL_THREADS) s_in[k][i] = __ldg(&g[i]);
+            __syncthreads();
+        }
+        const bool valid = (int)threadIdx.x < cnt;
+        unsigned int nz = 0;
+        float x[HW];
+#pragma unroll
+        for (int i = 0; i < HW; ++i) {
+            x[i] = valid ? s_in[k][threadIdx.x * HW + i] : 0.0f;
+            nz += (x[i] != 0.0f);
+        }
+        float* __restrict__ cbase = job.coef + p0 + threadIdx.x;
+        const long long stride = job.batch;
+        auto put = [&](int idx, float v) {
+            if (valid) cbase[(long long)idx * stride] = v;
+        };
+        SmallPlane<H, W, F, WT_SMALL_MAX_LEVEL, 0, Z>::analyze(x, job.level, bk, put);
+        // nonzeros of the input (dwt_pruning_NoEntropy.py:58) and numel
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) nz += __shfl_down_sync(0xffffffffu, nz, d);
+        if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = nz;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long t = 0;
+            for (int w = 0; w < WT_SMALL_THREADS / 32; ++w) t += s_cnt[w];
+            atomicAdd(reinterpret_cast<unsigned long long*>(counts + (size_t)job.layer * 4 + 3), t);
+            if (p0 == 0) counts[(size_t)job.layer * 4] = job.batch * HW;
+        }
+        __syncthreads();   // s_cnt is reused by the next tile
+    }
+}
+
 // MODE 1 as a kernel of its own: a CTA walks SM_TPC consecutive tiles of the class and carries its warp-private staging and
 // its counters from tile to tile, so the job's global counters see one atomic per CTA and job instead of one per warp and
 // tile (measured: with one tile per CTA the returning atomics on s_count made the haar analysis 3.7x slower).
@@ -400,8 +482,11 @@ int launch_analysis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, i
         if (MODE == 1)                                                                                                   \
             wt_small_analysis_compact_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH, kFma>>                                   \
                 <<<(n_tiles + SM_TPC - 1) / SM_TPC, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, n_tiles, counts, state); \
+        else if (MODE == 0)                                                                                              \
+            wt_small_analysis_pair_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH, kFma>>                                      \
+                <<<(n_tiles + PairTiles<H, W>::value - 1) / PairTiles<H, W>::value, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, n_tiles, counts); \
         else                                                                                                             \
-            wt_small_analysis_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH, kFma>, MODE == 1 ? 0 : MODE>                     \
+            wt_small_analysis_kernel<H, W, FL, ZeroTaps<DL, DH, RL, RH, kFma>, 2>                                        \
                 <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts, state, hist1, hist1c);             \
         WT_CUDA(cudaGetLastError());                                                                                     \
         return WT_OK;                                                                                                    \
@@ -413,8 +498,11 @@ int launch_analysis_hw(const WtBank& bank, const WtSmallJob* jobs, int n_jobs, i
         if (MODE == 1)                                                                                                    \
             wt_small_analysis_compact_kernel<H, W, FL, ZeroTaps<0, 0, 0, 0, kFma>>                                        \
                 <<<(n_tiles + SM_TPC - 1) / SM_TPC, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, n_tiles, counts, state); \
+        else if (MODE == 0)                                                                                               \
+            wt_small_analysis_pair_kernel<H, W, FL, ZeroTaps<0, 0, 0, 0, kFma>>                                           \
+                <<<(n_tiles + PairTiles<H, W>::value - 1) / PairTiles<H, W>::value, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, n_tiles, counts); \
         else                                                                                                              \
-            wt_small_analysis_kernel<H, W, FL, ZeroTaps<0, 0, 0, 0, kFma>, MODE == 1 ? 0 : MODE>                          \
+            wt_small_analysis_kernel<H, W, FL, ZeroTaps<0, 0, 0, 0, kFma>, 2>                                             \
                 <<<n_tiles, WT_SMALL_THREADS, 0, stream>>>(bank, jobs, n_jobs, counts, state, hist1, hist1c);              \
         break;
     switch (bank.F) {
