@@ -236,7 +236,11 @@ wt_small_analysis_kernel(const __grid_constant__ WtBank bk, const WtSmallJob* __
 #endif
 constexpr int SM_PAIR = WT_SMALL_PAIR;
 // tiles per CTA for H x W planes: as many as fit 40 KB of static shared memory (7 x 7 planes: one)
-template <int H, int W> struct PairTiles { static constexpr int value = (H * W * WT_SMALL_THREADS * 4 * SM_PAIR <= 40960) ? SM_PAIR : 1; };
+// (1 x 1 planes -- 512 bytes per tile, nothing but memory traffic -- take eight: measured on ResNet-152's 1 x 1 class 330 us with
+// one tile per CTA, 271 with two, 250 with four; the flop-bound 3 x 3 classes lose 3 us beyond two)
+template <int H, int W> struct PairTiles {
+    static constexpr int value = (H * W == 1) ? 8 : ((H * W * WT_SMALL_THREADS * 4 * SM_PAIR <= 40960) ? SM_PAIR : 1);
+};
 
 template <int H, int W, int F, class Z>
 __global__ void __launch_bounds__(WT_SMALL_THREADS)
@@ -249,7 +253,7 @@ wt_small_analysis_pair_kernel(const __grid_constant__ WtBank bk, const WtSmallJo
     __shared__ int s_job[NP], s_planes[NP], s_tma[NP];
     __shared__ long long s_p0[NP];
     const int tile0 = blockIdx.x * NP;
-    if (threadIdx.x < NP) {
+    if (threadIdx.x < NP) {   // NP <= 8 threads describe one tile each and start its copy
         const int k = threadIdx.x, tile = tile0 + k;
         s_planes[k] = 0;
         if (tile < n_tiles) {
