@@ -183,6 +183,17 @@ int wt_plan_set_peers(WtPlan* plan, int n_peers, const int64_t* byte_deltas);
 int wt_plan_set_multicast(WtPlan* plan, int64_t byte_delta);
 int wt_plan_phase_times(WtPlan* plan, int max_phases, float* ms, int* launches, char* names,
                         int name_stride);
+/* Staged runs for callers that take the order statistic outside the plan (no counterpart in the reference; used by the
+ * intra-layer multi-GPU split).  stage 1 = every layer's analysis (coefficients stay in the plan's workspace),
+ * stage 2 = threshold with the CURRENT contents of the plan's threshold array (wt_plan_thresholds_device: the caller writes
+ * them between the stages) + synthesis + counts.  Device percentile plans on the spill kernels without peers
+ * (WT_E_UNSUPPORTED otherwise); everything on `stream`, nothing synchronised.  wt_plan_results works after stage 2. */
+int wt_plan_run_stage(WtPlan* plan, int stage, void* stream);
+/* where stage 1 left layer `layer`'s coefficients: n_explicit floats at *coef (coefficient-major for conv-kernel planes,
+ * band by band for large planes -- the ORDER is internal, the multiset is the packed array's nonzero cells and more), plus
+ * n_implicit_zeros padding cells of pywt.coeffs_to_array that np.percentile also sees (dwt_pruning.py:70,27).  Level-0
+ * layers: the input itself. */
+int wt_plan_layer_coefficients(WtPlan* plan, int layer, const float** coef, int64_t* n_explicit, int64_t* n_implicit_zeros);
 /* device address of the int64 [n_layers][4] result block of the LAST run: columns 1..3 = {nonzero, zeros,
  * nonzero_before} (column 0 is scratch: numel is known on the host).  Percentile plans alternate between two blocks,
  * so ask again after every wt_plan_run.  Valid in stream order after the run; nothing is synchronised. */

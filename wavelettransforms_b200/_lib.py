@@ -27,7 +27,7 @@ EXPORTS = [
     'wt_version', 'wt_last_error', 'wt_wavelet_lookup', 'wt_wavelet_filters', 'wt_dwt_max_level', 'wt_dwt_coeff_len',
     'wt_packed_shape', 'wt_percentile_plan', 'wt_plan_create', 'wt_plan_destroy', 'wt_plan_device_bytes',
     'wt_plan_num_launches', 'wt_plan_set_io', 'wt_plan_run', 'wt_plan_results', 'wt_plan_counts_device', 'wt_plan_thresholds_device',
-    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path', 'wt_plan_set_arithmetic', 'wt_plan_set_multicast', 'wt_plan_set_graph',
+    'wt_plan_set_timing', 'wt_plan_phase_times', 'wt_plan_set_peers', 'wt_plan_select_path', 'wt_plan_set_arithmetic', 'wt_plan_set_multicast', 'wt_plan_set_graph', 'wt_plan_run_stage', 'wt_plan_layer_coefficients',
     'wt_dwt_prune_f32', 'wt_select_abs_f32', 'wt_select_abs_noalloc_f32', 'wt_wavedec2_packed_f32', 'wt_waverec2_packed_f32',
     'wt_min_weight_prune_f32', 'wt_scatter_zero_f32', 'wt_count_f32', 'wt_key_hist_f32',
 ]
@@ -66,6 +66,8 @@ def lib():
     L.wt_plan_thresholds_device.argtypes = [vp, P(vp)]
     L.wt_plan_set_timing.argtypes = [vp, ci]
     L.wt_plan_set_graph.argtypes = [vp, ci]
+    L.wt_plan_run_stage.argtypes = [vp, ci, vp]
+    L.wt_plan_layer_coefficients.argtypes = [vp, ci, P(vp), P(i64), P(i64)]
     L.wt_plan_select_path.argtypes = [vp]
     L.wt_plan_set_arithmetic.argtypes = [vp, ci]
     L.wt_plan_set_multicast.argtypes = [vp, i64]
@@ -182,6 +184,16 @@ class Plan:
         check(lib().wt_plan_results(self._h, ctypes.c_void_p(stream), counts, nzb, thr))
         c = np.array(counts[:3 * self.n], dtype=np.int64).reshape(self.n, 3)
         return c, np.array(nzb[:self.n], dtype=np.int64), np.array(thr[:self.n], dtype=np.float32)
+
+    def run_stage(self, stage, stream=0):
+        """1: analysis only; 2: threshold (whatever the plan's threshold array holds) + synthesis (wtprune.h: wt_plan_run_stage)"""
+        check(lib().wt_plan_run_stage(self._h, int(stage), ctypes.c_void_p(stream)))
+
+    def layer_coefficients(self, layer):
+        """(device address, explicit coefficients, implicit padding zeros) of a layer after run_stage(1)"""
+        p, n, z = ctypes.c_void_p(), ctypes.c_int64(), ctypes.c_int64()
+        check(lib().wt_plan_layer_coefficients(self._h, int(layer), ctypes.byref(p), ctypes.byref(n), ctypes.byref(z)))
+        return int(p.value or 0), int(n.value), int(z.value)
 
     def device_result_pointers(self):
         """(address of the int64 [n][4] block {scratch, nonzero, zeros, nonzero_before} of the last run, address of the

@@ -1140,6 +1140,73 @@ extern "C" int wt_plan_run(WtPlan* P, void* stream_) {
     return WT_OK;
 }
 
+// ---- staged runs: analysis and synthesis as separate calls, the threshold supplied by the caller ----------------------
+// For callers that take the order statistic OUTSIDE the plan -- the intra-layer multi-GPU split (sharded.py:
+// prune_tensor_split) agrees on one threshold over every rank's coefficients.  Stage 1 transforms (coefficients stay in
+// the plan's workspace: wt_plan_layer_coefficients), stage 2 thresholds with whatever sits in the plan's threshold
+// array (wt_plan_thresholds_device) and reconstructs.  Percentile plans on the caller's stream, kernels one after the other.
+extern "C" int wt_plan_run_stage(WtPlan* P, int stage, void* stream_) {
+    WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
+    WT_CHECK(stage == 1 || stage == 2, WT_E_INVALID, "wt_plan_run_stage: stage 1 (analysis) or 2 (threshold + synthesis)");
+    WT_CHECK(!P->host_io && P->thr_kind == WT_THRESHOLD_PERCENTILE && P->fused.empty() && !P->precompact && P->peers.n == 0,
+             WT_E_UNSUPPORTED, "wt_plan_run_stage: device percentile plans on the spill kernels, without peers");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int n = (int)P->layers.size();
+    int launches = 0, rc = WT_OK;
+    if (stage == 1) {
+        advance_run_state(P);
+        ++P->run_count;
+        // no select kernel runs here, and it is the select that zeroes the block of the plan's next run: clear both, so that
+        // staged and whole runs of one plan can be mixed
+        for (int q = 0; q < 2; ++q)
+            if (P->zero_blocks[q] && P->zero_bytes) WT_CUDA(cudaMemsetAsync(P->zero_blocks[q], 0, P->zero_bytes, stream));
+        for (auto& c : P->small) {
+            rc = wt_small_analysis_launch(c.H, c.W, P->bank, P->arithmetic, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->counts_dev, stream);
+            if (rc) return rc;
+            if (c.n_tiles) ++launches;
+        }
+        for (auto& g : P->generic) {
+            rc = (P->arithmetic ? wt_generic_analysis_fma : wt_generic_analysis)(P->bank, P->mode, g, P->counts_dev, stream, &launches);
+            if (rc) return rc;
+        }
+    } else {
+        for (int i = 0; i < n; ++i)   // level-0 layers: the compare itself (it also counts the nonzero inputs)
+            if (P->path[i] == PATH_LEVEL0) {
+                rc = wt_apply_threshold_launch(P->d_in[i], P->d_out[i], layer_numel(P->layers[i]), P->thresholds_dev + i, 0.0f,
+                                               P->counts_dev + (size_t)i * 4, stream);
+                if (rc) return rc;
+                ++launches;
+            }
+        for (auto& c : P->small) {
+            rc = wt_small_synthesis_launch(c.H, c.W, P->bank, P->arithmetic, c.jobs_dev, (int)c.jobs.size(), c.n_tiles, P->thresholds_dev,
+                                           P->counts_dev, stream);
+            if (rc) return rc;
+            if (c.n_tiles) ++launches;
+        }
+        for (auto& g : P->generic) {
+            rc = (P->arithmetic ? wt_generic_synthesis_fma : wt_generic_synthesis)(P->bank, P->mode, g, P->thresholds_dev, P->counts_dev, stream,
+                                                                                   &launches);
+            if (rc) return rc;
+        }
+    }
+    P->n_launches = launches;
+    return WT_OK;
+}
+
+extern "C" int wt_plan_layer_coefficients(WtPlan* P, int layer, const float** coef, int64_t* n_explicit, int64_t* n_implicit_zeros) {
+    WT_CHECK(P != nullptr && coef != nullptr && n_explicit != nullptr && n_implicit_zeros != nullptr, WT_E_INVALID, "NULL argument");
+    WT_CHECK(!P->host_io, WT_E_UNSUPPORTED, "host-I/O plans keep their workspaces per layer group");
+    WT_CHECK(layer >= 0 && layer < (int)P->layers.size(), WT_E_INVALID, "layer %d out of range", layer);
+    *coef = nullptr; *n_explicit = 0; *n_implicit_zeros = 0;
+    switch (P->path[layer]) {
+        case PATH_EMPTY: return WT_OK;
+        case PATH_LEVEL0: *coef = P->d_in[layer]; *n_explicit = layer_numel(P->layers[layer]); return WT_OK;   // level 0: the weights themselves
+        case PATH_SMALL:
+        case PATH_GENERIC: *coef = P->d_coef[layer]; *n_explicit = P->ncoef[layer]; *n_implicit_zeros = P->zeros[layer]; return WT_OK;
+        default: wt_set_error("layer %d runs on the fused recompute kernels, which keep no coefficients", layer); return WT_E_UNSUPPORTED;
+    }
+}
+
 extern "C" int wt_plan_set_graph(WtPlan* P, int enable) {
     WT_CHECK(P != nullptr, WT_E_INVALID, "plan is NULL");
     for (WtPlan* c : P->children) {

@@ -294,7 +294,11 @@ def prune_tensor_split(w: torch.Tensor, wavelet: str, level: int, percentile: fl
     the planes of `w` split over the ranks of `group`.  Every rank passes the same full tensor (host or device; only its own
     planes are uploaded).  Returns (pruned, threshold, zeros): the whole pruned tensor on every rank when gather=True, else
     this rank's planes [lo:hi] of the flattened batch; zeros = count over the whole tensor.  Bit-identical to the
-    single-GPU plan: same kernels, same order statistics, same interpolation."""
+    single-GPU plan: same kernels, same order statistics, same interpolation.
+
+    One plan per rank, run in two stages (wt_plan_run_stage): the analysis leaves the coefficients in the plan's workspace,
+    the ranks agree on the threshold (three histogram passes over them + three all-reduces per order statistic), the
+    threshold goes into the plan's threshold array, and the second stage thresholds and reconstructs."""
     from . import _lib, config, engine
     sem = numpy_semantics or config.numpy_semantics
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -304,34 +308,55 @@ def prune_tensor_split(w: torch.Tensor, wavelet: str, level: int, percentile: fl
     if w.ndim < 2:
         level = 0
     lo, hi = plane_slice(batch, rank, world)
-    planes = w.reshape(batch, H, W)[lo:hi]
-    x = engine.to_device_f32(planes, dev) if hi > lo else torch.empty((0, H, W), dtype=torch.float32, device=dev)
     sh, sw, _ = _lib.packed_shape(H, W, wavelet, level, mode)
     n_total = batch * sh * sw                                  # what np.percentile sees: the packed array, padding zeros included
     k0, k1, gamma = _lib.percentile_plan(n_total, float(percentile), sem)
-    packed = engine.wavedec2_packed(x, wavelet, level, mode) if hi > lo else x
-    hist = torch.zeros(1 << max(RADIX_DIGITS), dtype=torch.int64, device=dev)
     L, s = _lib.lib(), int(torch.cuda.current_stream().cuda_stream)
-
-    def local_hist(prefix, prefix_bits, digit_bits):
-        hist.zero_()
-        if packed.numel():
-            _lib.check(L.wt_key_hist_f32(packed.data_ptr(), packed.numel(), prefix, prefix_bits, digit_bits, hist.data_ptr(), s))
-        return hist[:1 << digit_bits].cpu().numpy()
-
-    ka = global_kth_key(k0, local_hist, group)
-    kb = ka if k1 == k0 else global_kth_key(k1, local_hist, group)
-    a, b = np.array([ka, kb], dtype=np.uint32).view(np.float32)
-    t = percentile_lerp(a, b, gamma, sem)
-    del packed
+    plan, x, out = None, None, None
+    coef_ptr, n_explicit, n_implicit = 0, 0, 0
     if hi > lo:
-        res = engine.prune_device_tensors([x], [level], wavelet, mode, _lib.THRESHOLD_ABSOLUTE, float(t), sem)
-        out, zeros = res.outputs[0], int(res.counts[0, 2])
-    else:
-        out, zeros = x, 0
+        x = engine.to_device_f32(w.reshape(batch, H, W)[lo:hi], dev)
+        out = torch.empty_like(x)
+        plan = _lib.Plan([(x.data_ptr(), out.data_ptr(), hi - lo, H, W, level)], wavelet, mode, _lib.THRESHOLD_PERCENTILE,
+                         float(percentile), sem)
+    try:
+        if plan is not None:
+            plan.run_stage(1, s)
+            coef_ptr, n_explicit, n_implicit = plan.layer_coefficients(0)
+        zt = torch.tensor([n_implicit], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(zt, op=dist.ReduceOp.SUM, group=group)
+        implicit_total = int(zt.item())                        # padding cells of coeffs_to_array over the whole tensor
+        hist = torch.zeros(1 << max(RADIX_DIGITS), dtype=torch.int64, device=dev)
+
+        def local_hist(prefix, prefix_bits, digit_bits):
+            hist.zero_()
+            if n_explicit:
+                _lib.check(L.wt_key_hist_f32(coef_ptr, n_explicit, prefix, prefix_bits, digit_bits, hist.data_ptr(), s))
+            return hist[:1 << digit_bits].cpu().numpy()
+
+        def kth(k):                                            # the implicit zeros sort first
+            return 0 if k < implicit_total else global_kth_key(k - implicit_total, local_hist, group)
+
+        ka = kth(k0)
+        kb = ka if k1 == k0 else kth(k1)
+        a, b = np.array([ka, kb], dtype=np.uint32).view(np.float32)
+        t = percentile_lerp(a, b, gamma, sem)
+        zeros = 0
+        if plan is not None:
+            _, thr_ptr = plan.device_result_pointers()
+            torch.as_tensor(engine._DeviceBlock(thr_ptr, (1,), '<f4'), device=dev).fill_(float(t))
+            plan.run_stage(2, s)
+            counts, _, _ = plan.results(s)
+            zeros = int(counts[0, 2])
+    finally:
+        if plan is not None:
+            plan.close()
     zt = torch.tensor([zeros], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(zt, op=dist.ReduceOp.SUM, group=group)
+    if out is None:
+        out = torch.empty((0, H, W), dtype=torch.float32, device=dev)
     if not gather:
         return out, np.float32(t), int(zt.item())
     if world == 1:
