@@ -135,3 +135,52 @@ def test_large_plane_plans_replay_by_default():
         for a, b in zip(bits, res[0][0]):
             assert np.array_equal(a, b), r
         assert np.array_equal(counts, res[0][1]) and np.array_equal(nzb, res[0][2]) and np.array_equal(thr, res[0][3]), r
+
+
+def test_staged_runs_equal_the_whole_run_and_can_be_mixed_with_it():
+    """wt_plan_run_stage: analysis and (threshold + synthesis) as two calls, the threshold taken from the plan's threshold
+    array -- here the one the whole run just left there -- give the whole run's bits and counts; whole runs before and
+    after a staged one (alternating scratch blocks, graph replay) stay right; the coefficient workspace is exposed"""
+    from wavelettransforms_b200 import _lib, engine
+    dev = torch.device('cuda', 0)
+    xs = [w.to(dev) for w in _weights(6)]
+    outs = [torch.empty_like(x) for x in xs]
+    levels = (2, 1, 0, 2)
+    items = [(x.data_ptr(), o.data_ptr()) + engine.plane_geometry(x.shape) + (lv,) for x, o, lv in zip(xs, outs, levels)]
+    plan = _lib.Plan(items, 'bior2.2', 'periodization', _lib.THRESHOLD_PERCENTILE, 72.0, 'legacy_1_22')
+    st = torch.cuda.Stream()
+    try:
+        with torch.cuda.stream(st):
+            s = int(st.cuda_stream)
+
+            def snapshot():
+                counts, nzb, thr = plan.results(s)
+                return [_bits(o).copy() for o in outs], np.array(counts), np.array(nzb), np.array(thr).view(np.uint32)
+
+            plan.run(s)
+            ref = snapshot()
+            for rounds in range(2):
+                for o in outs:
+                    o.fill_(float('nan'))
+                plan.run_stage(1, s)
+                ptr, n_explicit, n_implicit = plan.layer_coefficients(0)
+                b, h, w = engine.plane_geometry(xs[0].shape)
+                sh, sw, ncoef = _lib.packed_shape(h, w, 'bior2.2', levels[0], 'periodization')
+                assert ptr != 0 and n_explicit == b * ncoef and n_implicit == b * (sh * sw - ncoef)
+                ptr0, n0, z0 = plan.layer_coefficients(2)          # level 0: the input itself
+                assert ptr0 == xs[2].data_ptr() and n0 == xs[2].numel() and z0 == 0
+                plan.run_stage(2, s)
+                got = snapshot()
+                for a, bb in zip(got[0], ref[0]):
+                    assert np.array_equal(a, bb)
+                assert all(np.array_equal(a, bb) for a, bb in zip(got[1:], ref[1:]))
+                for _ in range(3):                                  # whole runs again: plain, capture, replay
+                    for o in outs:
+                        o.fill_(float('nan'))
+                    plan.run(s)
+                    got = snapshot()
+                    for a, bb in zip(got[0], ref[0]):
+                        assert np.array_equal(a, bb)
+                    assert all(np.array_equal(a, bb) for a, bb in zip(got[1:], ref[1:]))
+    finally:
+        plan.close()
